@@ -1,0 +1,142 @@
+/*
+ * ntxent_b200.h -- C ABI of the B200-native NT-Xent library (libntxent_b200.so).
+ *
+ * The library replaces ONE path of nzw0301/SimCLR: the NT-Xent loss forward and
+ * backward of `loss.py` (class NT_Xent, loss.py:4-65) plus the row-sharded
+ * multi-GPU form of it.  The reference is pure Python and has no FFI of its
+ * own; these entry points are what a ctypes binding inside the reference's
+ * `loss.py` would bind (INTEGRATION.md shows that stub).  Each declaration
+ * cites the reference lines it replaces.
+ *
+ * Conventions
+ *  - every function returns 0 on success, a negative NTX_E_* code otherwise;
+ *    ntx_last_error() returns a thread-local message for the last failure;
+ *  - no C++ exception crosses the boundary, no torch type appears in a signature;
+ *  - the caller owns every buffer (device memory, 16-byte aligned, row-major);
+ *    the library allocates nothing, creates no stream and never synchronises
+ *    the device -- all work is enqueued on `stream` (a cudaStream_t passed as
+ *    void*; NULL = the legacy default stream);
+ *  - callable from any host thread (PyTorch runs backward on its autograd
+ *    thread, main.py:115); no thread-affine state is kept;
+ *  - "views": the two (N, D) embedding matrices `view0`, `view1` of loss.py:25.
+ *    "rows": the 2N L2-normalised embeddings ordered [view0 ; view1].
+ *    "keys": the rows every query row is compared against -- the rank's own
+ *    rows, or with W ranks the rank-major concatenation of all ranks' rows.
+ */
+#ifndef NTXENT_B200_H
+#define NTXENT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NTX_VERSION 100 /* 0.1.0 */
+
+/* element types of caller buffers */
+#define NTX_F32 0
+#define NTX_BF16 1
+
+/* error codes */
+#define NTX_OK 0
+#define NTX_E_ARG (-1)       /* bad argument (shape, dtype, alignment, temperature) */
+#define NTX_E_WORKSPACE (-2) /* scratch buffer missing or too small */
+#define NTX_E_CUDA (-3)      /* a CUDA runtime / driver call failed */
+#define NTX_E_UNSUPPORTED (-4)
+
+/* reduction of loss.py:54-65 */
+#define NTX_REDUCE_NONE 0
+#define NTX_REDUCE_MEAN 1
+#define NTX_REDUCE_SUM 2
+
+/* Where this rank's rows sit among the keys.
+ * n_local : pairs held by this rank (N of loss.py:36 when world == 1)
+ * world   : number of ranks whose rows form the keys (1 = the reference's local loss)
+ * rank    : this rank's chunk; its 2*n_local rows are keys [rank*2*n_local, (rank+1)*2*n_local)
+ * Row r (0 <= r < 2*n_local) has self column rank*2*n_local + r (the diagonal the
+ * mask at loss.py:38,46-47 removes) and positive column
+ * rank*2*n_local + (r + n_local) mod 2*n_local (targets = arange(N), loss.py:37,51-52). */
+typedef struct NtxLayout {
+    int32_t n_local;
+    int32_t world;
+    int32_t rank;
+} NtxLayout;
+
+/* How a launch is cut into work: pure integer arithmetic, no device needed.
+ * Filled by ntx_plan(); the same plan drives the main kernel and its finalize. */
+typedef struct NtxPlan {
+    int32_t tile_rows;     /* query rows per tile */
+    int32_t tile_keys;     /* keys per tile */
+    int32_t row_blocks;    /* ceil(q_rows / tile_rows) */
+    int32_t key_tiles;     /* ceil(k_rows / tile_keys) */
+    int32_t grid;          /* CTAs of the main kernel; CTA i owns tiles [i*T/grid, (i+1)*T/grid) */
+    int32_t max_slots;     /* most CTAs that share one row block (partials per row) */
+    int32_t d_pad;         /* feature dim padded to the kernel's granule */
+    int32_t tensor_cores;  /* 1 = tcgen05 path (bf16 rows), 0 = fp32 CUDA-core path */
+    uint64_t fwd_ws_bytes; /* scratch ntx_fwd needs */
+    uint64_t bwd_ws_bytes; /* scratch ntx_bwd needs */
+} NtxPlan;
+
+int ntx_version(void);
+const char* ntx_last_error(void);
+
+/* Leading dimension (elements per row) the library wants for normalised rows of
+ * feature size d in dtype NTX_F32 / NTX_BF16: d rounded up to 4 (fp32) or 64 (bf16). */
+int ntx_row_pitch(int d, int dtype);
+
+/* Integer planning shared by ntx_fwd/ntx_bwd and their finalize kernels.
+ * sm_count <= 0 means "ask the current device". */
+int ntx_plan(int q_rows, int k_rows, int d, int dtype, int sm_count, NtxPlan* plan);
+
+/* L2-normalise both views into one [2n x ld] row buffer: rows [0,n) from view0,
+ * rows [n,2n) from view1, zero padded from d to ld.  Replaces the two
+ * F.normalize calls at loss.py:33-34 (x / max(||x||_2, 1e-12)).
+ * inv_norm[r] = 1 / max(||row r||, 1e-12).  view pointers are (n x d), contiguous. */
+int ntx_l2norm(const void* view0, const void* view1, int n, int d, int in_dtype,
+               void* rows, int ld, int rows_dtype, float* inv_norm, void* stream);
+
+/* Forward.  For each of this rank's q_rows = 2*n_local rows:
+ *   rowsum[r]   = sum over keys c != self of exp(s_rc - 1/tau),  s = <row r, key c> / tau
+ *   pos_logit[r]= s at the positive column
+ *   row_loss[r] = log(rowsum[r]) + 1/tau - pos_logit[r]     (layout (2, n_local): loss.py:55-58)
+ *   loss_sum[0] = sum of row_loss                             (loss.py:60-61)
+ *   loss_sum[1] = loss_sum[0] / q_rows                        (loss.py:65, "mean")
+ * Replaces loss.py:36-61: the three similarity GEMMs (:42,43,49), the boolean-mask
+ * diagonal removal (:38,46-47), the concatenations (:51-52) and both cross-entropies
+ * (:56-61); the 2N x 2N logits are never written to memory.
+ * q_rows_ptr/k_rows_ptr: normalised rows ([q_rows x ld], [k_rows x ld]) of `dtype`. */
+int ntx_fwd(const void* q_rows_ptr, const void* k_rows_ptr, int q_rows, int k_rows, int d, int ld,
+            int dtype, const NtxLayout* layout, float temperature, float* rowsum,
+            float* pos_logit, float* row_loss, float* loss_sum, void* workspace,
+            size_t workspace_bytes, void* stream);
+
+/* Row weights for backward from the upstream gradient: w_r = grad_output * scale
+ * (reduce mean/sum: grad_output is one float on the device, scale = 1/(2*n_local) or 1)
+ * or w_r = grad_output[r] (reduce none, (2, n_local) floats).  Writes w[r] and
+ * coef[r] = w_r / rowsum[r].  This is the d(cross_entropy)/d(logits) scaling that
+ * autograd derives from loss.py:56-65. */
+int ntx_bwd_prep(const float* rowsum, const float* grad_output, int reduction, int q_rows,
+                 float* w, float* coef, void* stream);
+
+/* Backward: gradient of sum_r w_r * row_loss_r with respect to view0/view1 for this
+ * rank's rows, including the terms in which its rows act as keys of other rows
+ * (coef_k carries w/rowsum of every key, all-gathered by the caller when world > 1).
+ * Replaces the autograd graph of loss.py:33-65 (softmax - onehot, un-concatenate,
+ * index_put through the mask, six GEMMs, normalisation Jacobian).
+ * dview0/dview1 are (n_local x d) in `in_dtype`, like view0/view1. */
+int ntx_bwd(const void* q_rows_ptr, const void* k_rows_ptr, int q_rows, int k_rows, int d, int ld,
+            int dtype, const NtxLayout* layout, float temperature, const float* coef_q,
+            const float* coef_k, const float* w_q, const void* view0, const void* view1,
+            int in_dtype, const float* inv_norm, void* dview0, void* dview1, void* workspace,
+            size_t workspace_bytes, void* stream);
+
+/* Test entry: the self and positive column of every row, computed on the device by
+ * the same helper the kernels use (bit-exact contract on loss.py:37-38 indexing). */
+int ntx_debug_indices(const NtxLayout* layout, int32_t* self_col, int32_t* pos_col, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NTXENT_B200_H */

@@ -1,0 +1,137 @@
+"""ctypes binding of libntxent_b200.so (include/ntxent_b200.h).
+
+The library is the product; there is no CPU or pure-PyTorch fallback.  If it
+has not been built, loading raises with the command that builds it.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import threading
+
+import torch
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG, "libntxent_b200.so")
+
+NTX_F32, NTX_BF16 = 0, 1
+REDUCTIONS = {"none": 0, "mean": 1, "sum": 2}
+DTYPES = {torch.float32: NTX_F32, torch.bfloat16: NTX_BF16}
+
+EXPORTS = (
+    "ntx_version", "ntx_last_error", "ntx_row_pitch", "ntx_plan", "ntx_l2norm", "ntx_fwd",
+    "ntx_bwd_prep", "ntx_bwd", "ntx_debug_indices",
+)
+
+
+class NtxLayout(ctypes.Structure):
+    _fields_ = [("n_local", ctypes.c_int32), ("world", ctypes.c_int32), ("rank", ctypes.c_int32)]
+
+
+class NtxPlan(ctypes.Structure):
+    _fields_ = [
+        ("tile_rows", ctypes.c_int32), ("tile_keys", ctypes.c_int32), ("row_blocks", ctypes.c_int32),
+        ("key_tiles", ctypes.c_int32), ("grid", ctypes.c_int32), ("max_slots", ctypes.c_int32),
+        ("d_pad", ctypes.c_int32), ("tensor_cores", ctypes.c_int32),
+        ("fwd_ws_bytes", ctypes.c_uint64), ("bwd_ws_bytes", ctypes.c_uint64),
+    ]
+
+
+class NtxError(RuntimeError):
+    def __init__(self, code: int, message: str):
+        super().__init__(f"libntxent_b200 error {code}: {message}")
+        self.code = code
+
+
+_lock = threading.Lock()
+_lib = None
+
+
+def _declare(lib):
+    vp, i, f, sz = ctypes.c_void_p, ctypes.c_int, ctypes.c_float, ctypes.c_size_t
+    lib.ntx_version.restype = i
+    lib.ntx_last_error.restype = ctypes.c_char_p
+    lib.ntx_row_pitch.argtypes = [i, i]
+    lib.ntx_plan.argtypes = [i, i, i, i, i, ctypes.POINTER(NtxPlan)]
+    lib.ntx_l2norm.argtypes = [vp, vp, i, i, i, vp, i, i, vp, vp]
+    lib.ntx_fwd.argtypes = [vp, vp, i, i, i, i, i, ctypes.POINTER(NtxLayout), f, vp, vp, vp, vp, vp, sz, vp]
+    lib.ntx_bwd_prep.argtypes = [vp, vp, i, i, vp, vp, vp]
+    lib.ntx_bwd.argtypes = [vp, vp, i, i, i, i, i, ctypes.POINTER(NtxLayout), f, vp, vp, vp, vp, vp, i,
+                            vp, vp, vp, vp, sz, vp]
+    lib.ntx_debug_indices.argtypes = [ctypes.POINTER(NtxLayout), vp, vp, vp]
+    for name in EXPORTS:
+        if name != "ntx_last_error":
+            getattr(lib, name).restype = i
+
+
+def load():
+    """The loaded library (built by ``python -m simclr_b200.build`` / ``__graft_entry__.build()``)."""
+    global _lib
+    if _lib is None:
+        with _lock:
+            if _lib is None:
+                if not os.path.exists(LIB_PATH):
+                    raise RuntimeError(
+                        f"{LIB_PATH} is missing: the CUDA library is the only implementation of this "
+                        "path (no CPU fallback). Build it with `python -m simclr_b200.build`.")
+                lib = ctypes.CDLL(LIB_PATH)
+                _declare(lib)
+                _lib = lib
+    return _lib
+
+
+def _check(rc: int):
+    if rc != 0:
+        raise NtxError(rc, load().ntx_last_error().decode("utf-8", "replace"))
+
+
+def _stream(t: torch.Tensor) -> int:
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+class Backend:
+    """Tensor-level view of the C ABI.  Every method enqueues on the current stream of the
+    tensors' device and returns immediately."""
+
+    name = "libntxent_b200"
+
+    def row_pitch(self, d: int, dtype: torch.dtype) -> int:
+        return load().ntx_row_pitch(d, DTYPES[dtype])
+
+    def plan(self, q_rows: int, k_rows: int, d: int, dtype: torch.dtype, sm_count: int = 0) -> NtxPlan:
+        p = NtxPlan()
+        _check(load().ntx_plan(q_rows, k_rows, d, DTYPES[dtype], sm_count, ctypes.byref(p)))
+        return p
+
+    def l2norm(self, view0, view1, rows, inv_norm):
+        n, d = view0.shape
+        _check(load().ntx_l2norm(view0.data_ptr(), view1.data_ptr(), n, d, DTYPES[view0.dtype],
+                                 rows.data_ptr(), rows.shape[1], DTYPES[rows.dtype],
+                                 inv_norm.data_ptr(), _stream(rows)))
+
+    def fwd(self, q, k, d, layout, temperature, rowsum, pos_logit, row_loss, loss_sum, workspace):
+        lay = NtxLayout(*layout)
+        _check(load().ntx_fwd(q.data_ptr(), k.data_ptr(), q.shape[0], k.shape[0], d, q.shape[1],
+                              DTYPES[q.dtype], ctypes.byref(lay), float(temperature), rowsum.data_ptr(),
+                              pos_logit.data_ptr(), row_loss.data_ptr(), loss_sum.data_ptr(),
+                              workspace.data_ptr(), workspace.numel() * workspace.element_size(),
+                              _stream(q)))
+
+    def bwd_prep(self, rowsum, grad_output, reduction, w, coef):
+        _check(load().ntx_bwd_prep(rowsum.data_ptr(), grad_output.data_ptr(), REDUCTIONS[reduction],
+                                   rowsum.numel(), w.data_ptr(), coef.data_ptr(), _stream(rowsum)))
+
+    def bwd(self, q, k, d, layout, temperature, coef_q, coef_k, w_q, view0, view1, inv_norm, dview0,
+            dview1, workspace):
+        lay = NtxLayout(*layout)
+        _check(load().ntx_bwd(q.data_ptr(), k.data_ptr(), q.shape[0], k.shape[0], d, q.shape[1],
+                              DTYPES[q.dtype], ctypes.byref(lay), float(temperature), coef_q.data_ptr(),
+                              coef_k.data_ptr(), w_q.data_ptr(), view0.data_ptr(), view1.data_ptr(),
+                              DTYPES[view0.dtype], inv_norm.data_ptr(), dview0.data_ptr(),
+                              dview1.data_ptr(), workspace.data_ptr(),
+                              workspace.numel() * workspace.element_size(), _stream(q)))
+
+    def debug_indices(self, layout, self_col, pos_col):
+        lay = NtxLayout(*layout)
+        _check(load().ntx_debug_indices(ctypes.byref(lay), self_col.data_ptr(), pos_col.data_ptr(),
+                                        _stream(self_col)))

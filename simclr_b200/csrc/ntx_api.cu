@@ -1,0 +1,216 @@
+// extern "C" surface of libntxent_b200.so (see include/ntxent_b200.h).
+// Validates arguments, derives the work partition and enqueues kernels on the
+// caller's stream.  Allocates nothing, never synchronises.
+#include <stdarg.h>
+#include <string.h>
+
+#include "ntx_common.cuh"
+
+static thread_local char g_err[512] = "";
+
+void ntx_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+namespace {
+
+constexpr int kTcMaxD = 256;   // widest padded feature dim the tcgen05 kernels hold in smem
+
+int cached_sm_count(int* out) {
+    static int counts[64];
+    static bool have[64];
+    int dev = 0;
+    NTX_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) dev = 0;
+    if (!have[dev]) {
+        int n = 0;
+        NTX_CUDA(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev));
+        counts[dev] = n;
+        have[dev] = true;
+    }
+    *out = counts[dev];
+    return NTX_OK;
+}
+
+int check_layout(const NtxLayout* L, int q_rows, int k_rows) {
+    NTX_CHECK_ARG(L != nullptr, "layout is NULL");
+    NTX_CHECK_ARG(L->n_local >= 1 && L->world >= 1 && L->rank >= 0 && L->rank < L->world,
+                  "bad layout (n_local=%d world=%d rank=%d)", L->n_local, L->world, L->rank);
+    NTX_CHECK_ARG(q_rows == 2 * L->n_local, "q_rows=%d must equal 2*n_local=%d", q_rows,
+                  2 * L->n_local);
+    NTX_CHECK_ARG((long long)k_rows == (long long)q_rows * L->world,
+                  "k_rows=%d must equal q_rows*world=%lld", k_rows, (long long)q_rows * L->world);
+    return NTX_OK;
+}
+
+int make_dims(int q_rows, int k_rows, int d, int ld, int dtype, const NtxLayout* L, float temperature,
+              NtxDims* dm) {
+    NTX_CHECK_ARG(dtype == NTX_F32 || dtype == NTX_BF16, "rows dtype %d not supported", dtype);
+    NTX_CHECK_ARG(d >= 1, "feature dim d=%d must be positive", d);
+    NTX_CHECK_ARG(ld == ntx_row_pitch(d, dtype), "ld=%d must be ntx_row_pitch(d=%d)=%d", ld, d,
+                  ntx_row_pitch(d, dtype));
+    NTX_CHECK_ARG(temperature > 0.f, "temperature must be positive (loss.py:16)");
+    NTX_CHECK_ARG(temperature >= NTX_MIN_TEMPERATURE,
+                  "temperature %g is below %g: the fixed-shift logsumexp would underflow fp32",
+                  (double)temperature, (double)NTX_MIN_TEMPERATURE);
+    int rc = check_layout(L, q_rows, k_rows);
+    if (rc) return rc;
+    dm->q_rows = q_rows; dm->k_rows = k_rows; dm->d = d; dm->ld = ld;
+    dm->n_local = L->n_local; dm->rank = L->rank;
+    dm->inv_tau = 1.0f / temperature;
+    dm->c1 = NTX_LOG2E / temperature;
+    return NTX_OK;
+}
+
+int aligned16(const void* p, const char* what) {
+    NTX_CHECK_ARG(p != nullptr, "%s is NULL", what);
+    NTX_CHECK_ARG(reinterpret_cast<uintptr_t>(p) % 16 == 0, "%s must be 16-byte aligned", what);
+    return NTX_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ntx_version(void) { return NTX_VERSION; }
+const char* ntx_last_error(void) { return g_err; }
+
+int ntx_row_pitch(int d, int dtype) {
+    if (d < 1) return 0;
+    const int g = dtype == NTX_BF16 ? 64 : 4;
+    return (d + g - 1) / g * g;
+}
+
+int ntx_plan(int q_rows, int k_rows, int d, int dtype, int sm_count, NtxPlan* plan) {
+    NTX_CHECK_ARG(plan != nullptr, "plan is NULL");
+    NTX_CHECK_ARG(q_rows >= 1 && k_rows >= q_rows && d >= 1, "bad sizes q_rows=%d k_rows=%d d=%d",
+                  q_rows, k_rows, d);
+    NTX_CHECK_ARG(dtype == NTX_F32 || dtype == NTX_BF16, "rows dtype %d not supported", dtype);
+    if (sm_count <= 0) {
+        int rc = cached_sm_count(&sm_count);
+        if (rc) return rc;
+    }
+    memset(plan, 0, sizeof(*plan));
+    plan->d_pad = ntx_row_pitch(d, dtype);
+    plan->tensor_cores = dtype == NTX_BF16 ? 1 : 0;
+    if (plan->tensor_cores) {
+        if (plan->d_pad > kTcMaxD) {
+            ntx_set_error("bf16 rows: d=%d pads to %d > %d features per tile", d, plan->d_pad, kTcMaxD);
+            return NTX_E_UNSUPPORTED;
+        }
+        if (plan->d_pad == 192) plan->d_pad = 256;   // kernels are built for 64 / 128 / 256
+        plan->tile_rows = 128;
+        plan->tile_keys = 128;
+    } else {
+        plan->tile_rows = 64;
+        plan->tile_keys = 64;
+    }
+    plan->row_blocks = (q_rows + plan->tile_rows - 1) / plan->tile_rows;
+    plan->key_tiles = (k_rows + plan->tile_keys - 1) / plan->tile_keys;
+    const long long T = (long long)plan->row_blocks * plan->key_tiles;
+    const long long ctas = (long long)sm_count * (plan->tensor_cores ? 1 : 2);
+    plan->grid = (int)(T < ctas ? T : ctas);
+    int max_slots = 1;
+    for (int rb = 0; rb < plan->row_blocks; ++rb) {
+        const int s = ntx_num_slots(T, plan->grid, plan->key_tiles, rb);
+        if (s > max_slots) max_slots = s;
+    }
+    plan->max_slots = max_slots;
+    const uint64_t rows_pad = (uint64_t)plan->row_blocks * plan->tile_rows;
+    plan->fwd_ws_bytes = (uint64_t)max_slots * rows_pad * sizeof(float);
+    plan->bwd_ws_bytes = (uint64_t)max_slots * rows_pad * plan->d_pad * sizeof(float);
+    return NTX_OK;
+}
+
+int ntx_l2norm(const void* view0, const void* view1, int n, int d, int in_dtype, void* rows, int ld,
+               int rows_dtype, float* inv_norm, void* stream) {
+    NTX_CHECK_ARG(n >= 1 && d >= 1, "bad sizes n=%d d=%d", n, d);
+    NTX_CHECK_ARG(view0 && view1 && rows && inv_norm, "NULL buffer");
+    NTX_CHECK_ARG(in_dtype == NTX_F32 || in_dtype == NTX_BF16, "view dtype %d not supported", in_dtype);
+    NTX_CHECK_ARG(rows_dtype == NTX_F32 || rows_dtype == NTX_BF16, "rows dtype %d not supported",
+                  rows_dtype);
+    NTX_CHECK_ARG(ld >= ntx_row_pitch(d, rows_dtype) && ld % (rows_dtype == NTX_BF16 ? 64 : 4) == 0,
+                  "ld=%d too small or misaligned for d=%d", ld, d);
+    return ntx_l2norm_launch(view0, view1, n, d, in_dtype, rows, ld, rows_dtype, inv_norm,
+                             (cudaStream_t)stream);
+}
+
+int ntx_fwd(const void* q, const void* k, int q_rows, int k_rows, int d, int ld, int dtype,
+            const NtxLayout* layout, float temperature, float* rowsum, float* pos_logit,
+            float* row_loss, float* loss_sum, void* workspace, size_t workspace_bytes, void* stream) {
+    NtxDims dm;
+    int rc = make_dims(q_rows, k_rows, d, ld, dtype, layout, temperature, &dm);
+    if (rc) return rc;
+    if ((rc = aligned16(q, "q rows")) || (rc = aligned16(k, "k rows"))) return rc;
+    NTX_CHECK_ARG(rowsum && pos_logit && row_loss && loss_sum, "NULL output buffer");
+    NtxPlan plan;
+    if ((rc = ntx_plan(q_rows, k_rows, d, dtype, 0, &plan))) return rc;
+    if (workspace == nullptr || workspace_bytes < plan.fwd_ws_bytes) {
+        ntx_set_error("ntx_fwd needs %llu bytes of workspace, got %llu",
+                      (unsigned long long)plan.fwd_ws_bytes, (unsigned long long)workspace_bytes);
+        return NTX_E_WORKSPACE;
+    }
+    if ((rc = aligned16(workspace, "workspace"))) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    float* partial = (float*)workspace;
+    if (plan.tensor_cores)
+        rc = ntx_tc_fwd_launch((const __nv_bfloat16*)q, (const __nv_bfloat16*)k, dm, plan, partial, st);
+    else
+        rc = ntx_simt_fwd_launch((const float*)q, (const float*)k, dm, plan, partial, st);
+    if (rc) return rc;
+    return ntx_fwd_finalize_launch(q, dtype, dm, plan, partial, rowsum, pos_logit, row_loss, loss_sum, st);
+}
+
+int ntx_bwd_prep(const float* rowsum, const float* grad_output, int reduction, int q_rows, float* w,
+                 float* coef, void* stream) {
+    NTX_CHECK_ARG(rowsum && grad_output && w && coef, "NULL buffer");
+    NTX_CHECK_ARG(q_rows >= 2 && q_rows % 2 == 0, "q_rows=%d must be even and positive", q_rows);
+    NTX_CHECK_ARG(reduction == NTX_REDUCE_NONE || reduction == NTX_REDUCE_MEAN ||
+                      reduction == NTX_REDUCE_SUM, "bad reduction %d (loss.py:17)", reduction);
+    return ntx_bwd_prep_launch(rowsum, grad_output, reduction, q_rows, w, coef, (cudaStream_t)stream);
+}
+
+int ntx_bwd(const void* q, const void* k, int q_rows, int k_rows, int d, int ld, int dtype,
+            const NtxLayout* layout, float temperature, const float* coef_q, const float* coef_k,
+            const float* w_q, const void* view0, const void* view1, int in_dtype,
+            const float* inv_norm, void* dview0, void* dview1, void* workspace,
+            size_t workspace_bytes, void* stream) {
+    NtxDims dm;
+    int rc = make_dims(q_rows, k_rows, d, ld, dtype, layout, temperature, &dm);
+    if (rc) return rc;
+    if ((rc = aligned16(q, "q rows")) || (rc = aligned16(k, "k rows"))) return rc;
+    NTX_CHECK_ARG(coef_q && coef_k && w_q && view0 && view1 && inv_norm && dview0 && dview1,
+                  "NULL buffer");
+    NTX_CHECK_ARG(in_dtype == NTX_F32 || in_dtype == NTX_BF16, "view dtype %d not supported", in_dtype);
+    NtxPlan plan;
+    if ((rc = ntx_plan(q_rows, k_rows, d, dtype, 0, &plan))) return rc;
+    if (workspace == nullptr || workspace_bytes < plan.bwd_ws_bytes) {
+        ntx_set_error("ntx_bwd needs %llu bytes of workspace, got %llu",
+                      (unsigned long long)plan.bwd_ws_bytes, (unsigned long long)workspace_bytes);
+        return NTX_E_WORKSPACE;
+    }
+    if ((rc = aligned16(workspace, "workspace"))) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    float* partial = (float*)workspace;
+    if (plan.tensor_cores)
+        rc = ntx_tc_bwd_launch((const __nv_bfloat16*)q, (const __nv_bfloat16*)k, dm, plan, coef_q,
+                               coef_k, partial, st);
+    else
+        rc = ntx_simt_bwd_launch((const float*)q, (const float*)k, dm, plan, coef_q, coef_k, partial, st);
+    if (rc) return rc;
+    return ntx_bwd_finalize_launch(dm, plan, partial, w_q, view0, view1, in_dtype, inv_norm, dview0,
+                                   dview1, st);
+}
+
+int ntx_debug_indices(const NtxLayout* layout, int32_t* self_col, int32_t* pos_col, void* stream) {
+    NTX_CHECK_ARG(layout && self_col && pos_col, "NULL argument");
+    int rc = check_layout(layout, 2 * layout->n_local, 2 * layout->n_local * layout->world);
+    if (rc) return rc;
+    return ntx_debug_indices_launch(layout->n_local, layout->rank, self_col, pos_col,
+                                    (cudaStream_t)stream);
+}
+
+}  // extern "C"

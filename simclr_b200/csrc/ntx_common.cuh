@@ -1,0 +1,100 @@
+// Shared host/device helpers of the NT-Xent library: error plumbing, the index
+// arithmetic of the self / positive columns, and the tile partition that both
+// main kernels and their finalize kernels follow.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/ntxent_b200.h"
+
+#define NTX_HD __host__ __device__ __forceinline__
+
+// ---------------------------------------------------------------------------
+// errors (thread-local message; no exception crosses the C boundary)
+// ---------------------------------------------------------------------------
+void ntx_set_error(const char* fmt, ...);
+
+#define NTX_CHECK_ARG(cond, ...)            \
+    do {                                    \
+        if (!(cond)) {                      \
+            ntx_set_error(__VA_ARGS__);     \
+            return NTX_E_ARG;               \
+        }                                   \
+    } while (0)
+
+#define NTX_CUDA(call)                                                              \
+    do {                                                                            \
+        cudaError_t e__ = (call);                                                   \
+        if (e__ != cudaSuccess) {                                                   \
+            ntx_set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__),  \
+                          __FILE__, __LINE__);                                      \
+            return NTX_E_CUDA;                                                      \
+        }                                                                           \
+    } while (0)
+
+// ---------------------------------------------------------------------------
+// index arithmetic -- the bit-exact part of the contract (loss.py:37-38,46-52)
+// ---------------------------------------------------------------------------
+// Row r of this rank (0 <= r < 2*n_local; view0 rows first) among rank-major keys.
+NTX_HD int ntx_row_offset(int n_local, int rank) { return rank * 2 * n_local; }
+NTX_HD int ntx_self_col(int r, int n_local, int rank) { return ntx_row_offset(n_local, rank) + r; }
+NTX_HD int ntx_pos_row(int r, int n_local) { return r < n_local ? r + n_local : r - n_local; }
+NTX_HD int ntx_pos_col(int r, int n_local, int rank) {
+    return ntx_row_offset(n_local, rank) + ntx_pos_row(r, n_local);
+}
+
+// ---------------------------------------------------------------------------
+// tile partition
+// ---------------------------------------------------------------------------
+// Tiles are numbered row-block-major: t = rb * key_tiles + kt.  CTA i owns the
+// contiguous range [i*T/G, (i+1)*T/G).  A row block can be shared by several
+// consecutive CTAs; each writes its partial into slot (i - first owner of the
+// block) and the finalize kernel adds the slots in order (deterministic).
+NTX_HD long long ntx_chunk_begin(long long T, int G, int i) { return (long long)i * T / G; }
+NTX_HD int ntx_tile_owner(long long T, int G, long long t) { return (int)(((t + 1) * G - 1) / T); }
+NTX_HD int ntx_first_owner(long long T, int G, int key_tiles, int rb) {
+    return ntx_tile_owner(T, G, (long long)rb * key_tiles);
+}
+NTX_HD int ntx_num_slots(long long T, int G, int key_tiles, int rb) {
+    return ntx_tile_owner(T, G, (long long)rb * key_tiles + key_tiles - 1) -
+           ntx_tile_owner(T, G, (long long)rb * key_tiles) + 1;
+}
+
+// log2(e) / tau and friends live in one place so every kernel shifts identically:
+// e_rc = exp(s_rc - 1/tau) = exp2(dot_rc * c1 - c1),  c1 = log2(e) / tau.
+#define NTX_LOG2E 1.4426950408889634f
+// exp2 argument range is [-2*c1, 0]; keep it inside fp32 normal range.
+#define NTX_MIN_TEMPERATURE 0.0235f
+
+struct NtxDims {
+    int q_rows, k_rows, d, ld;
+    int n_local, rank;
+    float c1;        // log2e / tau
+    float inv_tau;
+};
+
+// launch helpers implemented per translation unit
+int ntx_l2norm_launch(const void* v0, const void* v1, int n, int d, int in_dtype, void* rows, int ld,
+                      int rows_dtype, float* inv_norm, cudaStream_t st);
+int ntx_simt_fwd_launch(const float* q, const float* k, const NtxDims& dm, const NtxPlan& plan,
+                        float* partial, cudaStream_t st);
+int ntx_simt_bwd_launch(const float* q, const float* k, const NtxDims& dm, const NtxPlan& plan,
+                        const float* coef_q, const float* coef_k, float* partial, cudaStream_t st);
+int ntx_tc_fwd_launch(const __nv_bfloat16* q, const __nv_bfloat16* k, const NtxDims& dm,
+                      const NtxPlan& plan, float* partial, cudaStream_t st);
+int ntx_tc_bwd_launch(const __nv_bfloat16* q, const __nv_bfloat16* k, const NtxDims& dm,
+                      const NtxPlan& plan, const float* coef_q, const float* coef_k, float* partial,
+                      cudaStream_t st);
+int ntx_fwd_finalize_launch(const void* q, int dtype, const NtxDims& dm, const NtxPlan& plan,
+                            const float* partial, float* rowsum, float* pos_logit, float* row_loss,
+                            float* loss_sum, cudaStream_t st);
+int ntx_bwd_prep_launch(const float* rowsum, const float* grad_out, int reduction, int q_rows,
+                        float* w, float* coef, cudaStream_t st);
+int ntx_debug_indices_launch(int n_local, int rank, int32_t* self_col, int32_t* pos_col,
+                             cudaStream_t st);
+int ntx_bwd_finalize_launch(const NtxDims& dm, const NtxPlan& plan, const float* partial,
+                            const float* w_q, const void* view0, const void* view1, int in_dtype,
+                            const float* inv_norm, void* dview0, void* dview1, cudaStream_t st);

@@ -1,0 +1,182 @@
+"""Drop-in ``NT_Xent`` for nzw0301/SimCLR's ``loss.py`` on B200.
+
+Same class name, constructor (``temperature``, ``reduction``, ``device``) and call
+signature as the reference module (loss.py:4-65), so ``main.py:83`` /
+``main.py:114-115`` run unchanged after ``from simclr_b200.loss import NT_Xent``.
+The arithmetic runs in ``libntxent_b200.so`` (hand-written sm_100a kernels) through
+one ``torch.autograd.Function``; nothing of size (2N)^2 is ever allocated and the
+host is never synchronised (the reference syncs twice per call: the CPU-built mask
+at loss.py:38 and ``nonzero`` behind the boolean index at loss.py:46-47).
+
+New, keyword-only and off by default: ``gather=True`` makes the negatives span every
+rank of the process group (rows stay sharded by rank, keys are all-gathered) -- the
+reference computes the loss on each rank's local batch only.
+"""
+from __future__ import annotations
+
+import os
+
+import torch
+import torch.distributed as dist
+
+from . import _cabi
+
+_backend = _cabi.Backend()          # tests may swap in a stand-in with the same methods
+_workspaces: dict = {}
+
+
+def _workspace(device: torch.device, nbytes: int) -> torch.Tensor:
+    """Scratch for the partial row sums / dZ slabs, cached per (device, stream)."""
+    key = (device, torch.cuda.current_stream(device).cuda_stream if device.type == "cuda" else 0)
+    buf = _workspaces.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+        _workspaces[key] = buf
+    return buf
+
+
+def _env_flag(name: str) -> bool:
+    return os.environ.get(name, "0").lower() in ("1", "true", "yes", "on")
+
+
+class NTXentFunction(torch.autograd.Function):
+    """forward: loss of this rank's rows; backward: d loss / d view0, d view1.
+
+    Saves only O(N*D) tensors: the inputs, the normalised rows (keys when gathering),
+    the inverse norms and the per-row sums of exponentials.
+    """
+
+    @staticmethod
+    def forward(ctx, view0, view1, temperature, reduction, rows_dtype, group, world, rank):
+        be = _backend
+        n, d = view0.shape
+        dev = view0.device
+        q_rows = 2 * n
+        ld = be.row_pitch(d, rows_dtype)
+        rows = torch.empty((q_rows, ld), dtype=rows_dtype, device=dev)
+        stats = torch.empty((4, q_rows), dtype=torch.float32, device=dev)   # inv_norm, rowsum, pos, row loss
+        loss_sum = torch.empty(2, dtype=torch.float32, device=dev)
+        inv_norm, rowsum, pos_logit, row_loss = stats[0], stats[1], stats[2], stats[3]
+        be.l2norm(view0, view1, rows, inv_norm)
+        if world > 1:
+            keys = torch.empty((world * q_rows, ld), dtype=rows_dtype, device=dev)
+            dist.all_gather_into_tensor(keys, rows, group=group)          # rank-major key buffer
+            q = keys[rank * q_rows:(rank + 1) * q_rows]
+        else:
+            keys = q = rows
+        layout = (n, world, rank)
+        plan = be.plan(q_rows, keys.shape[0], d, rows_dtype)
+        ws = _workspace(dev, max(plan.fwd_ws_bytes, plan.bwd_ws_bytes))
+        be.fwd(q, keys, d, layout, temperature, rowsum, pos_logit, row_loss, loss_sum, ws)
+
+        ctx.save_for_backward(view0, view1, keys, stats)
+        ctx.meta = (temperature, reduction, group, world, rank, d)
+        if reduction == "none":
+            out = row_loss.view(2, n).clone()                              # loss.py:55-58
+        elif reduction == "sum":
+            out = loss_sum[0]                                              # loss.py:60-63
+        else:
+            out = loss_sum[1]                                              # loss.py:65
+        return out.to(view0.dtype)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        be = _backend
+        view0, view1, keys, stats = ctx.saved_tensors
+        temperature, reduction, group, world, rank, d = ctx.meta
+        n = view0.shape[0]
+        q_rows = 2 * n
+        dev = view0.device
+        inv_norm, rowsum = stats[0], stats[1]
+        g = grad_out.detach().to(torch.float32).contiguous()
+        wc = torch.empty((2, q_rows), dtype=torch.float32, device=dev)
+        w, coef = wc[0], wc[1]
+        be.bwd_prep(rowsum, g, reduction, w, coef)
+        if world > 1:
+            coef_k = torch.empty(world * q_rows, dtype=torch.float32, device=dev)
+            dist.all_gather_into_tensor(coef_k, coef, group=group)        # w / rowsum of every key
+            q = keys[rank * q_rows:(rank + 1) * q_rows]
+        else:
+            coef_k, q = coef, keys
+        dview0 = torch.empty_like(view0)
+        dview1 = torch.empty_like(view1)
+        plan = be.plan(q_rows, keys.shape[0], d, keys.dtype)
+        ws = _workspace(dev, max(plan.fwd_ws_bytes, plan.bwd_ws_bytes))
+        be.bwd(q, keys, d, (n, world, rank), temperature, coef, coef_k, w, view0, view1, inv_norm,
+               dview0, dview1, ws)
+        return dview0, dview1, None, None, None, None, None, None
+
+
+class NT_Xent(torch.nn.Module):
+    """
+    Normalised temperature-scaled cross entropy loss (B200 implementation).
+
+    Constructor and ``forward`` follow the reference module (loss.py:9-31); ``device``
+    is accepted for compatibility (main.py:83 passes an int) -- the kernels run on the
+    device of the inputs, which must be CUDA tensors.
+    """
+
+    def __init__(self, temperature: float = 0.1, reduction: str = "mean",
+                 device: torch.device = torch.device("cpu"), *, gather: bool | None = None,
+                 process_group=None, compute_dtype: torch.dtype | None = None) -> None:
+        """
+        :param temperature: Temperature parameter. The value must be positive.
+        :param reduction: Same to PyTorch's `reduction` in losses.
+        :param device: PyTorch's device instance (kept for signature compatibility).
+        :param gather: keyword-only. True = negatives from every rank of ``process_group``;
+            None = take it from the environment variable NTXENT_GATHER (default off, which
+            is the reference's behaviour: each rank's loss sees only its local batch).
+        :param process_group: keyword-only, group used when gathering (default: world).
+        :param compute_dtype: keyword-only. dtype of the normalised rows: torch.float32 (CUDA-core
+            kernels, 1e-5 parity), torch.bfloat16 (tcgen05 kernels) or None = the input dtype
+            (NTXENT_COMPUTE_DTYPE=bf16 overrides None).
+        """
+        assert temperature > 0.
+        assert reduction in {"none", "mean", "sum"}
+
+        super(NT_Xent, self).__init__()
+        self.temperature = temperature
+        self.reduction = reduction
+        self.device = device
+        self.gather = _env_flag("NTXENT_GATHER") if gather is None else bool(gather)
+        self.process_group = process_group
+        if compute_dtype is None and os.environ.get("NTXENT_COMPUTE_DTYPE", "").lower() in ("bf16", "bfloat16"):
+            compute_dtype = torch.bfloat16
+        if compute_dtype not in (None, torch.float32, torch.bfloat16):
+            raise TypeError(f"compute_dtype must be torch.float32 or torch.bfloat16, got {compute_dtype}")
+        self.compute_dtype = compute_dtype
+
+    def forward(self, view0: torch.Tensor, view1: torch.Tensor) -> torch.Tensor:
+        """
+        :param view0: Feature representation. The shape is (N, D).
+        :param view1: The other feature representations. The shape is same to `view0`'s shape.
+        :return: Loss value. The shape depends on `reduction`: (2, N) or a scaler.
+        """
+        if view0.dim() != 2 or view1.dim() != 2:
+            raise RuntimeError(f"NT_Xent expects two (N, D) tensors, got {tuple(view0.shape)} and "
+                               f"{tuple(view1.shape)}")
+        if view0.shape[0] != view1.shape[0]:
+            raise IndexError(f"view0 has {view0.shape[0]} rows but view1 has {view1.shape[0]}")
+        if view0.shape[1] != view1.shape[1]:
+            raise RuntimeError(f"feature sizes differ: {view0.shape[1]} vs {view1.shape[1]}")
+        if view0.dtype != view1.dtype or view0.device != view1.device:
+            raise RuntimeError("view0 and view1 must share dtype and device")
+        if view0.dtype not in (torch.float32, torch.bfloat16):
+            raise TypeError(f"NT_Xent (B200) supports float32 and bfloat16 inputs, got {view0.dtype}")
+        if view0.device.type != "cuda" and not getattr(_backend, "allows_cpu", False):
+            raise RuntimeError("NT_Xent (B200) has no CPU path: inputs must be CUDA tensors "
+                               f"(got {view0.device})")
+        if view0.shape[0] < 1 or view0.shape[1] < 1:
+            raise RuntimeError("empty batch or feature dimension")
+
+        world, rank, group = 1, 0, None
+        if self.gather and dist.is_available() and dist.is_initialized():
+            group = self.process_group
+            world, rank = dist.get_world_size(group), dist.get_rank(group)
+        rows_dtype = self.compute_dtype or view0.dtype
+        return NTXentFunction.apply(view0.contiguous(), view1.contiguous(), float(self.temperature),
+                                    self.reduction, rows_dtype, group, world, rank)
+
+    def extra_repr(self) -> str:
+        return (f"temperature={self.temperature}, reduction={self.reduction!r}, gather={self.gather}, "
+                f"compute_dtype={self.compute_dtype}")

@@ -1,0 +1,93 @@
+"""The C-ABI library without a GPU: it loads, exports every declared symbol, and its
+integer planning / argument validation behave.  No compute calls here."""
+import ctypes
+import os
+import re
+
+import pytest
+import torch
+
+from simclr_b200 import _cabi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "ntxent_b200.h")
+
+
+def declared_symbols():
+    text = open(HEADER).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(ntx_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_loads_and_exports_every_declared_symbol():
+    lib = _cabi.load()
+    names = declared_symbols()
+    assert len(names) >= 9
+    for name in names:
+        assert hasattr(lib, name), f"{name} declared in include/ntxent_b200.h but not exported"
+    assert set(names) == set(_cabi.EXPORTS)
+    assert lib.ntx_version() == 100
+
+
+def test_row_pitch():
+    be = _cabi.Backend()
+    assert be.row_pitch(128, torch.float32) == 128
+    assert be.row_pitch(20, torch.float32) == 20
+    assert be.row_pitch(21, torch.float32) == 24
+    assert be.row_pitch(128, torch.bfloat16) == 128
+    assert be.row_pitch(96, torch.bfloat16) == 128
+    assert be.row_pitch(1, torch.bfloat16) == 64
+
+
+def owner(T, G, t):
+    return ((t + 1) * G - 1) // T
+
+
+@pytest.mark.parametrize("q_rows,k_rows,d,dtype,sms", [
+    (16384, 16384, 128, torch.bfloat16, 148),     # BASELINE config 4 on one GPU
+    (2048, 16384, 128, torch.bfloat16, 148),      # config 4, one of 8 ranks
+    (8192, 65536, 256, torch.bfloat16, 148),      # config 5, one of 8 ranks
+    (512, 512, 128, torch.float32, 148),          # config 1
+    (1024, 1024, 128, torch.float32, 148),
+    (66, 66, 20, torch.float32, 148),
+    (2, 2, 8, torch.float32, 148),
+    (600, 1200, 100, torch.bfloat16, 7),
+])
+def test_plan_partition_is_exact(q_rows, k_rows, d, dtype, sms):
+    p = _cabi.Backend().plan(q_rows, k_rows, d, dtype, sms)
+    assert p.row_blocks == -(-q_rows // p.tile_rows) and p.key_tiles == -(-k_rows // p.tile_keys)
+    T, G = p.row_blocks * p.key_tiles, p.grid
+    assert 1 <= G <= T
+    begins = [i * T // G for i in range(G + 1)]
+    assert begins[0] == 0 and begins[-1] == T and all(b1 > b0 for b0, b1 in zip(begins, begins[1:]))
+    # the closed-form owner used by the finalize kernels agrees with the ranges
+    step = max(1, T // 5000)
+    for t in list(range(0, T, step)) + [T - 1]:
+        i = owner(T, G, t)
+        assert begins[i] <= t < begins[i + 1]
+    slots = 1
+    for rb in range(p.row_blocks):
+        first, last = owner(T, G, rb * p.key_tiles), owner(T, G, rb * p.key_tiles + p.key_tiles - 1)
+        slots = max(slots, last - first + 1)
+    assert p.max_slots == slots
+    rows_pad = p.row_blocks * p.tile_rows
+    assert p.fwd_ws_bytes == slots * rows_pad * 4
+    assert p.bwd_ws_bytes == slots * rows_pad * p.d_pad * 4
+    assert p.tensor_cores == (1 if dtype == torch.bfloat16 else 0)
+
+
+def test_argument_errors_are_reported_without_a_device():
+    lib = _cabi.load()
+    lay = _cabi.NtxLayout(4, 1, 0)
+    # temperature <= 0 is rejected like the reference's assert (loss.py:16)
+    rc = lib.ntx_fwd(16, 16, 8, 8, 8, 8, 0, ctypes.byref(lay), 0.0, 16, 16, 16, 16, 16, 64, None)
+    assert rc == -1 and b"temperature" in lib.ntx_last_error()
+    # rows must be 2 * n_local
+    rc = lib.ntx_fwd(16, 16, 10, 10, 8, 8, 0, ctypes.byref(lay), 0.5, 16, 16, 16, 16, 16, 64, None)
+    assert rc == -1 and b"q_rows" in lib.ntx_last_error()
+    rc = lib.ntx_bwd_prep(16, 16, 7, 8, 16, 16, None)
+    assert rc == -1 and b"reduction" in lib.ntx_last_error()
+    p = _cabi.NtxPlan()
+    assert lib.ntx_plan(16, 16, 512, 1, 148, ctypes.byref(p)) == -4     # bf16 rows wider than a tile
+    with pytest.raises(_cabi.NtxError):
+        _cabi.Backend().plan(16, 8, 8, torch.float32, 148)               # fewer keys than rows

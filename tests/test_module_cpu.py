@@ -1,0 +1,54 @@
+"""Host-side mirror of the reference module: constructor, state, argument errors."""
+import pytest
+import torch
+
+from simclr_b200 import NT_Xent
+
+
+def test_defaults_match_reference_constructor():
+    m = NT_Xent()
+    assert m.temperature == 0.1 and m.reduction == "mean" and m.device == torch.device("cpu")   # loss.py:9-10
+    assert m.gather is False and m.compute_dtype is None
+    assert list(m.parameters()) == [] and list(m.buffers()) == [] and m.state_dict() == {}
+
+
+def test_constructor_asserts_like_reference():
+    for bad in (0.0, -1.0):
+        with pytest.raises(AssertionError):      # loss.py:16
+            NT_Xent(temperature=bad)
+    with pytest.raises(AssertionError):          # loss.py:17
+        NT_Xent(reduction="avg")
+    NT_Xent(temperature=0.5, device=0)           # main.py:83 passes an int device
+    NT_Xent(0.5, "sum", "cuda:0")
+    with pytest.raises(TypeError):
+        NT_Xent(compute_dtype=torch.float16)
+
+
+def test_new_arguments_are_keyword_only():
+    with pytest.raises(TypeError):
+        NT_Xent(0.5, "mean", torch.device("cpu"), True)
+
+
+def test_env_switches(monkeypatch):
+    monkeypatch.setenv("NTXENT_GATHER", "1")
+    monkeypatch.setenv("NTXENT_COMPUTE_DTYPE", "bf16")
+    m = NT_Xent()
+    assert m.gather is True and m.compute_dtype == torch.bfloat16
+    assert NT_Xent(gather=False).gather is False
+
+
+def test_shape_and_dtype_errors():
+    m = NT_Xent(0.5)
+    with pytest.raises(IndexError):              # reference: mask shape mismatch -> IndexError
+        m(torch.randn(4, 8), torch.randn(5, 8))
+    with pytest.raises(RuntimeError):            # reference: matmul shape mismatch -> RuntimeError
+        m(torch.randn(4, 8), torch.randn(4, 9))
+    with pytest.raises(RuntimeError):
+        m(torch.randn(2, 4, 8), torch.randn(2, 4, 8))
+    with pytest.raises(TypeError):
+        m(torch.randn(4, 8).double(), torch.randn(4, 8).double())
+
+
+def test_no_cpu_fallback():
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        NT_Xent(0.5)(torch.randn(4, 8), torch.randn(4, 8))
