@@ -1,0 +1,326 @@
+#!/usr/bin/env python
+"""NT-Xent forward+backward throughput on B200 (BASELINE.json metric).
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+    python bench.py --impl reference --gpus N ...            # the reference algorithm on host CPU cores
+
+Workload (BASELINE.json configs[3], the one the metric and target are quoted on):
+global batch N = 8192 pairs, D = 128, bf16 embeddings, tau = 0.5, synthetic N(0,1)
+inputs (seed 7).  With N GPUs the global batch is sharded by rows (strong scaling):
+each rank owns N/W pairs and all-gathers the normalised keys.
+
+A "step" = one forward + backward of the loss module (loss value + dview0, dview1).
+value   : pairs/s with inputs resident in HBM (CUDA events per step, L2 flushed between steps).
+e2e     : pairs/s through the public module from PINNED HOST buffers, H2D copies and the
+          D2H read of the loss inside the timed region.
+roofline: dominant kernel (tcgen05 backward), algorithmic flops 12*N^2*D / W per launch.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_GLOBAL, DIM, TAU, SEED = 8192, 128, 0.5, 7
+METRIC, UNIT = "ntxent_fwd_bwd_pairs_per_sec", "pairs/s"
+FALLBACK_TFLOPS = 1590.0          # B200_PROFILING.md fallback when MEASURED_PEAKS.json is absent
+KERNELS_PER_STEP = 7              # l2norm, fwd, fwd_finalize, loss_reduce, bwd_prep, bwd, bwd_finalize
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def workload_config(world):
+    return {"workload": f"NT-Xent fwd+bwd, global batch {N_GLOBAL} pairs ({2 * N_GLOBAL} views), d={DIM}, "
+                        f"tau={TAU}, bf16 (BASELINE configs[3])",
+            "global_batch": N_GLOBAL, "d": DIM, "temperature": TAU,
+            "parallelism": f"rows sharded over {world} rank(s), keys all-gathered" if world > 1 else "single GPU",
+            "l2": "flushed between timed steps (256 MiB write)"}
+
+
+def synthetic(dtype):
+    import torch
+    g = torch.Generator().manual_seed(SEED)
+    v0 = torch.randn(N_GLOBAL, DIM, generator=g, dtype=torch.float32)
+    v1 = torch.randn(N_GLOBAL, DIM, generator=g, dtype=torch.float32)
+    return v0.to(dtype), v1.to(dtype)
+
+
+# ----------------------------------------------------------------------------- clocks
+class ClockSampler:
+    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def __exit__(self, *exc):
+        if self.proc:
+            self.proc.terminate()
+            self.thread.join(timeout=2)
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for name, val in zip(names, r[2:6]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------- CPU arm
+def cpu_steps(n, steps, warmup, threads=None):
+    """fwd+bwd of the reference-form port (oracle) on host cores; returns per-step seconds."""
+    import torch
+    from oracle import ntxent_oracle as orc
+    if threads:
+        torch.set_num_threads(threads)
+    v0, v1 = synthetic(torch.bfloat16)                       # same bf16-rounded values the GPU sees,
+    v0 = v0[:n].float().requires_grad_(True)                 # computed in fp32 like the reference would
+    v1 = v1[:n].float().requires_grad_(True)
+    times = []
+    for i in range(warmup + steps):
+        v0.grad = v1.grad = None
+        t0 = time.perf_counter()
+        orc.ntxent_reference_form(v0, v1, TAU, "mean").backward()
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+    return times
+
+
+def cpu_baseline_block():
+    import torch
+    cores = torch.get_num_threads()
+    t = cpu_steps(N_GLOBAL, steps=2, warmup=1)
+    sec = statistics.median(t)
+    return {"value": N_GLOBAL / sec, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"2 timed + 1 warm-up fwd+bwd steps of oracle.ntxent_reference_form at the full "
+                      f"N={N_GLOBAL}, D={DIM} (fp32 arithmetic on the bf16-rounded inputs), "
+                      f"{sec * 1e3:.0f} ms/step"}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    import torch
+    cores = torch.get_num_threads()
+    probe = cpu_steps(N_GLOBAL, steps=1, warmup=0)[0]       # also serves as a first warm-up
+    budget = 240.0
+    total = args.steps + args.warmup
+    n = N_GLOBAL
+    while n > 512 and probe * (n / N_GLOBAL) ** 2 * total > budget:
+        n //= 2
+    times = cpu_steps(n, args.steps, args.warmup)
+    sec = statistics.mean(times)
+    scale = (N_GLOBAL / n) ** 2                              # work is quadratic in the batch
+    sec_full = sec * scale
+    value = N_GLOBAL / sec_full
+    sample = (f"each step = fwd+bwd of the reference-form port on {n} of {N_GLOBAL} pairs"
+              + ("" if n == N_GLOBAL else f", time scaled by (N/n)^2 = {scale:.0f} to the full batch"))
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec_full * 1e3,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "fp32",
+            "data": "synthetic", "config": workload_config(1),
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ----------------------------------------------------------------------------- GPU arm
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from simclr_b200 import NT_Xent, _cabi
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the CUDA library is the only implementation")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    if N_GLOBAL % world:
+        raise SystemExit(f"global batch {N_GLOBAL} is not divisible by {world} ranks")
+    _cabi.load()
+    n_local = N_GLOBAL // world
+    K, W = args.steps, max(args.warmup, 3)
+
+    v0_all, v1_all = synthetic(torch.bfloat16)
+    sl = slice(rank * n_local, (rank + 1) * n_local)
+    host0, host1 = v0_all[sl].contiguous().pin_memory(), v1_all[sl].contiguous().pin_memory()
+    d0 = host0.to(dev).requires_grad_(True)
+    d1 = host1.to(dev).requires_grad_(True)
+    crit = NT_Xent(temperature=TAU, reduction="mean", device=local_rank, gather=world > 1)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def step(a, b):
+        a.grad = b.grad = None
+        loss = crit(a, b)
+        loss.backward()
+        return loss
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing: per-step CUDA events, L2 flushed between steps
+    for _ in range(W):
+        step(d0, d1)
+    barrier()
+    starts = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
+    stops = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
+    with ClockSampler(local_rank) as clocks:
+        for i in range(K):
+            flush.zero_()
+            starts[i].record()
+            step(d0, d1)
+            stops[i].record()
+        barrier()
+    dev_ms = sum(s.elapsed_time(e) for s, e in zip(starts, stops))
+
+    # ---- end to end: pinned host -> device, module fwd+bwd, loss back to the host
+    def e2e_step():
+        a = host0.to(dev, non_blocking=True).requires_grad_(True)
+        b = host1.to(dev, non_blocking=True).requires_grad_(True)
+        return float(step(a, b))
+    for _ in range(W):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(K):
+        last_loss = e2e_step()
+    barrier()
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+
+    # ---- dominant kernel alone (tcgen05 backward) through the C ABI, CUDA events on its stream
+    be = _cabi.Backend()
+    q_rows = 2 * n_local
+    ld = be.row_pitch(DIM, torch.bfloat16)
+    with torch.no_grad():
+        rows = torch.empty(q_rows, ld, dtype=torch.bfloat16, device=dev)
+        stats = torch.empty(4, q_rows, device=dev)
+        be.l2norm(d0, d1, rows, stats[0])
+        keys = rows
+        if world > 1:
+            keys = torch.empty(world * q_rows, ld, dtype=torch.bfloat16, device=dev)
+            dist.all_gather_into_tensor(keys, rows)
+        q = keys[rank * q_rows:(rank + 1) * q_rows]
+        plan = be.plan(q_rows, keys.shape[0], DIM, torch.bfloat16)
+        ws = torch.empty(max(plan.fwd_ws_bytes, plan.bwd_ws_bytes), dtype=torch.uint8, device=dev)
+        loss_sum = torch.empty(2, device=dev)
+        lay = (n_local, world, rank)
+        wc = torch.empty(2, q_rows, device=dev)
+        g0, g1 = torch.empty_like(d0), torch.empty_like(d1)
+        one = torch.ones((), device=dev)
+        kt = {0: [], 1: []}
+        for i in range(W + K):
+            evs = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+            for e in evs:
+                e.record()
+            flush.zero_()
+            be.profile_next(0, evs[0], evs[1])
+            be.fwd(q, keys, DIM, lay, TAU, stats[1], stats[2], stats[3], loss_sum, ws)
+            be.bwd_prep(stats[1], one, "mean", wc[0], wc[1])
+            coef_k = wc[1]
+            if world > 1:
+                coef_k = torch.empty(world * q_rows, device=dev)
+                dist.all_gather_into_tensor(coef_k, wc[1])
+            be.profile_next(1, evs[2], evs[3])
+            be.bwd(q, keys, DIM, lay, TAU, wc[1], coef_k, wc[0], d0, d1, stats[0], g0, g1, ws)
+            torch.cuda.synchronize()
+            if i >= W:
+                kt[0].append(evs[0].elapsed_time(evs[1]))
+                kt[1].append(evs[2].elapsed_time(evs[3]))
+    fwd_ms, bwd_ms = statistics.mean(kt[0]), statistics.mean(kt[1])
+
+    if world > 1:
+        t = torch.tensor([dev_ms, e2e_ms, fwd_ms, bwd_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dev_ms, e2e_ms, fwd_ms, bwd_ms = t.tolist()
+
+    if rank == 0:
+        peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        if os.path.exists(peaks_path):
+            peak, peak_src = json.load(open(peaks_path))["bf16_tflops"], "measured (MEASURED_PEAKS.json bf16_tflops, burst)"
+        else:
+            peak, peak_src = FALLBACK_TFLOPS, "fallback (B200_PROFILING.md)"
+        bwd_flops = 12.0 * N_GLOBAL * N_GLOBAL * DIM / world      # algorithmic, SURVEY.md 8a row a8
+        fwd_flops = 6.0 * N_GLOBAL * N_GLOBAL * DIM / world
+        achieved = bwd_flops / (bwd_ms * 1e-3) / 1e12
+        ms_per_step = dev_ms / K
+        line = {
+            "metric": METRIC, "value": N_GLOBAL / (ms_per_step * 1e-3), "unit": UNIT, "n_gpus": world,
+            "steps": K, "warmup": W, "ms_per_step": ms_per_step, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": workload_config(world),
+            "e2e": {"value": N_GLOBAL / (e2e_ms / K * 1e-3), "unit": UNIT,
+                    "h2d_bytes_per_step": 2 * N_GLOBAL * DIM * 2, "d2h_bytes_per_step": 2 * world,
+                    "ms_per_step": e2e_ms / K, "loss": last_loss},
+            "gpu_launches": KERNELS_PER_STEP * K,
+            "roofline": {"bound": "tensor", "kernel": "tc_bwd_kernel<2>", "achieved": achieved, "peak": peak,
+                         "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
+                         "peak_source": peak_src, "algorithmic_flops_per_launch": bwd_flops,
+                         "kernel_ms": bwd_ms,
+                         "fwd_kernel": {"kernel": "tc_fwd_kernel<2>", "kernel_ms": fwd_ms,
+                                        "achieved": fwd_flops / (fwd_ms * 1e-3) / 1e12},
+                         "whole_step_frac": 18.0 * N_GLOBAL * N_GLOBAL * DIM / world / (ms_per_step * 1e-3) / 1e12 / peak},
+            "clocks": clocks.summary(),
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline_block()
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    a = parse()
+    sys.exit(run_reference(a) if a.impl == "reference" else run_ours(a))

@@ -136,6 +136,13 @@ int ntx_bwd(const void* q_rows_ptr, const void* k_rows_ptr, int q_rows, int k_ro
  * the same helper the kernels use (bit-exact contract on loss.py:37-38 indexing). */
 int ntx_debug_indices(const NtxLayout* layout, int32_t* self_col, int32_t* pos_col, void* stream);
 
+/* Measurement hook (bench.py): the next ntx_fwd (which = 0) or ntx_bwd (which = 1) call made
+ * by this host thread records ev_start just before and ev_stop just after its MAIN kernel
+ * (not the finalize kernels) on the call's stream, then disarms itself.  ev_* are
+ * cudaEvent_t handles owned by the caller.  No counterpart in the reference, which has no
+ * profiling hooks. */
+int ntx_profile_next(int which, void* ev_start, void* ev_stop);
+
 #ifdef __cplusplus
 }
 #endif

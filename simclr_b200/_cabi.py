@@ -20,7 +20,7 @@ DTYPES = {torch.float32: NTX_F32, torch.bfloat16: NTX_BF16}
 
 EXPORTS = (
     "ntx_version", "ntx_last_error", "ntx_row_pitch", "ntx_plan", "ntx_l2norm", "ntx_fwd",
-    "ntx_bwd_prep", "ntx_bwd", "ntx_debug_indices",
+    "ntx_bwd_prep", "ntx_bwd", "ntx_debug_indices", "ntx_profile_next",
 )
 
 
@@ -59,6 +59,7 @@ def _declare(lib):
     lib.ntx_bwd.argtypes = [vp, vp, i, i, i, i, i, ctypes.POINTER(NtxLayout), f, vp, vp, vp, vp, vp, i,
                             vp, vp, vp, vp, sz, vp]
     lib.ntx_debug_indices.argtypes = [ctypes.POINTER(NtxLayout), vp, vp, vp]
+    lib.ntx_profile_next.argtypes = [i, vp, vp]
     for name in EXPORTS:
         if name != "ntx_last_error":
             getattr(lib, name).restype = i
@@ -130,6 +131,11 @@ class Backend:
                               DTYPES[view0.dtype], inv_norm.data_ptr(), dview0.data_ptr(),
                               dview1.data_ptr(), workspace.data_ptr(),
                               workspace.numel() * workspace.element_size(), _stream(q)))
+
+    def profile_next(self, which: int, ev_start: "torch.cuda.Event", ev_stop: "torch.cuda.Event"):
+        """Arm the measurement hook: the next fwd (0) / bwd (1) call on this thread brackets its
+        main kernel with the two events (which must already exist: record them once first)."""
+        _check(load().ntx_profile_next(which, ev_start.cuda_event, ev_stop.cuda_event))
 
     def debug_indices(self, layout, self_col, pos_col):
         lay = NtxLayout(*layout)

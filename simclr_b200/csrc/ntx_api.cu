@@ -17,6 +17,22 @@ void ntx_set_error(const char* fmt, ...) {
 
 namespace {
 
+// armed by ntx_profile_next(); consumed by the next matching call on this thread
+thread_local cudaEvent_t g_prof_start[2] = {nullptr, nullptr};
+thread_local cudaEvent_t g_prof_stop[2] = {nullptr, nullptr};
+
+struct ProfScope {
+    int which;
+    cudaStream_t st;
+    ProfScope(int w, cudaStream_t s) : which(w), st(s) {
+        if (g_prof_start[which]) cudaEventRecord(g_prof_start[which], st);
+    }
+    ~ProfScope() {
+        if (g_prof_stop[which]) cudaEventRecord(g_prof_stop[which], st);
+        g_prof_start[which] = g_prof_stop[which] = nullptr;
+    }
+};
+
 constexpr int kTcMaxD = 256;   // widest padded feature dim the tcgen05 kernels hold in smem
 
 int cached_sm_count(int* out) {
@@ -156,10 +172,13 @@ int ntx_fwd(const void* q, const void* k, int q_rows, int k_rows, int d, int ld,
     if ((rc = aligned16(workspace, "workspace"))) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     float* partial = (float*)workspace;
-    if (plan.tensor_cores)
-        rc = ntx_tc_fwd_launch((const __nv_bfloat16*)q, (const __nv_bfloat16*)k, dm, plan, partial, st);
-    else
-        rc = ntx_simt_fwd_launch((const float*)q, (const float*)k, dm, plan, partial, st);
+    {
+        ProfScope prof(0, st);
+        if (plan.tensor_cores)
+            rc = ntx_tc_fwd_launch((const __nv_bfloat16*)q, (const __nv_bfloat16*)k, dm, plan, partial, st);
+        else
+            rc = ntx_simt_fwd_launch((const float*)q, (const float*)k, dm, plan, partial, st);
+    }
     if (rc) return rc;
     return ntx_fwd_finalize_launch(q, dtype, dm, plan, partial, rowsum, pos_logit, row_loss, loss_sum, st);
 }
@@ -195,14 +214,24 @@ int ntx_bwd(const void* q, const void* k, int q_rows, int k_rows, int d, int ld,
     if ((rc = aligned16(workspace, "workspace"))) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     float* partial = (float*)workspace;
-    if (plan.tensor_cores)
-        rc = ntx_tc_bwd_launch((const __nv_bfloat16*)q, (const __nv_bfloat16*)k, dm, plan, coef_q,
-                               coef_k, partial, st);
-    else
-        rc = ntx_simt_bwd_launch((const float*)q, (const float*)k, dm, plan, coef_q, coef_k, partial, st);
+    {
+        ProfScope prof(1, st);
+        if (plan.tensor_cores)
+            rc = ntx_tc_bwd_launch((const __nv_bfloat16*)q, (const __nv_bfloat16*)k, dm, plan, coef_q,
+                                   coef_k, partial, st);
+        else
+            rc = ntx_simt_bwd_launch((const float*)q, (const float*)k, dm, plan, coef_q, coef_k, partial, st);
+    }
     if (rc) return rc;
     return ntx_bwd_finalize_launch(dm, plan, partial, w_q, view0, view1, in_dtype, inv_norm, dview0,
                                    dview1, st);
+}
+
+int ntx_profile_next(int which, void* ev_start, void* ev_stop) {
+    NTX_CHECK_ARG(which == 0 || which == 1, "which must be 0 (forward) or 1 (backward)");
+    g_prof_start[which] = (cudaEvent_t)ev_start;
+    g_prof_stop[which] = (cudaEvent_t)ev_stop;
+    return NTX_OK;
 }
 
 int ntx_debug_indices(const NtxLayout* layout, int32_t* self_col, int32_t* pos_col, void* stream) {

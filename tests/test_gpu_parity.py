@@ -1,0 +1,261 @@
+"""Parity of the CUDA path (through the C ABI and the NT_Xent module) with the oracle.
+
+Tolerances (BASELINE.json north_star): indices bit-exact; loss and gradients within
+1e-5 relative for fp32 rows, 1e-2 relative for bf16 rows (against the reference run in
+fp32 on the same bf16-rounded inputs).  Relative = max |got - want| / max |want|.
+"""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import grad_err, grad_floor, rel_err as _rel_err
+from oracle import ntxent_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+FP32_TOL = 1e-5
+BF16_TOL = 1e-2
+
+
+def rel_err(got, want, floor=1.0):
+    """Loss values are O(log 2N) >= 1 except the N=1 case whose exact value is 0: compare
+    relative to max(|want|, 1) so that case is an absolute 1e-5 check."""
+    return _rel_err(got, want, floor)
+
+
+@pytest.fixture(scope="module")
+def dev():
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    from simclr_b200 import _cabi
+    _cabi.load()                      # the CUDA library must be the thing that runs
+    return torch.device("cuda:0")
+
+
+def run_module(case, dev, compute_dtype=None, in_dtype=torch.float32):
+    from simclr_b200 import NT_Xent
+    a = torch.tensor(case.view0, device=dev, dtype=in_dtype, requires_grad=True)
+    b = torch.tensor(case.view1, device=dev, dtype=in_dtype, requires_grad=True)
+    loss = NT_Xent(temperature=case.tau, reduction=case.reduction, device=0, compute_dtype=compute_dtype)(a, b)
+    if case.reduction == "none":
+        loss.backward(torch.tensor(case.grad_out, device=dev, dtype=loss.dtype))
+    else:
+        loss.backward()
+    return loss.detach().float().cpu().numpy(), a.grad.float().cpu().numpy(), b.grad.float().cpu().numpy()
+
+
+def test_golden_fp32(golden_case, dev):
+    c = golden_case
+    loss, g0, g1 = run_module(c, dev)
+    assert loss.shape == c.loss.shape
+    assert rel_err(loss, c.loss) < FP32_TOL
+    assert grad_err(g0, c.dview0, c) < FP32_TOL
+    assert grad_err(g1, c.dview1, c) < FP32_TOL
+
+
+def test_golden_bf16_rows(golden_case, dev):
+    """fp32 inputs, bf16 normalised rows on the tcgen05 kernels."""
+    c = golden_case
+    loss, g0, g1 = run_module(c, dev, compute_dtype=torch.bfloat16)
+    assert rel_err(loss, c.loss) < BF16_TOL
+    assert grad_err(g0, c.dview0, c) < BF16_TOL
+    assert grad_err(g1, c.dview1, c) < BF16_TOL
+
+
+def test_golden_bf16_inputs(dev):
+    from conftest import GOLDEN
+    for c in (g for g in GOLDEN if g.bf16):       # inputs already bf16-representable
+        loss, g0, g1 = run_module(c, dev, in_dtype=torch.bfloat16)
+        assert rel_err(loss, c.loss) < BF16_TOL
+        assert grad_err(g0, c.dview0, c) < BF16_TOL
+        assert grad_err(g1, c.dview1, c) < BF16_TOL
+
+
+@pytest.mark.parametrize("n_local,world,rank", [(5, 1, 0), (128, 1, 0), (37, 4, 2), (4096, 8, 7)])
+def test_indices_bit_exact(n_local, world, rank, dev):
+    from simclr_b200 import _cabi
+    s = torch.empty(2 * n_local, dtype=torch.int32, device=dev)
+    p = torch.empty(2 * n_local, dtype=torch.int32, device=dev)
+    _cabi.Backend().debug_indices((n_local, world, rank), s, p)
+    want_s, want_p = orc.index_maps(n_local, world, rank)
+    assert np.array_equal(s.cpu().numpy(), want_s)
+    assert np.array_equal(p.cpu().numpy(), want_p)
+
+
+@pytest.mark.parametrize("in_dtype,rows_dtype", [(torch.float32, torch.float32), (torch.float32, torch.bfloat16),
+                                                 (torch.bfloat16, torch.bfloat16), (torch.bfloat16, torch.float32)])
+@pytest.mark.parametrize("n,d", [(7, 5), (64, 128), (33, 257)])
+def test_l2norm_matches_f_normalize(in_dtype, rows_dtype, n, d, dev):
+    from simclr_b200 import _cabi
+    be = _cabi.Backend()
+    g = torch.Generator().manual_seed(n + d)
+    a = (torch.randn(n, d, generator=g) * 3).to(in_dtype).to(dev)
+    b = torch.randn(n, d, generator=g).to(in_dtype).to(dev)
+    b[0].zero_()                                              # eps clamp row
+    ld = be.row_pitch(d, rows_dtype)
+    rows = torch.full((2 * n, ld), 7.0, dtype=rows_dtype, device=dev)
+    inv = torch.empty(2 * n, device=dev)
+    be.l2norm(a, b, rows, inv)
+    want = torch.nn.functional.normalize(torch.cat([a, b]).float(), p=2, dim=1)       # loss.py:33-34
+    tol = 1e-6 if rows_dtype == torch.float32 else 4e-3
+    assert (rows[:, :d].float() - want).abs().max().item() <= tol
+    assert rows[:, d:].float().abs().max().item() == 0.0 if ld > d else True
+    norm = torch.cat([a, b]).float().norm(dim=1).clamp_min(1e-12)
+    assert torch.allclose(inv, 1.0 / norm, rtol=1e-6)
+
+
+@pytest.mark.parametrize("n,d,tau,dtype", [
+    (2, 8, 0.5, torch.float32), (100, 33, 0.05, torch.float32), (513, 200, 1.0, torch.float32),
+    (640, 512, 0.3, torch.float32), (2, 8, 0.5, torch.bfloat16), (100, 33, 0.07, torch.bfloat16),
+    (513, 200, 1.0, torch.bfloat16), (1000, 256, 0.2, torch.bfloat16), (2048, 128, 0.5, torch.bfloat16),
+])
+@pytest.mark.parametrize("reduction", ["mean", "none"])
+def test_random_sizes_against_fp64_oracle(n, d, tau, dtype, reduction, dev):
+    from simclr_b200 import NT_Xent
+    g = torch.Generator().manual_seed(n * 31 + d)
+    a = torch.randn(n, d, generator=g).to(dtype)
+    b = (torch.randn(n, d, generator=g) + 0.5 * a.float()).to(dtype)        # correlated positives
+    gout = (torch.rand(2, n, generator=g) + 0.25) if reduction == "none" else None
+    w = orc.weights_for(reduction, n, None if gout is None else gout.numpy())
+    ref = orc.ntxent_rows_fp64(a.float().numpy(), b.float().numpy(), tau, weights=w)
+    ta = a.to(dev).requires_grad_(True)
+    tb = b.to(dev).requires_grad_(True)
+    loss = NT_Xent(tau, reduction)(ta, tb)
+    loss.backward(None if gout is None else gout.to(dev).to(loss.dtype))
+    tol = FP32_TOL if dtype == torch.float32 else BF16_TOL
+    assert rel_err(loss.float().cpu().numpy(), orc.reduce_rows(ref["loss"], reduction)) < tol
+    scale = max(np.abs(ref["dview0"]).max(), np.abs(ref["dview1"]).max())
+    assert np.abs(ta.grad.float().cpu().numpy() - ref["dview0"]).max() / scale < tol
+    assert np.abs(tb.grad.float().cpu().numpy() - ref["dview1"]).max() / scale < tol
+
+
+def test_known_answers_on_device(dev):
+    from simclr_b200 import NT_Xent
+    for dtype in (torch.float32, torch.bfloat16):
+        for fill in (1.0, 0.0):                                   # identical rows / eps clamp
+            v = torch.full((4, 8), fill, device=dev, dtype=dtype)
+            rows = NT_Xent(0.1, "none")(v, v).float()
+            assert rows.shape == (2, 4)
+            assert torch.allclose(rows, torch.full_like(rows, math.log(7.0)), atol=2e-2 if dtype == torch.bfloat16 else 1e-5)
+        one = NT_Xent(0.1)(torch.randn(1, 8, device=dev, dtype=dtype), torch.randn(1, 8, device=dev, dtype=dtype))
+        assert abs(float(one)) < 1e-5                              # N = 1: a single logit
+    a, b = torch.randn(16, 12, device=dev), torch.randn(16, 12, device=dev)
+    none, mean, total = (NT_Xent(0.5, r)(a, b) for r in ("none", "mean", "sum"))
+    assert torch.allclose(mean, total / 32, rtol=1e-6) and torch.allclose(none.sum(), total, rtol=1e-5)
+
+
+def test_module_behaviour_on_device(dev):
+    from simclr_b200 import NT_Xent
+    a = torch.randn(8, 8, device=dev)
+    nc = torch.randn(8, 16, device=dev)[:, ::2]                    # non-contiguous input is accepted
+    out = NT_Xent(0.5)(a, nc)
+    want = orc.ntxent_rows_fp64(a.cpu().numpy(), nc.cpu().numpy(), 0.5)["loss"].mean()
+    assert abs(float(out) - want) < 1e-5 * abs(want)
+    assert NT_Xent(0.5)(a.bfloat16(), a.bfloat16()).dtype == torch.bfloat16   # dtype follows the input
+    from simclr_b200 import _cabi
+    with pytest.raises(_cabi.NtxError):
+        NT_Xent(0.001)(a, a)                                       # below the fixed-shift range
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, FP32_TOL), (torch.bfloat16, BF16_TOL)])
+@pytest.mark.parametrize("world", [2, 4])
+def test_sharded_layout_one_gpu(world, dtype, tol, dev):
+    """Every rank's kernels run one after another on one GPU against the rank-major key
+    buffer; result = the reference on the concatenated batch."""
+    from conftest import GOLDEN
+    from simclr_b200 import _cabi
+    be = _cabi.Backend()
+    c = next(g for g in GOLDEN if g.name == f"shard_w{world}")
+    nl, d = c.n // world, c.d
+    q_rows = 2 * nl
+    ld = be.row_pitch(d, dtype)
+    views, rows, invs = [], [], []
+    for k in range(world):
+        a = torch.tensor(c.view0[k * nl:(k + 1) * nl], device=dev)
+        b = torch.tensor(c.view1[k * nl:(k + 1) * nl], device=dev)
+        r = torch.empty(q_rows, ld, dtype=dtype, device=dev)
+        inv = torch.empty(q_rows, device=dev)
+        be.l2norm(a, b, r, inv)
+        views.append((a, b)); rows.append(r); invs.append(inv)
+    keys = torch.cat(rows)                                         # what all_gather_into_tensor builds
+    plan = be.plan(q_rows, keys.shape[0], d, dtype)
+    ws = torch.empty(max(plan.fwd_ws_bytes, plan.bwd_ws_bytes, 16), dtype=torch.uint8, device=dev)
+    stats, coefs, ws_w = [], [], []
+    for k in range(world):
+        st = torch.empty(3, q_rows, device=dev)
+        ls = torch.empty(2, device=dev)
+        be.fwd(keys[k * q_rows:(k + 1) * q_rows], keys, d, (nl, world, k), c.tau, st[0], st[1], st[2], ls, ws)
+        wc = torch.empty(2, q_rows, device=dev)
+        be.bwd_prep(st[0], torch.ones((), device=dev), "mean", wc[0], wc[1])
+        stats.append((st, ls)); coefs.append(wc[1]); ws_w.append(wc[0])
+    # mean over ranks of the per-rank mean == the reference's global mean
+    assert rel_err(np.mean([float(ls[1]) for _, ls in stats]), float(c.loss)) < tol
+    coef_k = torch.cat(coefs)
+    for k in range(world):
+        a, b = views[k]
+        d0, d1 = torch.empty_like(a), torch.empty_like(b)
+        be.bwd(keys[k * q_rows:(k + 1) * q_rows], keys, d, (nl, world, k), c.tau, coefs[k], coef_k, ws_w[k],
+               a, b, invs[k], d0, d1, ws)
+        # each rank's loss is a mean over its own rows: grads are W x the global-mean grads; DDP divides by W
+        sl = slice(k * nl, (k + 1) * nl)
+        floor = grad_floor(c)
+        assert rel_err(d0.cpu().numpy() / world, c.dview0[sl], floor) < tol
+        assert rel_err(d1.cpu().numpy() / world, c.dview1[sl], floor) < tol
+
+
+def test_full_size_config4_properties(dev):
+    """BASELINE config 4 (N=8192, D=128, bf16): size-independent properties + oracle on all rows."""
+    from simclr_b200 import NT_Xent
+    n, d, tau = 8192, 128, 0.5
+    g = torch.Generator().manual_seed(7)
+    a = torch.randn(n, d, generator=g).bfloat16()
+    b = torch.randn(n, d, generator=g).bfloat16()
+    ta, tb = a.to(dev).requires_grad_(True), b.to(dev).requires_grad_(True)
+    none = NT_Xent(tau, "none")(ta, tb).float()
+    mean = NT_Xent(tau, "mean")(ta, tb).float()
+    total = NT_Xent(tau, "sum")(ta, tb).float()
+    assert none.shape == (2, n)
+    assert abs(float(none.sum()) - float(total)) < 4e-3 * float(total)      # outputs are bf16-rounded
+    assert abs(float(mean) - float(total) / (2 * n)) < 8e-3 * float(mean)
+    ref = orc.ntxent_rows_fp64(a.float().numpy(), b.float().numpy(), tau, weights=orc.weights_for("mean", n))
+    assert rel_err(none.cpu().numpy(), ref["loss"]) < BF16_TOL
+    loss = NT_Xent(tau, "mean")(ta, tb)
+    loss.backward()
+    scale = max(np.abs(ref["dview0"]).max(), np.abs(ref["dview1"]).max())
+    assert np.abs(ta.grad.float().cpu().numpy() - ref["dview0"]).max() / scale < BF16_TOL
+    assert np.abs(tb.grad.float().cpu().numpy() - ref["dview1"]).max() / scale < BF16_TOL
+    # determinism: the same inputs give bit-identical outputs (fixed-order slot sums)
+    ta2, tb2 = a.to(dev).requires_grad_(True), b.to(dev).requires_grad_(True)
+    loss2 = NT_Xent(tau, "mean")(ta2, tb2)
+    loss2.backward()
+    assert torch.equal(loss, loss2) and torch.equal(ta.grad, ta2.grad) and torch.equal(tb.grad, tb2.grad)
+
+
+def test_training_step_call_pattern(dev):
+    """main.py:104-122 call pattern: model(view0), model(view1), loss, backward, SGD step --
+    with the reference-form oracle on the same weights as the checker."""
+    from simclr_b200 import NT_Xent
+    torch.manual_seed(7)                                                     # conf/config.yaml:9
+    def make():
+        return torch.nn.Sequential(
+            torch.nn.Conv2d(3, 16, 3, padding=1), torch.nn.ReLU(), torch.nn.AdaptiveAvgPool2d(4), torch.nn.Flatten(),
+            torch.nn.Linear(256, 256), torch.nn.BatchNorm1d(256), torch.nn.ReLU(), torch.nn.Linear(256, 128, bias=False))
+    ours, theirs = make().to(dev), make().to(dev)
+    theirs.load_state_dict(ours.state_dict())
+    crit = NT_Xent(temperature=0.5, device=0)                                # main.py:83
+    opt_a = torch.optim.SGD(ours.parameters(), lr=0.1, momentum=0.9)
+    opt_b = torch.optim.SGD(theirs.parameters(), lr=0.1, momentum=0.9)
+    for step in range(3):
+        v0, v1 = torch.rand(512, 3, 32, 32, device=dev), torch.rand(512, 3, 32, 32, device=dev)
+        opt_a.zero_grad(); opt_b.zero_grad()
+        la = crit(ours(v0), ours(v1))                                        # main.py:112-114
+        la.backward()                                                        # main.py:115
+        lb = orc.ntxent_reference_form(theirs(v0), theirs(v1), 0.5, "mean")
+        lb.backward()
+        assert abs(float(la) - float(lb)) < 1e-5 * abs(float(lb))
+        ga = torch.cat([p.grad.flatten() for p in ours.parameters()])
+        gb = torch.cat([p.grad.flatten() for p in theirs.parameters()])
+        assert (ga - gb).abs().max() < 1e-4 * gb.abs().max()
+        opt_a.step(); opt_b.step()

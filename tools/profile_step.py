@@ -1,0 +1,38 @@
+"""A few fwd+bwd steps of the benchmark workload straight through the C ABI (for ncu).
+
+    python tools/profile_step.py [n_pairs] [d] [steps]
+"""
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from simclr_b200 import _cabi  # noqa: E402
+
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 8192
+d = int(sys.argv[2]) if len(sys.argv) > 2 else 128
+steps = int(sys.argv[3]) if len(sys.argv) > 3 else 3
+dev = torch.device("cuda:0")
+be = _cabi.Backend()
+g = torch.Generator().manual_seed(7)
+v0 = torch.randn(n, d, generator=g).bfloat16().to(dev)
+v1 = torch.randn(n, d, generator=g).bfloat16().to(dev)
+q_rows = 2 * n
+ld = be.row_pitch(d, torch.bfloat16)
+rows = torch.empty(q_rows, ld, dtype=torch.bfloat16, device=dev)
+stats = torch.empty(4, q_rows, device=dev)
+loss_sum = torch.empty(2, device=dev)
+plan = be.plan(q_rows, q_rows, d, torch.bfloat16)
+ws = torch.empty(max(plan.fwd_ws_bytes, plan.bwd_ws_bytes), dtype=torch.uint8, device=dev)
+wc = torch.empty(2, q_rows, device=dev)
+g0, g1 = torch.empty_like(v0), torch.empty_like(v1)
+one = torch.ones((), device=dev)
+for _ in range(steps):
+    be.l2norm(v0, v1, rows, stats[0])
+    be.fwd(rows, rows, d, (n, 1, 0), 0.5, stats[1], stats[2], stats[3], loss_sum, ws)
+    be.bwd_prep(stats[1], one, "mean", wc[0], wc[1])
+    be.bwd(rows, rows, d, (n, 1, 0), 0.5, wc[1], wc[1], wc[0], v0, v1, stats[0], g0, g1, ws)
+torch.cuda.synchronize()
+print("loss", float(loss_sum[1]))
