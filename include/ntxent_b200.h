@@ -46,11 +46,6 @@ extern "C" {
 #define NTX_E_CUDA (-3)      /* a CUDA runtime / driver call failed */
 #define NTX_E_UNSUPPORTED (-4)
 
-/* reduction of loss.py:54-65 */
-#define NTX_REDUCE_NONE 0
-#define NTX_REDUCE_MEAN 1
-#define NTX_REDUCE_SUM 2
-
 /* Where this rank's rows sit among the keys.
  * n_local : pairs held by this rank (N of loss.py:36 when world == 1)
  * world   : number of ranks whose rows form the keys (1 = the reference's local loss)
@@ -112,25 +107,22 @@ int ntx_fwd(const void* q_rows_ptr, const void* k_rows_ptr, int q_rows, int k_ro
             float* pos_logit, float* row_loss, float* loss_sum, void* workspace,
             size_t workspace_bytes, void* stream);
 
-/* Row weights for backward from the upstream gradient: w_r = grad_output * scale
- * (reduce mean/sum: grad_output is one float on the device, scale = 1/(2*n_local) or 1)
- * or w_r = grad_output[r] (reduce none, (2, n_local) floats).  Writes w[r] and
- * coef[r] = w_r / rowsum[r].  This is the d(cross_entropy)/d(logits) scaling that
- * autograd derives from loss.py:56-65. */
-int ntx_bwd_prep(const float* rowsum, const float* grad_output, int reduction, int q_rows,
-                 float* w, float* coef, void* stream);
-
-/* Backward: gradient of sum_r w_r * row_loss_r with respect to view0/view1 for this
- * rank's rows, including the terms in which its rows act as keys of other rows
- * (coef_k carries w/rowsum of every key, all-gathered by the caller when world > 1).
- * Replaces the autograd graph of loss.py:33-65 (softmax - onehot, un-concatenate,
- * index_put through the mask, six GEMMs, normalisation Jacobian).
+/* Backward: gradient of  sum_r w_r * row_loss_r  with respect to view0/view1 for this rank's
+ * rows, including the terms in which its rows act as keys of other rows.
+ *   w_r = w_q[r * w_stride] * w_scale for this rank's rows, w_c = w_k[c * w_stride] * w_scale for keys:
+ *     reduction mean / sum: w_stride = 0, w_q = w_k = the upstream gradient (one device float),
+ *                           w_scale = 1 / q_rows (mean, loss.py:65) or 1 (sum);
+ *     reduction none      : w_stride = 1, w_q = upstream gradient laid out (2, n_local), w_scale = 1.
+ *   rowsum_q / rowsum_k: the forward's rowsum of this rank's rows / of every key (with world > 1 the
+ *   caller all-gathers rowsum and, for w_stride = 1, the weights).
+ * Replaces the autograd graph of loss.py:33-65 (softmax - onehot, un-concatenate, index_put through
+ * the mask, six GEMMs, normalisation Jacobian).
  * dview0/dview1 are (n_local x d) in `in_dtype`, like view0/view1. */
 int ntx_bwd(const void* q_rows_ptr, const void* k_rows_ptr, int q_rows, int k_rows, int d, int ld,
-            int dtype, const NtxLayout* layout, float temperature, const float* coef_q,
-            const float* coef_k, const float* w_q, const void* view0, const void* view1,
-            int in_dtype, const float* inv_norm, void* dview0, void* dview1, void* workspace,
-            size_t workspace_bytes, void* stream);
+            int dtype, const NtxLayout* layout, float temperature, const float* rowsum_q,
+            const float* rowsum_k, const float* w_q, const float* w_k, int w_stride, float w_scale,
+            const void* view0, const void* view1, int in_dtype, const float* inv_norm, void* dview0,
+            void* dview1, void* workspace, size_t workspace_bytes, void* stream);
 
 /* Test entry: the self and positive column of every row, computed on the device by
  * the same helper the kernels use (bit-exact contract on loss.py:37-38 indexing). */

@@ -12,15 +12,14 @@ import threading
 import torch
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG, "libntxent_b200.so")
+LIB_PATH = os.environ.get("NTXENT_B200_LIB") or os.path.join(_PKG, "libntxent_b200.so")
 
 NTX_F32, NTX_BF16 = 0, 1
-REDUCTIONS = {"none": 0, "mean": 1, "sum": 2}
 DTYPES = {torch.float32: NTX_F32, torch.bfloat16: NTX_BF16}
 
 EXPORTS = (
     "ntx_version", "ntx_last_error", "ntx_row_pitch", "ntx_plan", "ntx_l2norm", "ntx_fwd",
-    "ntx_bwd_prep", "ntx_bwd", "ntx_debug_indices", "ntx_profile_next",
+    "ntx_bwd", "ntx_debug_indices", "ntx_profile_next",
 )
 
 
@@ -55,9 +54,8 @@ def _declare(lib):
     lib.ntx_plan.argtypes = [i, i, i, i, i, ctypes.POINTER(NtxPlan)]
     lib.ntx_l2norm.argtypes = [vp, vp, i, i, i, vp, i, i, vp, vp]
     lib.ntx_fwd.argtypes = [vp, vp, i, i, i, i, i, ctypes.POINTER(NtxLayout), f, vp, vp, vp, vp, vp, sz, vp]
-    lib.ntx_bwd_prep.argtypes = [vp, vp, i, i, vp, vp, vp]
-    lib.ntx_bwd.argtypes = [vp, vp, i, i, i, i, i, ctypes.POINTER(NtxLayout), f, vp, vp, vp, vp, vp, i,
-                            vp, vp, vp, vp, sz, vp]
+    lib.ntx_bwd.argtypes = [vp, vp, i, i, i, i, i, ctypes.POINTER(NtxLayout), f, vp, vp, vp, vp, i, f,
+                            vp, vp, i, vp, vp, vp, vp, sz, vp]
     lib.ntx_debug_indices.argtypes = [ctypes.POINTER(NtxLayout), vp, vp, vp]
     lib.ntx_profile_next.argtypes = [i, vp, vp]
     for name in EXPORTS:
@@ -118,19 +116,16 @@ class Backend:
                               workspace.data_ptr(), workspace.numel() * workspace.element_size(),
                               _stream(q)))
 
-    def bwd_prep(self, rowsum, grad_output, reduction, w, coef):
-        _check(load().ntx_bwd_prep(rowsum.data_ptr(), grad_output.data_ptr(), REDUCTIONS[reduction],
-                                   rowsum.numel(), w.data_ptr(), coef.data_ptr(), _stream(rowsum)))
-
-    def bwd(self, q, k, d, layout, temperature, coef_q, coef_k, w_q, view0, view1, inv_norm, dview0,
-            dview1, workspace):
+    def bwd(self, q, k, d, layout, temperature, rowsum_q, rowsum_k, w_q, w_k, w_stride, w_scale, view0,
+            view1, inv_norm, dview0, dview1, workspace):
         lay = NtxLayout(*layout)
         _check(load().ntx_bwd(q.data_ptr(), k.data_ptr(), q.shape[0], k.shape[0], d, q.shape[1],
-                              DTYPES[q.dtype], ctypes.byref(lay), float(temperature), coef_q.data_ptr(),
-                              coef_k.data_ptr(), w_q.data_ptr(), view0.data_ptr(), view1.data_ptr(),
-                              DTYPES[view0.dtype], inv_norm.data_ptr(), dview0.data_ptr(),
-                              dview1.data_ptr(), workspace.data_ptr(),
-                              workspace.numel() * workspace.element_size(), _stream(q)))
+                              DTYPES[q.dtype], ctypes.byref(lay), float(temperature), rowsum_q.data_ptr(),
+                              rowsum_k.data_ptr(), w_q.data_ptr(), w_k.data_ptr(), int(w_stride),
+                              float(w_scale), view0.data_ptr(), view1.data_ptr(), DTYPES[view0.dtype],
+                              inv_norm.data_ptr(), dview0.data_ptr(), dview1.data_ptr(),
+                              workspace.data_ptr(), workspace.numel() * workspace.element_size(),
+                              _stream(q)))
 
     def profile_next(self, which: int, ev_start: "torch.cuda.Event", ev_stop: "torch.cuda.Event"):
         """Arm the measurement hook: the next fwd (0) / bwd (1) call on this thread brackets its

@@ -37,20 +37,24 @@ def stale() -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    if not force and not stale():
+def build(force: bool = False, verbose: bool = False, defines=(), out: str = LIB) -> str:
+    """`defines`/`out` build instrumented variants (e.g. -DNTX_TIMING) next to the product library."""
+    if not force and not defines and not stale():
         return LIB
-    cmd = [find_nvcc(), *NVCC_FLAGS]
+    cmd = [find_nvcc(), *NVCC_FLAGS, *[f"-D{d}" for d in defines]]
     if verbose:
         cmd += ["-Xptxas", "-v"]
-    cmd += [os.path.join(CSRC, f) for f in SOURCES] + ["-o", LIB]
+    cmd += [os.path.join(CSRC, f) for f in SOURCES] + ["-o", out]
     proc = subprocess.run(cmd, capture_output=True, text=True)
     if proc.returncode != 0:
         raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + proc.stdout + proc.stderr)
     if verbose:
         print(proc.stderr)
-    return LIB
+    return out
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    if "--timing" in sys.argv:
+        print(build(force=True, defines=("NTX_TIMING",), out=os.path.join(PKG, "libntxent_b200_timing.so")))
+    else:
+        print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

@@ -136,7 +136,7 @@ int ntx_plan(int q_rows, int k_rows, int d, int dtype, int sm_count, NtxPlan* pl
     }
     plan->max_slots = max_slots;
     const uint64_t rows_pad = (uint64_t)plan->row_blocks * plan->tile_rows;
-    plan->fwd_ws_bytes = (uint64_t)max_slots * rows_pad * sizeof(float);
+    plan->fwd_ws_bytes = (uint64_t)max_slots * rows_pad * sizeof(float) + 16;   // + finalize ticket
     plan->bwd_ws_bytes = (uint64_t)max_slots * rows_pad * plan->d_pad * sizeof(float);
     return NTX_OK;
 }
@@ -172,37 +172,32 @@ int ntx_fwd(const void* q, const void* k, int q_rows, int k_rows, int d, int ld,
     if ((rc = aligned16(workspace, "workspace"))) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     float* partial = (float*)workspace;
+    unsigned int* counter = (unsigned int*)((char*)workspace + plan.fwd_ws_bytes - 16);
     {
         ProfScope prof(0, st);
         if (plan.tensor_cores)
-            rc = ntx_tc_fwd_launch((const __nv_bfloat16*)q, (const __nv_bfloat16*)k, dm, plan, partial, st);
+            rc = ntx_tc_fwd_launch((const __nv_bfloat16*)q, (const __nv_bfloat16*)k, dm, plan, partial,
+                                   counter, st);
         else
-            rc = ntx_simt_fwd_launch((const float*)q, (const float*)k, dm, plan, partial, st);
+            rc = ntx_simt_fwd_launch((const float*)q, (const float*)k, dm, plan, partial, counter, st);
     }
     if (rc) return rc;
-    return ntx_fwd_finalize_launch(q, dtype, dm, plan, partial, rowsum, pos_logit, row_loss, loss_sum, st);
-}
-
-int ntx_bwd_prep(const float* rowsum, const float* grad_output, int reduction, int q_rows, float* w,
-                 float* coef, void* stream) {
-    NTX_CHECK_ARG(rowsum && grad_output && w && coef, "NULL buffer");
-    NTX_CHECK_ARG(q_rows >= 2 && q_rows % 2 == 0, "q_rows=%d must be even and positive", q_rows);
-    NTX_CHECK_ARG(reduction == NTX_REDUCE_NONE || reduction == NTX_REDUCE_MEAN ||
-                      reduction == NTX_REDUCE_SUM, "bad reduction %d (loss.py:17)", reduction);
-    return ntx_bwd_prep_launch(rowsum, grad_output, reduction, q_rows, w, coef, (cudaStream_t)stream);
+    return ntx_fwd_finalize_launch(q, dtype, dm, plan, partial, counter, rowsum, pos_logit, row_loss,
+                                   loss_sum, st);
 }
 
 int ntx_bwd(const void* q, const void* k, int q_rows, int k_rows, int d, int ld, int dtype,
-            const NtxLayout* layout, float temperature, const float* coef_q, const float* coef_k,
-            const float* w_q, const void* view0, const void* view1, int in_dtype,
-            const float* inv_norm, void* dview0, void* dview1, void* workspace,
-            size_t workspace_bytes, void* stream) {
+            const NtxLayout* layout, float temperature, const float* rowsum_q, const float* rowsum_k,
+            const float* w_q, const float* w_k, int w_stride, float w_scale, const void* view0,
+            const void* view1, int in_dtype, const float* inv_norm, void* dview0, void* dview1,
+            void* workspace, size_t workspace_bytes, void* stream) {
     NtxDims dm;
     int rc = make_dims(q_rows, k_rows, d, ld, dtype, layout, temperature, &dm);
     if (rc) return rc;
     if ((rc = aligned16(q, "q rows")) || (rc = aligned16(k, "k rows"))) return rc;
-    NTX_CHECK_ARG(coef_q && coef_k && w_q && view0 && view1 && inv_norm && dview0 && dview1,
+    NTX_CHECK_ARG(rowsum_q && rowsum_k && w_q && w_k && view0 && view1 && inv_norm && dview0 && dview1,
                   "NULL buffer");
+    NTX_CHECK_ARG(w_stride == 0 || w_stride == 1, "w_stride must be 0 (one weight) or 1 (one per row)");
     NTX_CHECK_ARG(in_dtype == NTX_F32 || in_dtype == NTX_BF16, "view dtype %d not supported", in_dtype);
     NtxPlan plan;
     if ((rc = ntx_plan(q_rows, k_rows, d, dtype, 0, &plan))) return rc;
@@ -214,16 +209,16 @@ int ntx_bwd(const void* q, const void* k, int q_rows, int k_rows, int d, int ld,
     if ((rc = aligned16(workspace, "workspace"))) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     float* partial = (float*)workspace;
+    const NtxWeights wt{rowsum_q, rowsum_k, w_q, w_k, w_stride, w_scale};
     {
         ProfScope prof(1, st);
         if (plan.tensor_cores)
-            rc = ntx_tc_bwd_launch((const __nv_bfloat16*)q, (const __nv_bfloat16*)k, dm, plan, coef_q,
-                                   coef_k, partial, st);
+            rc = ntx_tc_bwd_launch((const __nv_bfloat16*)q, (const __nv_bfloat16*)k, dm, plan, wt, partial, st);
         else
-            rc = ntx_simt_bwd_launch((const float*)q, (const float*)k, dm, plan, coef_q, coef_k, partial, st);
+            rc = ntx_simt_bwd_launch((const float*)q, (const float*)k, dm, plan, wt, partial, st);
     }
     if (rc) return rc;
-    return ntx_bwd_finalize_launch(dm, plan, partial, w_q, view0, view1, in_dtype, inv_norm, dview0,
+    return ntx_bwd_finalize_launch(dm, plan, partial, wt, view0, view1, in_dtype, inv_norm, dview0,
                                    dview1, st);
 }
 

@@ -76,25 +76,32 @@ struct NtxDims {
     float inv_tau;
 };
 
+// Backward weights: alpha_r = w_q[r*stride]*scale / rowsum_q[r],  beta_c = w_k[c*stride]*scale / rowsum_k[c]
+struct NtxWeights {
+    const float* rowsum_q;
+    const float* rowsum_k;
+    const float* w_q;
+    const float* w_k;
+    int w_stride;      // 0: one upstream gradient for every row (mean / sum), 1: one per row (none)
+    float w_scale;     // 1 / q_rows for mean, 1 otherwise
+};
+
 // launch helpers implemented per translation unit
 int ntx_l2norm_launch(const void* v0, const void* v1, int n, int d, int in_dtype, void* rows, int ld,
                       int rows_dtype, float* inv_norm, cudaStream_t st);
 int ntx_simt_fwd_launch(const float* q, const float* k, const NtxDims& dm, const NtxPlan& plan,
-                        float* partial, cudaStream_t st);
+                        float* partial, unsigned int* counter, cudaStream_t st);
 int ntx_simt_bwd_launch(const float* q, const float* k, const NtxDims& dm, const NtxPlan& plan,
-                        const float* coef_q, const float* coef_k, float* partial, cudaStream_t st);
+                        const NtxWeights& w, float* partial, cudaStream_t st);
 int ntx_tc_fwd_launch(const __nv_bfloat16* q, const __nv_bfloat16* k, const NtxDims& dm,
-                      const NtxPlan& plan, float* partial, cudaStream_t st);
+                      const NtxPlan& plan, float* partial, unsigned int* counter, cudaStream_t st);
 int ntx_tc_bwd_launch(const __nv_bfloat16* q, const __nv_bfloat16* k, const NtxDims& dm,
-                      const NtxPlan& plan, const float* coef_q, const float* coef_k, float* partial,
-                      cudaStream_t st);
+                      const NtxPlan& plan, const NtxWeights& w, float* partial, cudaStream_t st);
 int ntx_fwd_finalize_launch(const void* q, int dtype, const NtxDims& dm, const NtxPlan& plan,
-                            const float* partial, float* rowsum, float* pos_logit, float* row_loss,
-                            float* loss_sum, cudaStream_t st);
-int ntx_bwd_prep_launch(const float* rowsum, const float* grad_out, int reduction, int q_rows,
-                        float* w, float* coef, cudaStream_t st);
+                            const float* partial, unsigned int* counter, float* rowsum, float* pos_logit,
+                            float* row_loss, float* loss_sum, cudaStream_t st);
 int ntx_debug_indices_launch(int n_local, int rank, int32_t* self_col, int32_t* pos_col,
                              cudaStream_t st);
 int ntx_bwd_finalize_launch(const NtxDims& dm, const NtxPlan& plan, const float* partial,
-                            const float* w_q, const void* view0, const void* view1, int in_dtype,
+                            const NtxWeights& w, const void* view0, const void* view1, int in_dtype,
                             const float* inv_norm, void* dview0, void* dview1, cudaStream_t st);

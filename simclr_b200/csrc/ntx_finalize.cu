@@ -4,131 +4,211 @@
 //                 positive logit as a direct dot product with the partner row
 //                 (targets = arange(N) of loss.py:37 -> ntx_pos_row), and form
 //                 row_loss = log(rowsum) + 1/tau - pos  (= logsumexp - positive,
-//                 the per-row cross entropy of loss.py:56-61).
-//  loss_reduce  : fixed-order sum of the row losses (loss.py:60-61).
-//  bwd_prep     : row weights from the upstream gradient and coef = w / rowsum.
+//                 the per-row cross entropy of loss.py:56-61).  The last block to
+//                 finish adds all row losses in a fixed order (loss.py:60-65).
 //  bwd_finalize : add the dZ partials, subtract the positive-pair term, scale by
 //                 1/tau and apply the Jacobian of x / max(||x||, eps)
 //                 (loss.py:33-34 backward), write dview0 / dview1.
-// All are HBM/L2-bound O(rows * d) passes; one warp per row.
+// Both are HBM/L2-bound O(rows * d) passes with 128-bit accesses.
 #include "ntx_common.cuh"
 
 namespace {
 
-constexpr int kWarps = 8;
+constexpr int kThreads = 256;
 
-__device__ __forceinline__ float warp_sum(float v) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+__device__ __forceinline__ float ldf(const float* p, size_t i) { return __ldg(p + i); }
+__device__ __forceinline__ float ldf(const __nv_bfloat16* p, size_t i) { return __bfloat162float(p[i]); }
+__device__ __forceinline__ void stf(float* p, size_t i, float v) { p[i] = v; }
+__device__ __forceinline__ void stf(__nv_bfloat16* p, size_t i, float v) { p[i] = __float2bfloat16_rn(v); }
+
+// 4 consecutive elements as floats (16-byte fp32 / 8-byte bf16 accesses)
+__device__ __forceinline__ float4 ld4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+__device__ __forceinline__ float4 ld4(const __nv_bfloat16* p) {
+    const uint2 t = __ldg(reinterpret_cast<const uint2*>(p));
+    const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&t.x));
+    const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&t.y));
+    return make_float4(a.x, a.y, b.x, b.y);
+}
+__device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+__device__ __forceinline__ void st4(__nv_bfloat16* p, float4 v) {
+    __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
+    uint2 t;
+    t.x = *reinterpret_cast<uint32_t*>(&a);
+    t.y = *reinterpret_cast<uint32_t*>(&b);
+    *reinterpret_cast<uint2*>(p) = t;
+}
+
+// sum over the `width` consecutive lanes that share a row (width = power of two <= 32)
+__device__ __forceinline__ float group_sum(float v, int width) {
+    for (int o = width >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     return v;
 }
 
-__device__ __forceinline__ float ldf(const float* p, size_t i) { return __ldg(p + i); }
-__device__ __forceinline__ float ldf(const __nv_bfloat16* p, size_t i) {
-    return __bfloat162float(p[i]);
-}
-__device__ __forceinline__ void stf(float* p, size_t i, float v) { p[i] = v; }
-__device__ __forceinline__ void stf(__nv_bfloat16* p, size_t i, float v) {
-    p[i] = __float2bfloat16_rn(v);
-}
-
+// ------------------------------------------------------------------ forward finalize
+// `lanes` threads per row (power of two), each covers 4-element groups sub, sub+lanes, ...
 template <typename T>
-__global__ void __launch_bounds__(kWarps * 32)
-fwd_finalize_kernel(const T* __restrict__ q, NtxDims dm, int tile_rows, int key_tiles, long long Tt,
-                    int G, int rows_pad, const float* __restrict__ partial,
-                    float* __restrict__ rowsum, float* __restrict__ pos_logit,
-                    float* __restrict__ row_loss) {
-    const int lane = threadIdx.x & 31;
-    const int r = blockIdx.x * kWarps + (threadIdx.x >> 5);
-    if (r >= dm.q_rows) return;
-    const int rb = r / tile_rows;
-    const int ns = ntx_num_slots(Tt, G, key_tiles, rb);
-    float R = 0.f;
-    for (int s = 0; s < ns; ++s) R += __ldg(partial + (size_t)s * rows_pad + r);
-
-    const int p = ntx_pos_row(r, dm.n_local);
-    const T* a = q + (size_t)r * dm.ld;
-    const T* b = q + (size_t)p * dm.ld;
-    float dot = 0.f;
-    for (int c = lane; c < dm.ld; c += 32) dot = fmaf(ldf(a, c), ldf(b, c), dot);
-    dot = warp_sum(dot);
-    if (lane == 0) {
-        const float pos = dot * dm.inv_tau;
-        rowsum[r] = R;
-        pos_logit[r] = pos;
-        row_loss[r] = logf(R) + dm.inv_tau - pos;
+__global__ void __launch_bounds__(kThreads)
+fwd_finalize_kernel(const T* __restrict__ q, NtxDims dm, int lanes, int tile_rows, int key_tiles,
+                    long long Tt, int G, int rows_pad, const float* __restrict__ partial,
+                    unsigned int* __restrict__ counter, float* __restrict__ rowsum,
+                    float* __restrict__ pos_logit, float* __restrict__ row_loss,
+                    float* __restrict__ loss_sum) {
+    const int rows_per_block = kThreads / lanes;
+    const int sub = threadIdx.x % lanes;
+    const int r_raw = blockIdx.x * rows_per_block + threadIdx.x / lanes;
+    const bool live = r_raw < dm.q_rows;
+    const int r = live ? r_raw : dm.q_rows - 1;              // keep every lane in the shuffles
+    {
+        const int p = ntx_pos_row(r, dm.n_local);
+        const T* a = q + (size_t)r * dm.ld;
+        const T* b = q + (size_t)p * dm.ld;
+        float dot = 0.f;
+        for (int c = sub * 4; c < dm.ld; c += lanes * 4) {      // ld is a multiple of 4
+            const float4 x = ld4(a + c), y = ld4(b + c);
+            dot = fmaf(x.x, y.x, fmaf(x.y, y.y, fmaf(x.z, y.z, fmaf(x.w, y.w, dot))));
+        }
+        dot = group_sum(dot, lanes);
+        if (sub == 0 && live) {
+            const int rb = r / tile_rows;
+            const int ns = ntx_num_slots(Tt, G, key_tiles, rb);
+            float R = 0.f;
+            for (int s = 0; s < ns; ++s) R += __ldg(partial + (size_t)s * rows_pad + r);
+            const float pos = dot * dm.inv_tau;
+            rowsum[r] = R;
+            pos_logit[r] = pos;
+            row_loss[r] = logf(R) + dm.inv_tau - pos;
+        }
     }
-}
-
-__global__ void __launch_bounds__(1024)
-loss_reduce_kernel(const float* __restrict__ row_loss, int rows, float* __restrict__ loss_sum) {
-    __shared__ double part[32];
+    // last block standing adds every row loss in index order: deterministic (loss.py:60-65)
+    __shared__ bool is_last;
+    __shared__ double part[kThreads / 32];
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) is_last = atomicAdd(counter, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
     double acc = 0.0;
-    for (int i = threadIdx.x; i < rows; i += 1024) acc += (double)row_loss[i];
+    for (int i = threadIdx.x; i < dm.q_rows; i += kThreads) acc += (double)__ldcg(row_loss + i);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
     if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = acc;
     __syncthreads();
-    if (threadIdx.x < 32) {
-        double v = part[threadIdx.x];
+    if (threadIdx.x == 0) {
+        double v = 0.0;
+        for (int w = 0; w < kThreads / 32; ++w) v += part[w];
+        loss_sum[0] = (float)v;                              // reduction="sum"
+        loss_sum[1] = (float)(v / (double)dm.q_rows);        // reduction="mean": sum / N * 0.5, rows = 2N
+        *counter = 0;
+    }
+}
+
+// ------------------------------------------------------------------ backward finalize
+struct BwdFinArgs {
+    NtxDims dm;
+    int tile_rows, key_tiles, G, rows_pad, d_pad;
+    long long Tt;
+    const float* partial;
+    NtxWeights w;
+    const float* inv_norm;
+};
+
+__device__ __forceinline__ float pair_weight(const NtxWeights& w, int r, int p) {
+    // (P - Y) and its transpose both hit the positive pair: weight w_r + w_p
+    return (__ldg(w.w_q + (size_t)r * w.w_stride) + __ldg(w.w_q + (size_t)p * w.w_stride)) * w.w_scale;
+}
+
+// fast path: d % 4 == 0, one group of `lanes` threads per row, up to kMaxV float4 per thread
+template <typename TIn, int kMaxV>
+__global__ void __launch_bounds__(kThreads)
+bwd_finalize_vec_kernel(BwdFinArgs A, int lanes, const TIn* __restrict__ view0,
+                        const TIn* __restrict__ view1, TIn* __restrict__ dview0, TIn* __restrict__ dview1) {
+    const NtxDims& dm = A.dm;
+    const int rows_per_block = kThreads / lanes;
+    const int sub = threadIdx.x % lanes;
+    const int r_raw = blockIdx.x * rows_per_block + threadIdx.x / lanes;
+    const bool live = r_raw < dm.q_rows;
+    const int r = live ? r_raw : dm.q_rows - 1;              // keep every lane in the shuffles
+    const int n = dm.n_local, d = dm.d;
+    const int p = ntx_pos_row(r, n);
+    const int ns = ntx_num_slots(A.Tt, A.G, A.key_tiles, r / A.tile_rows);
+    const TIn* zr = r < n ? view0 + (size_t)r * d : view1 + (size_t)(r - n) * d;
+    const TIn* zp = p < n ? view0 + (size_t)p * d : view1 + (size_t)(p - n) * d;
+    TIn* out = r < n ? dview0 + (size_t)r * d : dview1 + (size_t)(r - n) * d;
+    const float inr = __ldg(A.inv_norm + r), inp = __ldg(A.inv_norm + p);
+    const float wpair = pair_weight(A.w, r, p);
+    const float* part = A.partial + (size_t)r * A.d_pad;
+    const size_t slot_stride = (size_t)A.rows_pad * A.d_pad;
+
+    float4 g[kMaxV], zh[kMaxV];
+    float proj = 0.f;
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        if (threadIdx.x == 0) {
-            loss_sum[0] = (float)v;                    // reduction="sum"
-            loss_sum[1] = (float)(v / (double)rows);   // reduction="mean": sum / N * 0.5, rows = 2N
+    for (int v = 0; v < kMaxV; ++v) {
+        const int c = (sub + v * lanes) * 4;
+        if (c < d) {
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int s = 0; s < ns; ++s) {
+                const float4 t = __ldg(reinterpret_cast<const float4*>(part + s * slot_stride + c));
+                acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+            }
+            const float4 zpv = ld4(zp + c), zrv = ld4(zr + c);
+            const float k = wpair * inp, it = dm.inv_tau;
+            g[v] = make_float4((acc.x - k * zpv.x) * it, (acc.y - k * zpv.y) * it, (acc.z - k * zpv.z) * it,
+                               (acc.w - k * zpv.w) * it);
+            zh[v] = make_float4(zrv.x * inr, zrv.y * inr, zrv.z * inr, zrv.w * inr);
+            proj = fmaf(zh[v].x, g[v].x, fmaf(zh[v].y, g[v].y, fmaf(zh[v].z, g[v].z, fmaf(zh[v].w, g[v].w, proj))));
+        }
+    }
+    proj = group_sum(proj, lanes);
+    const bool clamped = inr >= 1e12f;    // ||z|| <= eps: denominator was the constant eps
+#pragma unroll
+    for (int v = 0; v < kMaxV; ++v) {
+        const int c = (sub + v * lanes) * 4;
+        if (c < d && live) {
+            float4 o;
+            if (clamped) {
+                o = make_float4(g[v].x * inr, g[v].y * inr, g[v].z * inr, g[v].w * inr);
+            } else {
+                o = make_float4((g[v].x - zh[v].x * proj) * inr, (g[v].y - zh[v].y * proj) * inr,
+                                (g[v].z - zh[v].z * proj) * inr, (g[v].w - zh[v].w * proj) * inr);
+            }
+            st4(out + c, o);
         }
     }
 }
 
-__global__ void bwd_prep_kernel(const float* __restrict__ rowsum, const float* __restrict__ grad_out,
-                                int reduction, int q_rows, float* __restrict__ w,
-                                float* __restrict__ coef) {
-    const int r = blockIdx.x * blockDim.x + threadIdx.x;
-    if (r >= q_rows) return;
-    float wr;
-    if (reduction == NTX_REDUCE_NONE) wr = grad_out[r];
-    else if (reduction == NTX_REDUCE_MEAN) wr = grad_out[0] / (float)q_rows;   // loss / N * 0.5
-    else wr = grad_out[0];
-    w[r] = wr;
-    coef[r] = wr / rowsum[r];
-}
-
+// generic path: any d, one warp per row, two passes
 template <typename TIn>
-__global__ void __launch_bounds__(kWarps * 32)
-bwd_finalize_kernel(NtxDims dm, int tile_rows, int key_tiles, long long Tt, int G, int rows_pad,
-                    int d_pad, const float* __restrict__ partial, const float* __restrict__ w_q,
-                    const TIn* __restrict__ view0, const TIn* __restrict__ view1,
-                    const float* __restrict__ inv_norm, TIn* __restrict__ dview0,
-                    TIn* __restrict__ dview1) {
+__global__ void __launch_bounds__(kThreads)
+bwd_finalize_kernel(BwdFinArgs A, const TIn* __restrict__ view0, const TIn* __restrict__ view1,
+                    TIn* __restrict__ dview0, TIn* __restrict__ dview1) {
+    const NtxDims& dm = A.dm;
     const int lane = threadIdx.x & 31;
-    const int r = blockIdx.x * kWarps + (threadIdx.x >> 5);
-    if (r >= dm.q_rows) return;
+    const int r = blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5);
+    if (r >= dm.q_rows) return;                              // whole warps leave together
     const int n = dm.n_local, d = dm.d;
     const int p = ntx_pos_row(r, n);
-    const int rb = r / tile_rows;
-    const int ns = ntx_num_slots(Tt, G, key_tiles, rb);
+    const int ns = ntx_num_slots(A.Tt, A.G, A.key_tiles, r / A.tile_rows);
     const TIn* zr = r < n ? view0 + (size_t)r * d : view1 + (size_t)(r - n) * d;
     const TIn* zp = p < n ? view0 + (size_t)p * d : view1 + (size_t)(p - n) * d;
     TIn* out = r < n ? dview0 + (size_t)r * d : dview1 + (size_t)(r - n) * d;
-    const float inr = __ldg(inv_norm + r), inp = __ldg(inv_norm + p);
-    const float wpair = __ldg(w_q + r) + __ldg(w_q + p);   // (P - Y) and its transpose both hit the pair
-    const float* part = partial + (size_t)r * d_pad;
-    const size_t slot_stride = (size_t)rows_pad * d_pad;
+    const float inr = __ldg(A.inv_norm + r), inp = __ldg(A.inv_norm + p);
+    const float wpair = pair_weight(A.w, r, p);
+    const float* part = A.partial + (size_t)r * A.d_pad;
+    const size_t slot_stride = (size_t)A.rows_pad * A.d_pad;
 
     auto dzhat = [&](int c) {
         float acc = 0.f;
         for (int s = 0; s < ns; ++s) acc += __ldg(part + s * slot_stride + c);
         return (acc - wpair * (ldf(zp, c) * inp)) * dm.inv_tau;
     };
-
     float proj = 0.f;
     for (int c = lane; c < d; c += 32) proj = fmaf(ldf(zr, c) * inr, dzhat(c), proj);
-    proj = warp_sum(proj);
-    const bool clamped = inr >= 1e12f;    // ||z|| <= eps: denominator was the constant eps
+    proj = group_sum(proj, 32);
+    const bool clamped = inr >= 1e12f;
     for (int c = lane; c < d; c += 32) {
         const float g = dzhat(c);
-        const float v = clamped ? g * inr : (g - ldf(zr, c) * inr * proj) * inr;
-        stf(out, c, v);
+        stf(out, c, clamped ? g * inr : (g - ldf(zr, c) * inr * proj) * inr);
     }
 }
 
@@ -138,6 +218,40 @@ __global__ void debug_indices_kernel(int n_local, int rank, int32_t* __restrict_
     if (r >= 2 * n_local) return;
     self_col[r] = ntx_self_col(r, n_local, rank);
     pos_col[r] = ntx_pos_col(r, n_local, rank);
+}
+
+int lanes_for(int groups4) {       // threads per row: power of two covering the row's float4 groups
+    int l = 1;
+    while (l < groups4 && l < 32) l <<= 1;
+    return l;
+}
+
+template <typename TIn>
+int launch_bwd_finalize(const BwdFinArgs& A, const void* view0, const void* view1, void* dview0,
+                        void* dview1, cudaStream_t st) {
+    const int d = A.dm.d;
+    const bool vec = d % 4 == 0 && d <= 1024 &&
+                     reinterpret_cast<uintptr_t>(view0) % 16 == 0 && reinterpret_cast<uintptr_t>(view1) % 16 == 0 &&
+                     reinterpret_cast<uintptr_t>(dview0) % 16 == 0 && reinterpret_cast<uintptr_t>(dview1) % 16 == 0;
+    if (vec) {
+        const int lanes = lanes_for(d / 4);
+        const int grid = (A.dm.q_rows + kThreads / lanes - 1) / (kThreads / lanes);
+        if (d <= 128)
+            bwd_finalize_vec_kernel<TIn, 1><<<grid, kThreads, 0, st>>>(A, lanes, (const TIn*)view0, (const TIn*)view1,
+                                                                       (TIn*)dview0, (TIn*)dview1);
+        else if (d <= 256)
+            bwd_finalize_vec_kernel<TIn, 2><<<grid, kThreads, 0, st>>>(A, lanes, (const TIn*)view0, (const TIn*)view1,
+                                                                       (TIn*)dview0, (TIn*)dview1);
+        else
+            bwd_finalize_vec_kernel<TIn, 8><<<grid, kThreads, 0, st>>>(A, lanes, (const TIn*)view0, (const TIn*)view1,
+                                                                       (TIn*)dview0, (TIn*)dview1);
+    } else {
+        const int grid = (A.dm.q_rows + kThreads / 32 - 1) / (kThreads / 32);
+        bwd_finalize_kernel<TIn><<<grid, kThreads, 0, st>>>(A, (const TIn*)view0, (const TIn*)view1, (TIn*)dview0,
+                                                            (TIn*)dview1);
+    }
+    NTX_CUDA(cudaGetLastError());
+    return NTX_OK;
 }
 
 }  // namespace
@@ -150,47 +264,38 @@ int ntx_debug_indices_launch(int n_local, int rank, int32_t* self_col, int32_t* 
 }
 
 int ntx_fwd_finalize_launch(const void* q, int dtype, const NtxDims& dm, const NtxPlan& plan,
-                            const float* partial, float* rowsum, float* pos_logit, float* row_loss,
-                            float* loss_sum, cudaStream_t st) {
+                            const float* partial, unsigned int* counter, float* rowsum, float* pos_logit,
+                            float* row_loss, float* loss_sum, cudaStream_t st) {
     const long long T = (long long)plan.row_blocks * plan.key_tiles;
     const int rows_pad = plan.row_blocks * plan.tile_rows;
-    const int grid = (dm.q_rows + kWarps - 1) / kWarps;
+    const int lanes = lanes_for(dm.ld / 4);
+    const int grid = (dm.q_rows + kThreads / lanes - 1) / (kThreads / lanes);
     if (dtype == NTX_F32)
-        fwd_finalize_kernel<float><<<grid, kWarps * 32, 0, st>>>(
-            (const float*)q, dm, plan.tile_rows, plan.key_tiles, T, plan.grid, rows_pad, partial,
-            rowsum, pos_logit, row_loss);
+        fwd_finalize_kernel<float><<<grid, kThreads, 0, st>>>(
+            (const float*)q, dm, lanes, plan.tile_rows, plan.key_tiles, T, plan.grid, rows_pad, partial,
+            counter, rowsum, pos_logit, row_loss, loss_sum);
     else
-        fwd_finalize_kernel<__nv_bfloat16><<<grid, kWarps * 32, 0, st>>>(
-            (const __nv_bfloat16*)q, dm, plan.tile_rows, plan.key_tiles, T, plan.grid, rows_pad,
-            partial, rowsum, pos_logit, row_loss);
-    NTX_CUDA(cudaGetLastError());
-    loss_reduce_kernel<<<1, 1024, 0, st>>>(row_loss, dm.q_rows, loss_sum);
-    NTX_CUDA(cudaGetLastError());
-    return NTX_OK;
-}
-
-int ntx_bwd_prep_launch(const float* rowsum, const float* grad_out, int reduction, int q_rows,
-                        float* w, float* coef, cudaStream_t st) {
-    bwd_prep_kernel<<<(q_rows + 255) / 256, 256, 0, st>>>(rowsum, grad_out, reduction, q_rows, w, coef);
+        fwd_finalize_kernel<__nv_bfloat16><<<grid, kThreads, 0, st>>>(
+            (const __nv_bfloat16*)q, dm, lanes, plan.tile_rows, plan.key_tiles, T, plan.grid, rows_pad,
+            partial, counter, rowsum, pos_logit, row_loss, loss_sum);
     NTX_CUDA(cudaGetLastError());
     return NTX_OK;
 }
 
 int ntx_bwd_finalize_launch(const NtxDims& dm, const NtxPlan& plan, const float* partial,
-                            const float* w_q, const void* view0, const void* view1, int in_dtype,
+                            const NtxWeights& w, const void* view0, const void* view1, int in_dtype,
                             const float* inv_norm, void* dview0, void* dview1, cudaStream_t st) {
-    const long long T = (long long)plan.row_blocks * plan.key_tiles;
-    const int rows_pad = plan.row_blocks * plan.tile_rows;
-    const int grid = (dm.q_rows + kWarps - 1) / kWarps;
-    if (in_dtype == NTX_F32)
-        bwd_finalize_kernel<float><<<grid, kWarps * 32, 0, st>>>(
-            dm, plan.tile_rows, plan.key_tiles, T, plan.grid, rows_pad, plan.d_pad, partial, w_q,
-            (const float*)view0, (const float*)view1, inv_norm, (float*)dview0, (float*)dview1);
-    else
-        bwd_finalize_kernel<__nv_bfloat16><<<grid, kWarps * 32, 0, st>>>(
-            dm, plan.tile_rows, plan.key_tiles, T, plan.grid, rows_pad, plan.d_pad, partial, w_q,
-            (const __nv_bfloat16*)view0, (const __nv_bfloat16*)view1, inv_norm,
-            (__nv_bfloat16*)dview0, (__nv_bfloat16*)dview1);
-    NTX_CUDA(cudaGetLastError());
-    return NTX_OK;
+    BwdFinArgs A;
+    A.dm = dm;
+    A.tile_rows = plan.tile_rows;
+    A.key_tiles = plan.key_tiles;
+    A.G = plan.grid;
+    A.rows_pad = plan.row_blocks * plan.tile_rows;
+    A.d_pad = plan.d_pad;
+    A.Tt = (long long)plan.row_blocks * plan.key_tiles;
+    A.partial = partial;
+    A.w = w;
+    A.inv_norm = inv_norm;
+    if (in_dtype == NTX_F32) return launch_bwd_finalize<float>(A, view0, view1, dview0, dview1, st);
+    return launch_bwd_finalize<__nv_bfloat16>(A, view0, view1, dview0, dview1, st);
 }

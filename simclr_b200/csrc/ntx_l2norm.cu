@@ -2,7 +2,7 @@
 // Replaces F.normalize(view, p=2, dim=1) at loss.py:33-34: x / max(||x||_2, 1e-12).
 //
 // HBM-bound: reads 2n*d input elements once (second pass hits L1), writes 2n*ld
-// output elements + 2n floats.  One warp per row, 128-bit accesses when the row
+// output elements + 2n floats.  A group of lanes per row, 128-bit accesses when the row
 // length allows, fp32 accumulation.  Output rows are zero padded from d to ld so
 // the tensor-core kernels can TMA whole 64-element swizzle atoms.
 #include "ntx_common.cuh"
@@ -10,12 +10,6 @@
 namespace {
 
 constexpr int kWarpsPerBlock = 8;
-
-__device__ __forceinline__ float warp_sum(float v) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    return v;
-}
 
 template <typename T> struct Vec;   // 16-byte vector of T
 template <> struct Vec<float> {
@@ -62,37 +56,42 @@ __device__ __forceinline__ void storev(__nv_bfloat16* p, const float (&v)[N]) {
     }
 }
 
+// `lanes` consecutive threads (power of two <= 32) share one row, so short rows
+// (d = 128 bf16 is only 16 sixteen-byte loads) still keep every lane busy.
 template <typename TIn, typename TOut, bool kVector>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 l2norm_kernel(const TIn* __restrict__ view0, const TIn* __restrict__ view1, int n, int d,
-              TOut* __restrict__ rows, int ld, float* __restrict__ inv_norm) {
-    const int lane = threadIdx.x & 31;
-    const int r = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
-    if (r >= 2 * n) return;
+              TOut* __restrict__ rows, int ld, float* __restrict__ inv_norm, int lanes) {
+    const int sub = threadIdx.x % lanes;
+    const int rows_per_block = kWarpsPerBlock * 32 / lanes;
+    const int r_raw = blockIdx.x * rows_per_block + threadIdx.x / lanes;
+    const bool live = r_raw < 2 * n;
+    const int r = live ? r_raw : 2 * n - 1;                   // keep every lane in the shuffles
     const TIn* src = (r < n) ? view0 + (size_t)r * d : view1 + (size_t)(r - n) * d;
     TOut* dst = rows + (size_t)r * ld;
     constexpr int V = Vec<TIn>::N;
 
     float ss = 0.f;
     if constexpr (kVector) {
-        for (int c = lane * V; c < d; c += 32 * V) {
+        for (int c = sub * V; c < d; c += lanes * V) {
             float v[V];
             Vec<TIn>::load(src + c, v);
 #pragma unroll
             for (int i = 0; i < V; ++i) ss = fmaf(v[i], v[i], ss);
         }
     } else {
-        for (int c = lane; c < d; c += 32) {
+        for (int c = sub; c < d; c += lanes) {
             float v = to_f32(src[c]);
             ss = fmaf(v, v, ss);
         }
     }
-    ss = warp_sum(ss);
+    for (int o = lanes >> 1; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
     const float denom = fmaxf(sqrtf(ss), 1e-12f);   // clamp_min(eps) of F.normalize
-    if (lane == 0) inv_norm[r] = 1.0f / denom;
+    if (!live) return;
+    if (sub == 0) inv_norm[r] = 1.0f / denom;
 
     if constexpr (kVector) {
-        for (int c = lane * V; c < ld; c += 32 * V) {   // ld is a multiple of V on this path
+        for (int c = sub * V; c < ld; c += lanes * V) {   // ld is a multiple of V on this path
             float v[V];
             if (c < d) {
                 Vec<TIn>::load(src + c, v);
@@ -105,7 +104,7 @@ l2norm_kernel(const TIn* __restrict__ view0, const TIn* __restrict__ view1, int 
             storev<V>(dst + c, v);
         }
     } else {
-        for (int c = lane; c < ld; c += 32) store1(dst + c, c < d ? to_f32(src[c]) / denom : 0.f);
+        for (int c = sub; c < ld; c += lanes) store1(dst + c, c < d ? to_f32(src[c]) / denom : 0.f);
     }
 }
 
@@ -117,13 +116,17 @@ int launch(const void* v0, const void* v1, int n, int d, void* rows, int ld, flo
                      (reinterpret_cast<uintptr_t>(v0) % 16 == 0) &&
                      (reinterpret_cast<uintptr_t>(v1) % 16 == 0) &&
                      (reinterpret_cast<uintptr_t>(rows) % 16 == 0);
-    const int grid = (2 * n + kWarpsPerBlock - 1) / kWarpsPerBlock;
+    const int work = vec ? (ld + V - 1) / V : ld;
+    int lanes = 1;
+    while (lanes < work && lanes < 32) lanes <<= 1;
+    const int rows_per_block = kWarpsPerBlock * 32 / lanes;
+    const int grid = (2 * n + rows_per_block - 1) / rows_per_block;
     if (vec)
         l2norm_kernel<TIn, TOut, true><<<grid, kWarpsPerBlock * 32, 0, st>>>(
-            (const TIn*)v0, (const TIn*)v1, n, d, (TOut*)rows, ld, inv_norm);
+            (const TIn*)v0, (const TIn*)v1, n, d, (TOut*)rows, ld, inv_norm, lanes);
     else
         l2norm_kernel<TIn, TOut, false><<<grid, kWarpsPerBlock * 32, 0, st>>>(
-            (const TIn*)v0, (const TIn*)v1, n, d, (TOut*)rows, ld, inv_norm);
+            (const TIn*)v0, (const TIn*)v1, n, d, (TOut*)rows, ld, inv_norm, lanes);
     NTX_CUDA(cudaGetLastError());
     return NTX_OK;
 }

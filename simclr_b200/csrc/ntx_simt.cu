@@ -7,7 +7,7 @@
 //   forward : per (row block, key tile) similarity tile in registers ->
 //             e = exp2(dot*c1 - c1), self / out-of-range columns zeroed ->
 //             row sums; the logits never leave the SM        (loss.py:42-61)
-//   backward: recompute the tile -> C = e * (coef_q[r] + coef_k[c]) ->
+//   backward: recompute the tile -> C = e * (w_r/R_r + w_c/R_c) ->
 //             dZ[row block] += C . K[key tile]               (autograd of the above)
 // Work is cut by the NtxPlan partition; every (CTA, row block) segment writes its
 // partial into its slot of the scratch buffer and the finalize kernels add the
@@ -70,12 +70,14 @@ __device__ __forceinline__ void similarity_tile(float (&acc)[4][4], float (*As)[
 
 __global__ void __launch_bounds__(NT)
 simt_fwd_kernel(const float* __restrict__ q, const float* __restrict__ k, NtxDims dm, int key_tiles,
-                long long T, int rows_pad, float* __restrict__ partial) {
+                long long T, int rows_pad, float* __restrict__ partial,
+                unsigned int* __restrict__ done_counter) {
     __shared__ __align__(16) float As[BK][PITCH];
     __shared__ __align__(16) float Bs[BK][PITCH];
     const int G = gridDim.x, cta = blockIdx.x;
     const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
     const long long t_begin = ntx_chunk_begin(T, G, cta), t_end = ntx_chunk_begin(T, G, cta + 1);
+    if (cta == 0 && threadIdx.x == 0) *done_counter = 0;    // ticket of the finalize kernel
 
     int cur_rb = -1;
     float rowsum[4] = {0.f, 0.f, 0.f, 0.f};
@@ -118,8 +120,7 @@ simt_fwd_kernel(const float* __restrict__ q, const float* __restrict__ k, NtxDim
 
 __global__ void __launch_bounds__(NT)
 simt_bwd_kernel(const float* __restrict__ q, const float* __restrict__ k, NtxDims dm, int key_tiles,
-                long long T, int rows_pad, int d_pad, const float* __restrict__ coef_q,
-                const float* __restrict__ coef_k, float* __restrict__ partial) {
+                long long T, int rows_pad, int d_pad, NtxWeights wt, float* __restrict__ partial) {
     __shared__ __align__(16) float As[BK][PITCH];
     __shared__ __align__(16) float Bs[BK][PITCH];
     __shared__ __align__(16) float Ct[BN][PITCH];     // coefficient tile, [key][row]
@@ -165,13 +166,17 @@ simt_bwd_kernel(const float* __restrict__ q, const float* __restrict__ k, NtxDim
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const int r = rb * BM + ty * 4 + i;
-            alpha[i] = r < dm.q_rows ? __ldg(coef_q + r) : 0.f;
+            alpha[i] = r < dm.q_rows
+                           ? __ldg(wt.w_q + (size_t)r * wt.w_stride) * wt.w_scale / __ldg(wt.rowsum_q + r)
+                           : 0.f;
             self[i] = ntx_self_col(r, dm.n_local, dm.rank);
         }
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const int c = kt * BN + tx * 4 + j;
-            beta[j] = c < dm.k_rows ? __ldg(coef_k + c) : 0.f;
+            beta[j] = c < dm.k_rows
+                          ? __ldg(wt.w_k + (size_t)c * wt.w_stride) * wt.w_scale / __ldg(wt.rowsum_k + c)
+                          : 0.f;
         }
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -222,21 +227,20 @@ simt_bwd_kernel(const float* __restrict__ q, const float* __restrict__ k, NtxDim
 }  // namespace
 
 int ntx_simt_fwd_launch(const float* q, const float* k, const NtxDims& dm, const NtxPlan& plan,
-                        float* partial, cudaStream_t st) {
+                        float* partial, unsigned int* counter, cudaStream_t st) {
     const long long T = (long long)plan.row_blocks * plan.key_tiles;
     const int rows_pad = plan.row_blocks * plan.tile_rows;
-    simt_fwd_kernel<<<plan.grid, NT, 0, st>>>(q, k, dm, plan.key_tiles, T, rows_pad, partial);
+    simt_fwd_kernel<<<plan.grid, NT, 0, st>>>(q, k, dm, plan.key_tiles, T, rows_pad, partial, counter);
     NTX_CUDA(cudaGetLastError());
     return NTX_OK;
 }
 
 int ntx_simt_bwd_launch(const float* q, const float* k, const NtxDims& dm, const NtxPlan& plan,
-                        const float* coef_q, const float* coef_k, float* partial, cudaStream_t st) {
+                        const NtxWeights& wt, float* partial, cudaStream_t st) {
     const long long T = (long long)plan.row_blocks * plan.key_tiles;
     const int rows_pad = plan.row_blocks * plan.tile_rows;
     dim3 grid(plan.grid, (plan.d_pad + BD - 1) / BD);
-    simt_bwd_kernel<<<grid, NT, 0, st>>>(q, k, dm, plan.key_tiles, T, rows_pad, plan.d_pad, coef_q,
-                                         coef_k, partial);
+    simt_bwd_kernel<<<grid, NT, 0, st>>>(q, k, dm, plan.key_tiles, T, rows_pad, plan.d_pad, wt, partial);
     NTX_CUDA(cudaGetLastError());
     return NTX_OK;
 }

@@ -1,52 +1,46 @@
 // bf16 mode of the fused NT-Xent kernels on the 5th-gen tensor cores (tcgen05).
 //
-// One persistent CTA per SM, 10 warps, warp specialised:
-//   warps 0-3 / 4-7 : two epilogue warpgroups; tile i of the CTA goes to group i % 2.
-//                     Thread = one row of the 128 x 128 similarity tile (TMEM lane).
-//   warp 8          : TMA producer (cp.async.bulk.tensor, 128B swizzle, mbarrier tx)
-//   warp 9          : TMEM allocator + the one thread that issues tcgen05.mma
+// One persistent CTA per SM, warp specialised:
+//   NWG epilogue warpgroups (4 warps each); tile i of the CTA goes to group i % NWG.
+//        Thread = one row of the 128 x 128 similarity tile (= one TMEM lane).
+//   1 TMA producer warp (cp.async.bulk.tensor, 128B swizzle, mbarrier transaction bytes)
+//   1 warp that allocates TMEM and whose lane 0 issues every tcgen05.mma
 //
-// Forward  (loss.py:42-61): S = Q . K^T lands in TMEM (4 buffers of 128 fp32 columns);
-//   the epilogue reads it with tcgen05.ld, forms e = exp2(s*c1 - c1) (fixed shift
-//   1/tau, |cos| <= 1), zeroes the self column / columns past the last key in edge
-//   tiles, and keeps per-row sums in registers.  The 2N x 2N logits never leave the SM.
-// Backward (autograd of the same lines): recompute S, C = e * (coef_q[r] + coef_k[c])
-//   as bf16 into a 128B-swizzled smem tile, second MMA  dZ += C . K  with the SAME key
-//   tile read MN-major, accumulator resident in TMEM across the CTA's key tiles.
+// Forward  (loss.py:42-61): S = Q . K^T lands in TMEM (4 buffers of 128 fp32 columns,
+//   one per epilogue group); the group reads it with tcgen05.ld, forms
+//   e = exp2(s*c1 - c1) (fixed shift 1/tau, |cos| <= 1), zeroes the self column and
+//   columns past the last key in edge tiles, and keeps per-row sums in registers.
+//   The 2N x 2N logits never leave the SM.
+// Backward (autograd of the same lines): recompute S, turn it IN PLACE in TMEM into the
+//   bf16 coefficient tile C = e * (w_r/R_r + w_c/R_c) (tcgen05.st over the fp32 columns
+//   already consumed), second MMA  dZ += C . K  with A read from TMEM and the SAME key
+//   tile read MN-major from shared memory; the dZ accumulator stays in TMEM across the
+//   CTA's key tiles.
 //
 // Work partition and scratch slots: see NtxPlan / ntx_common.cuh.
-#include <stdlib.h>
-
 #include "ntx_common.cuh"
 #include "ntx_umma.cuh"
+
+#ifdef NTX_TIMING
+// bring-up only: per-CTA cycle counters (fwd: slots 0-7, bwd: slots 8-15), read by ntx_debug_timers()
+__device__ long long g_ntx_timers[148][16];
+#define NTX_T(var) long long var = 0
+#define NTX_TIC(var) const long long var##_t0 = clock64()
+#define NTX_TOC(var) var += clock64() - var##_t0
+#define NTX_TSAVE(slot, var) g_ntx_timers[blockIdx.x % 148][slot] = (var)
+#else
+#define NTX_T(var)
+#define NTX_TIC(var)
+#define NTX_TOC(var)
+#define NTX_TSAVE(slot, var)
+#endif
 
 namespace {
 
 using namespace umma;
 
-constexpr int kThreads = 320;
-constexpr int kProducerWarp = 8;
-constexpr int kMmaWarp = 9;
 constexpr uint32_t kBlkBytes = 128 * 128;   // one [128 rows x 64 bf16] swizzled block
 constexpr uint32_t kTmemCols = 512;
-
-template <int NDB> struct FwdCfg { static constexpr int NS = NDB == 1 ? 6 : (NDB == 2 ? 4 : 2); };
-template <int NDB> struct BwdCfg {
-    static constexpr int NS = NDB == 1 ? 4 : (NDB == 2 ? 3 : 2);
-    static constexpr int NP = NDB == 4 ? 1 : 2;
-};
-
-template <int NS> struct FwdCtl {
-    uint64_t q_full, q_empty, k_full[NS], k_empty[NS], s_full[4], s_empty[4];
-    uint32_t tmem_base;
-    alignas(16) float xch[2][128];
-};
-template <int NS> struct BwdCtl {
-    uint64_t q_full, q_empty, k_full[NS], k_empty[NS], s_full[2], s_empty[2], p_full[2], p_empty[2],
-        dz_full, dz_empty;
-    uint32_t tmem_base;
-    alignas(16) float beta[2][2][128];
-};
 
 // dynamic smem is declared __align__(1024) (128B-swizzle atoms are 1024 B); refuse to run otherwise
 __device__ __forceinline__ uint8_t* checked_1024(uint8_t* p) {
@@ -99,11 +93,50 @@ __device__ __forceinline__ void issue_gemm1(uint32_t d_tmem, const uint8_t* q_sm
         }
 }
 
+// TMA producer shared by both kernels: the Q tile of each row block, then its key tiles
+template <int NDB, int NS, class Ctl>
+__device__ __forceinline__ void producer_loop(Ctl* ctl, uint8_t* q_smem, uint8_t* k_smem,
+                                              const CUtensorMap* tmap_q, const CUtensorMap* tmap_k,
+                                              long long t_begin, int n_tiles, int key_tiles) {
+    constexpr uint32_t kTileBytes = NDB * kBlkBytes;
+    int cur_rb = -1, seg = 0;
+    for (int i = 0; i < n_tiles; ++i) {
+        const long long t = t_begin + i;
+        const int rb = (int)(t / key_tiles), kt = (int)(t % key_tiles);
+        if (rb != cur_rb) {
+            if (cur_rb >= 0) mbar_wait(&ctl->q_empty, (seg - 1) & 1);   // GEMM1s of the old block done
+            mbar_expect_tx(&ctl->q_full, kTileBytes);
+#pragma unroll
+            for (int b = 0; b < NDB; ++b)
+                tma_load_2d(q_smem + b * kBlkBytes, tmap_q, b * 64, rb * 128, &ctl->q_full);
+            cur_rb = rb;
+            ++seg;
+        }
+        const int s = i % NS;
+        mbar_wait(&ctl->k_empty[s], ((i / NS) & 1) ^ 1);
+        mbar_expect_tx(&ctl->k_full[s], kTileBytes);
+#pragma unroll
+        for (int b = 0; b < NDB; ++b)
+            tma_load_2d(k_smem + s * kTileBytes + b * kBlkBytes, tmap_k, b * 64, kt * 128, &ctl->k_full[s]);
+    }
+}
+
 // ============================================================================ forward
+constexpr int kFwdWG = 4;                                  // epilogue groups = S buffers
+constexpr int kFwdThreads = kFwdWG * 128 + 96;             // + producer warp + two MMA-issuing warps
+// NS divides kFwdWG so the MMA loop can be unrolled by kFwdWG with compile-time stage / buffer indices
+template <int NDB> struct FwdCfg { static constexpr int NS = NDB == 4 ? 2 : 4; };
+template <int NS> struct FwdCtl {
+    uint64_t q_full, q_empty, k_full[NS], k_empty[NS], s_full[kFwdWG], s_empty[kFwdWG];
+    uint32_t tmem_base;
+    alignas(16) float xch[2][kFwdWG - 1][128];
+};
+
 template <int NDB>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kFwdThreads, 1)
 tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
-              NtxDims dm, int key_tiles, long long T, int rows_pad, float* __restrict__ partial) {
+              NtxDims dm, int key_tiles, long long T, int rows_pad, float* __restrict__ partial,
+              unsigned int* __restrict__ done_counter) {
     constexpr int NS = FwdCfg<NDB>::NS;
     constexpr uint32_t kTileBytes = NDB * kBlkBytes;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -116,12 +149,14 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     const int G = gridDim.x, cta = blockIdx.x;
     const long long t_begin = ntx_chunk_begin(T, G, cta);
     const int n_tiles = (int)(ntx_chunk_begin(T, G, cta + 1) - t_begin);
+    constexpr int kProducerWarp = kFwdWG * 4, kMmaWarp = kFwdWG * 4 + 1;   // MMA warps: kMmaWarp, kMmaWarp + 1
 
     if (threadIdx.x == 0) {
+        if (cta == 0) *done_counter = 0;                   // ticket of the finalize kernel
         mbar_init(&ctl->q_full, 1);
-        mbar_init(&ctl->q_empty, 1);
+        mbar_init(&ctl->q_empty, 2);                       // both MMA warps release the Q tile
         for (int s = 0; s < NS; ++s) { mbar_init(&ctl->k_full[s], 1); mbar_init(&ctl->k_empty[s], 1); }
-        for (int b = 0; b < 4; ++b) { mbar_init(&ctl->s_full[b], 1); mbar_init(&ctl->s_empty[b], 4); }
+        for (int b = 0; b < kFwdWG; ++b) { mbar_init(&ctl->s_full[b], 1); mbar_init(&ctl->s_empty[b], 4); }
         fence_barrier_init();
     }
     if (warp == kMmaWarp) tmem_alloc(&ctl->tmem_base, kTmemCols);
@@ -129,71 +164,84 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem_base = ctl->tmem_base;
+    // the whole TMEM (512 columns) is ours, so the allocation starts at column 0, lane 0;
+    // using the literal keeps every TMEM address a compile-time constant
+    if (ctl->tmem_base != 0) {
+        if (threadIdx.x == 0) printf("ntxent: unexpected TMEM base %u\n", ctl->tmem_base);
+        __trap();
+    }
+    constexpr uint32_t tmem_base = 0;
 
     if (warp == kProducerWarp) {
-        if (lane == 0) {
-            int cur_rb = -1, seg = 0;
-            for (int i = 0; i < n_tiles; ++i) {
-                const long long t = t_begin + i;
-                const int rb = (int)(t / key_tiles), kt = (int)(t % key_tiles);
-                if (rb != cur_rb) {
-                    if (cur_rb >= 0) mbar_wait(&ctl->q_empty, (seg - 1) & 1);
-                    mbar_expect_tx(&ctl->q_full, kTileBytes);
+        if (elect_one())
+            producer_loop<NDB, NS>(ctl, q_smem, k_smem, &tmap_q, &tmap_k, t_begin, n_tiles, key_tiles);
+    } else if (warp >= kMmaWarp) {
+        // Two issuing warps take alternate tiles: tcgen05.mma issue blocks while the tensor pipe's
+        // short queue is full, so one warp's barrier waits (~150-200 cycles each, even when the
+        // phase is already complete) run while the other warp's MMAs execute.
+        // Unrolled by kFwdWG: stage and buffer indices are compile-time constants, so every
+        // descriptor is a uniform value and tcgen05.mma issues back to back.
+        const int m = warp - kMmaWarp;
+        int rb = (int)(t_begin / key_tiles), kt = (int)(t_begin % key_tiles), seg = 0;
+        bool new_seg = true;
+        NTX_T(tm_k); NTX_T(tm_s); NTX_T(tm_issue); NTX_T(tm_total);
+        NTX_TIC(tm_total);
+        for (int i0 = 0; i0 < n_tiles; i0 += kFwdWG) {
+            const uint32_t ph_k = (uint32_t)(i0 / NS), ph_s = (uint32_t)(i0 / kFwdWG);
 #pragma unroll
-                    for (int b = 0; b < NDB; ++b)
-                        tma_load_2d(q_smem + b * kBlkBytes, &tmap_q, b * 64, rb * 128, &ctl->q_full);
-                    cur_rb = rb;
-                    ++seg;
+            for (int j = 0; j < kFwdWG; ++j) {
+                const int i = i0 + j;
+                if (i >= n_tiles) break;
+                const int s = j % NS, buf = j;
+                const bool last_of_seg = (i + 1 == n_tiles) || (kt + 1 == key_tiles);
+                if ((j & 1) == m) {
+                    if (new_seg) mbar_wait(&ctl->q_full, seg & 1);
+                    new_seg = false;
+                    { NTX_TIC(tm_k); mbar_wait(&ctl->k_full[s], (ph_k + j / NS) & 1); NTX_TOC(tm_k); }
+                    { NTX_TIC(tm_s); mbar_wait(&ctl->s_empty[buf], (ph_s & 1) ^ 1); NTX_TOC(tm_s); }
+                    tc_fence_after();
+                    NTX_TIC(tm_issue);
+                    if (elect_one()) {
+                        issue_gemm1<NDB>(tmem_base + buf * 128, q_smem, k_smem + s * kTileBytes);
+                        mma_commit(&ctl->k_empty[s]);
+                        mma_commit(&ctl->s_full[buf]);
+                    }
+                    __syncwarp();
+                    NTX_TOC(tm_issue);
                 }
-                const int s = i % NS;
-                mbar_wait(&ctl->k_empty[s], ((i / NS) & 1) ^ 1);
-                mbar_expect_tx(&ctl->k_full[s], kTileBytes);
-#pragma unroll
-                for (int b = 0; b < NDB; ++b)
-                    tma_load_2d(k_smem + s * kTileBytes + b * kBlkBytes, &tmap_k, b * 64, kt * 128,
-                                &ctl->k_full[s]);
+                if (last_of_seg) {
+                    // both warps release Q: every GEMM1 this warp issued for the row block is done
+                    if (elect_one()) mma_commit(&ctl->q_empty);
+                    __syncwarp();
+                    ++seg;
+                    new_seg = true;
+                }
+                if (++kt == key_tiles) { kt = 0; ++rb; }
             }
         }
-    } else if (warp == kMmaWarp) {
-        int cur_rb = -1, seg = -1;
-        for (int i = 0; i < n_tiles; ++i) {
-            const long long t = t_begin + i;
-            const int rb = (int)(t / key_tiles);
-            if (rb != cur_rb) {
-                ++seg;
-                mbar_wait(&ctl->q_full, seg & 1);
-                cur_rb = rb;
-            }
-            const int s = i % NS, buf = i & 3;
-            mbar_wait(&ctl->k_full[s], (i / NS) & 1);
-            mbar_wait(&ctl->s_empty[buf], ((i >> 2) & 1) ^ 1);
-            tc_fence_after();
-            if (lane == 0) {
-                issue_gemm1<NDB>(tmem_base + buf * 128, q_smem, k_smem + s * kTileBytes);
-                mma_commit(&ctl->k_empty[s]);
-                mma_commit(&ctl->s_full[buf]);
-                const bool last_of_seg = (i + 1 == n_tiles) || ((int)((t + 1) / key_tiles) != rb);
-                if (last_of_seg) mma_commit(&ctl->q_empty);
-            }
-            __syncwarp();
-        }
+        NTX_TOC(tm_total);
+        if (lane == 0 && m == 0) { NTX_TSAVE(0, tm_total); NTX_TSAVE(1, tm_k); NTX_TSAVE(2, tm_s); NTX_TSAVE(3, tm_issue); }
+        (void)rb;
     } else {
         // ---------------------------------------------------------------- epilogue groups
         const int g = warp >> 2;
         const int row_in_tile = (warp & 3) * 32 + lane;
-        const uint32_t t_lane = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
+        const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + g * 128;
         const float c1 = dm.c1, nc1 = -dm.c1;
         float acc[4] = {0.f, 0.f, 0.f, 0.f};
         int cur_rb = -1, flushes = 0;
+        NTX_T(te_wait); NTX_T(te_total); NTX_T(te_ld);
+        NTX_TIC(te_total);
 
+        // row sums of the groups are added in group order: deterministic
         auto flush = [&](int rb) {
             float rs = (acc[0] + acc[1]) + (acc[2] + acc[3]);
-            float* x = ctl->xch[flushes & 1];
-            if (g == 1) x[row_in_tile] = rs;
-            named_bar_sync(1, 256);
+            float (*x)[128] = ctl->xch[flushes & 1];
+            if (g > 0) x[g - 1][row_in_tile] = rs;
+            named_bar_sync(1, kFwdWG * 128);
             if (g == 0) {
-                rs += x[row_in_tile];
+#pragma unroll
+                for (int o = 0; o < kFwdWG - 1; ++o) rs += x[o][row_in_tile];
                 const int slot = cta - ntx_first_owner(T, G, key_tiles, rb);
                 partial[(size_t)slot * rows_pad + rb * 128 + row_in_tile] = rs;
             }
@@ -208,11 +256,9 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
                 if (cur_rb >= 0) flush(cur_rb);
                 cur_rb = rb;
             }
-            if ((i & 1) != g) continue;
-            const int buf = i & 3;
-            mbar_wait(&ctl->s_full[buf], (i >> 2) & 1);
+            if (i % kFwdWG != g) continue;
+            { NTX_TIC(te_wait); mbar_wait(&ctl->s_full[g], (i / kFwdWG) & 1); NTX_TOC(te_wait); }
             tc_fence_after();
-            const uint32_t taddr = t_lane + buf * 128;
             const bool edge = edge_tile(rb, kt, dm);
             const int self = ntx_self_col(rb * 128 + row_in_tile, dm.n_local, dm.rank);
             uint32_t v[2][32];
@@ -225,7 +271,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
                 } else {   // the whole tile is in registers: hand the TMEM buffer back
                     tc_fence_before();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(&ctl->s_empty[buf]);
+                    if (lane == 0) mbar_arrive(&ctl->s_empty[g]);
                 }
                 if (!edge) {
 #pragma unroll
@@ -243,6 +289,8 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
             }
         }
         if (cur_rb >= 0) flush(cur_rb);
+        NTX_TOC(te_total);
+        if (threadIdx.x == 0) { NTX_TSAVE(4, te_total); NTX_TSAVE(5, te_wait); }
     }
 
     tc_fence_before();
@@ -251,41 +299,89 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
 }
 
 // ============================================================================ backward
+// NDB = 1, 2 (d_pad 64, 128): dZ in TMEM columns [0, 128), three S/C buffers, three groups.
+// NDB = 4       (d_pad 256) : dZ in TMEM columns [0, 256), two S/C buffers, two groups.
+template <int NDB> struct BwdCfg {
+    static constexpr int NWG = NDB == 4 ? 2 : 3;           // epilogue groups = S/C buffers
+    static constexpr int NS = NDB == 4 ? 2 : 6;            // multiple of NWG: the MMA loop unrolls by NS
+    static constexpr int DP = NDB * 64;                    // dZ columns
+    static constexpr uint32_t kSCol = NDB == 4 ? 256 : 128;
+    static constexpr int kThreads = NWG * 128 + 96;        // + producer warp + GEMM1 warp + GEMM2 warp
+};
+template <int NS, int NWG> struct BwdCtl {
+    uint64_t q_full, q_empty, k_full[NS], k_empty[NS], s_full[NWG], c_full[NWG], buf_free[NWG], dz_full,
+        dz_empty;
+    uint32_t tmem_base;
+    alignas(16) float beta[NWG][128];
+};
+
+struct BwdWeights {
+    const float* rowsum_q;
+    const float* rowsum_k;
+    const float* w_q;
+    const float* w_k;
+    int w_stride;       // 0: one weight for every row, 1: one per row
+    float w_scale;
+};
+
+// 32 similarity values of one row -> 32 coefficients, packed bf16x2
+template <bool kEdge>
+__device__ __forceinline__ void coef_chunk(const uint32_t (&v)[32], uint32_t (&pk)[16], const float* bt,
+                                           float alpha, float c1, float nc1, int col0, int self, int k_rows,
+                                           bool row_ok) {
+#pragma unroll
+    for (int j4 = 0; j4 < 8; ++j4) {
+        const float4 b = *reinterpret_cast<const float4*>(bt + j4 * 4);
+        const float bb[4] = {b.x, b.y, b.z, b.w};
+        float cv[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float e = ex2(fmaf(__uint_as_float(v[j4 * 4 + j]), c1, nc1));
+            cv[j] = e * (alpha + bb[j]);
+            if (kEdge) {
+                const int col = col0 + j4 * 4 + j;
+                if (col == self || col >= k_rows || !row_ok) cv[j] = 0.f;
+            }
+        }
+        __nv_bfloat162 h0 = __floats2bfloat162_rn(cv[0], cv[1]);
+        __nv_bfloat162 h1 = __floats2bfloat162_rn(cv[2], cv[3]);
+        pk[j4 * 2] = *reinterpret_cast<uint32_t*>(&h0);
+        pk[j4 * 2 + 1] = *reinterpret_cast<uint32_t*>(&h1);
+    }
+}
+
 template <int NDB>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(BwdCfg<NDB>::kThreads, 1)
 tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
-              NtxDims dm, int key_tiles, long long T, int rows_pad, const float* __restrict__ coef_q,
-              const float* __restrict__ coef_k, float* __restrict__ partial, uint32_t b2_lbo,
-              uint32_t b2_sbo) {
-    constexpr int NS = BwdCfg<NDB>::NS, NP = BwdCfg<NDB>::NP;
-    constexpr int DP = NDB * 64;                      // dZ columns (fp32) held in TMEM [0, DP)
-    constexpr uint32_t kSCol = 256;                   // S buffers at TMEM columns 256 and 384
+              NtxDims dm, int key_tiles, long long T, int rows_pad, BwdWeights wt,
+              float* __restrict__ partial) {
+    using Cfg = BwdCfg<NDB>;
+    constexpr int NS = Cfg::NS, NWG = Cfg::NWG, DP = Cfg::DP;
+    constexpr uint32_t kSCol = Cfg::kSCol;
     constexpr uint32_t kTileBytes = NDB * kBlkBytes;
-    constexpr uint32_t kPBytes = 2 * kBlkBytes;       // [128 rows x 128 keys] bf16
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = checked_1024(smem_raw);
     uint8_t* q_smem = smem;
     uint8_t* k_smem = smem + kTileBytes;
-    uint8_t* p_smem = k_smem + NS * kTileBytes;
-    BwdCtl<NS>* ctl = reinterpret_cast<BwdCtl<NS>*>(p_smem + NP * kPBytes);
+    BwdCtl<NS, NWG>* ctl = reinterpret_cast<BwdCtl<NS, NWG>*>(k_smem + NS * kTileBytes);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int G = gridDim.x, cta = blockIdx.x;
     const long long t_begin = ntx_chunk_begin(T, G, cta);
     const int n_tiles = (int)(ntx_chunk_begin(T, G, cta + 1) - t_begin);
+    constexpr int kProducerWarp = NWG * 4, kMmaWarp = NWG * 4 + 1;
 
     if (threadIdx.x == 0) {
         mbar_init(&ctl->q_full, 1);
         mbar_init(&ctl->q_empty, 1);
         for (int s = 0; s < NS; ++s) { mbar_init(&ctl->k_full[s], 1); mbar_init(&ctl->k_empty[s], 1); }
-        for (int b = 0; b < 2; ++b) {
+        for (int b = 0; b < NWG; ++b) {
             mbar_init(&ctl->s_full[b], 1);
-            mbar_init(&ctl->s_empty[b], 4);
-            mbar_init(&ctl->p_full[b], 4);
-            mbar_init(&ctl->p_empty[b], 1);
+            mbar_init(&ctl->c_full[b], 4);
+            mbar_init(&ctl->buf_free[b], 1);
         }
         mbar_init(&ctl->dz_full, 1);
-        mbar_init(&ctl->dz_empty, 8);
+        mbar_init(&ctl->dz_empty, NWG * 4);
         fence_barrier_init();
     }
     if (warp == kMmaWarp) tmem_alloc(&ctl->tmem_base, kTmemCols);
@@ -293,110 +389,115 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem_base = ctl->tmem_base;
+    // the whole TMEM (512 columns) is ours, so the allocation starts at column 0, lane 0;
+    // using the literal keeps every TMEM address a compile-time constant
+    if (ctl->tmem_base != 0) {
+        if (threadIdx.x == 0) printf("ntxent: unexpected TMEM base %u\n", ctl->tmem_base);
+        __trap();
+    }
+    constexpr uint32_t tmem_base = 0;
 
     if (warp == kProducerWarp) {
-        if (lane == 0) {
-            int cur_rb = -1, seg = 0;
-            for (int i = 0; i < n_tiles; ++i) {
-                const long long t = t_begin + i;
-                const int rb = (int)(t / key_tiles), kt = (int)(t % key_tiles);
-                if (rb != cur_rb) {
-                    if (cur_rb >= 0) mbar_wait(&ctl->q_empty, (seg - 1) & 1);
-                    mbar_expect_tx(&ctl->q_full, kTileBytes);
-#pragma unroll
-                    for (int b = 0; b < NDB; ++b)
-                        tma_load_2d(q_smem + b * kBlkBytes, &tmap_q, b * 64, rb * 128, &ctl->q_full);
-                    cur_rb = rb;
-                    ++seg;
-                }
-                const int s = i % NS;
-                mbar_wait(&ctl->k_empty[s], ((i / NS) & 1) ^ 1);
-                mbar_expect_tx(&ctl->k_full[s], kTileBytes);
-#pragma unroll
-                for (int b = 0; b < NDB; ++b)
-                    tma_load_2d(k_smem + s * kTileBytes + b * kBlkBytes, &tmap_k, b * 64, kt * 128,
-                                &ctl->k_full[s]);
-            }
-        }
+        if (elect_one())
+            producer_loop<NDB, NS>(ctl, q_smem, k_smem, &tmap_q, &tmap_k, t_begin, n_tiles, key_tiles);
     } else if (warp == kMmaWarp) {
-        constexpr uint32_t idesc2 = instr_desc_bf16(128, DP, 1);
-        int seg2 = -1;
-        // dZ += C(tile j) . K(tile j): 8 MMAs of K = 16 keys, N = DP features
-        auto gemm2 = [&](int j) {
-            const long long tj = t_begin + j;
-            const int rbj = (int)(tj / key_tiles);
-            const bool first_of_seg = (j == 0) || ((int)((tj - 1) / key_tiles) != rbj);
-            const bool last_of_seg = (j + 1 == n_tiles) || ((int)((tj + 1) / key_tiles) != rbj);
-            if (first_of_seg) {
-                ++seg2;
-                mbar_wait(&ctl->dz_empty, (seg2 & 1) ^ 1);   // previous row block drained
-            }
-            const int pb = j % NP, sj = j % NS;
-            mbar_wait(&ctl->p_full[pb], (j / NP) & 1);
-            tc_fence_after();
-            if (lane == 0) {
-                const uint8_t* p_tile = p_smem + pb * kPBytes;
-                const uint8_t* k_tile = k_smem + sj * kTileBytes;
+        // GEMM1 issuer: S(i) = Q . K(i)^T as soon as the key tile has landed and S/C buffer i % NWG
+        // is free again.  Unrolled by NS (a multiple of NWG): stage / buffer indices are compile-time
+        // constants, so descriptors and TMEM addresses are uniform values.
+        int kt = (int)(t_begin % key_tiles), seg = 0;
+        bool new_seg = true;
+        NTX_T(tm_k); NTX_T(tm_free); NTX_T(tm_issue); NTX_T(tm_total);
+        NTX_TIC(tm_total);
+        for (int i0 = 0; i0 < n_tiles; i0 += NS) {
 #pragma unroll
-                for (int kk = 0; kk < 8; ++kk) {
-                    const uint64_t a = smem_desc_sw128(
-                        smem_u32(p_tile + (kk >> 2) * kBlkBytes + (kk & 3) * 32), 16, 1024);
-                    const uint64_t bd = smem_desc_sw128(smem_u32(k_tile + kk * 2048), b2_lbo, b2_sbo);
-                    mma_bf16_ss(tmem_base, a, bd, idesc2, (first_of_seg && kk == 0) ? 0u : 1u);
+            for (int jj = 0; jj < NS; ++jj) {
+                const int i = i0 + jj;
+                if (i >= n_tiles) break;
+                const int s = jj, sb = jj % NWG;
+                const bool last_of_seg = (i + 1 == n_tiles) || (kt + 1 == key_tiles);
+                if (new_seg) mbar_wait(&ctl->q_full, seg & 1);
+                new_seg = false;
+                { NTX_TIC(tm_k); mbar_wait(&ctl->k_full[s], (i0 / NS) & 1); NTX_TOC(tm_k); }
+                { NTX_TIC(tm_free); mbar_wait(&ctl->buf_free[sb], ((i / NWG) & 1) ^ 1); NTX_TOC(tm_free); }
+                tc_fence_after();
+                NTX_TIC(tm_issue);
+                if (elect_one()) {
+                    issue_gemm1<NDB>(tmem_base + kSCol + sb * 128, q_smem, k_smem + s * kTileBytes);
+                    mma_commit(&ctl->s_full[sb]);
+                    if (last_of_seg) mma_commit(&ctl->q_empty);
                 }
-                mma_commit(&ctl->k_empty[sj]);
-                mma_commit(&ctl->p_empty[pb]);
-                if (last_of_seg) mma_commit(&ctl->dz_full);
+                __syncwarp();
+                NTX_TOC(tm_issue);
+                if (last_of_seg) { ++seg; new_seg = true; }
+                if (++kt == key_tiles) kt = 0;
             }
-            __syncwarp();
-        };
-
-        int cur_rb = -1, seg = -1;
-        for (int i = 0; i < n_tiles; ++i) {
-            const long long t = t_begin + i;
-            const int rb = (int)(t / key_tiles);
-            if (rb != cur_rb) {
-                ++seg;
-                mbar_wait(&ctl->q_full, seg & 1);
-                cur_rb = rb;
-            }
-            const int s = i % NS, sb = i & 1;
-            mbar_wait(&ctl->k_full[s], (i / NS) & 1);
-            mbar_wait(&ctl->s_empty[sb], ((i >> 1) & 1) ^ 1);
-            tc_fence_after();
-            if (lane == 0) {
-                issue_gemm1<NDB>(tmem_base + kSCol + sb * 128, q_smem, k_smem + s * kTileBytes);
-                mma_commit(&ctl->s_full[sb]);
-                const bool last_of_seg = (i + 1 == n_tiles) || ((int)((t + 1) / key_tiles) != rb);
-                if (last_of_seg) mma_commit(&ctl->q_empty);
-            }
-            __syncwarp();
-            if (i > 0) gemm2(i - 1);
         }
-        if (n_tiles > 0) gemm2(n_tiles - 1);
+        NTX_TOC(tm_total);
+        if (lane == 0) { NTX_TSAVE(8, tm_total); NTX_TSAVE(9, tm_k); NTX_TSAVE(10, tm_free); NTX_TSAVE(12, tm_issue); }
+    } else if (warp == kMmaWarp + 1) {
+        // GEMM2 issuer: dZ += C(j) . K(j) once the epilogue group has written C(j) into TMEM.
+        // C is read from TMEM (bf16, 8 columns per 16 keys), K MN-major from the same smem tile.
+        // A second issuing warp keeps the tensor pipe fed while the GEMM1 warp sits in its waits.
+        constexpr uint32_t idesc2 = instr_desc_bf16(128, DP, 1);
+        int kt = (int)(t_begin % key_tiles), seg = 0;
+        bool first_of_seg = true;
+        NTX_T(tm_c); NTX_T(tm_issue);
+        for (int j0 = 0; j0 < n_tiles; j0 += NS) {
+#pragma unroll
+            for (int jj = 0; jj < NS; ++jj) {
+                const int j = j0 + jj;
+                if (j >= n_tiles) break;
+                const int sj = jj, cb = jj % NWG;
+                const bool last_of_seg = (j + 1 == n_tiles) || (kt + 1 == key_tiles);
+                if (first_of_seg) mbar_wait(&ctl->dz_empty, (seg & 1) ^ 1);   // previous row block drained
+                { NTX_TIC(tm_c); mbar_wait(&ctl->c_full[cb], (j / NWG) & 1); NTX_TOC(tm_c); }
+                tc_fence_after();
+                NTX_TIC(tm_issue);
+                if (elect_one()) {
+                    const uint32_t c_tmem = tmem_base + kSCol + cb * 128;
+                    const uint8_t* k_tile = k_smem + sj * kTileBytes;
+#pragma unroll
+                    for (int kk = 0; kk < 8; ++kk) {
+                        // MN-major key tile: next 64 features one 16 KB block away, 8-key groups 1 KB apart
+                        const uint64_t bd = smem_desc_sw128(smem_u32(k_tile + kk * 2048), kBlkBytes, 1024);
+                        mma_bf16_ts(tmem_base, c_tmem + kk * 8, bd, idesc2, (first_of_seg && kk == 0) ? 0u : 1u);
+                    }
+                    mma_commit(&ctl->k_empty[sj]);
+                    mma_commit(&ctl->buf_free[cb]);
+                    if (last_of_seg) mma_commit(&ctl->dz_full);
+                }
+                __syncwarp();
+                NTX_TOC(tm_issue);
+                first_of_seg = last_of_seg;
+                if (last_of_seg) ++seg;
+                if (++kt == key_tiles) kt = 0;
+            }
+        }
+        if (lane == 0) { NTX_TSAVE(11, tm_c); NTX_TSAVE(15, tm_issue); }
     } else {
         // ---------------------------------------------------------------- epilogue groups
         const int g = warp >> 2;
         const int tid_g = threadIdx.x & 127;
         const int row_in_tile = (warp & 3) * 32 + lane;
         const uint32_t t_lane = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
+        const uint32_t taddr = t_lane + kSCol + g * 128;
         const float c1 = dm.c1, nc1 = -dm.c1;
-        const uint32_t sw = (uint32_t)(row_in_tile & 7);
-        int cur_rb = -1, seg = -1, mine = 0;
+        int cur_rb = -1, seg = -1;
         float alpha = 0.f;
         bool row_ok = false;
+        NTX_T(te_wait); NTX_T(te_total); NTX_T(te_drain);
+        NTX_TIC(te_total);
 
-        // move this group's half of the dZ accumulator to its scratch slot
+        // move this group's 32-column chunks of the dZ accumulator to the scratch slot
         auto drain = [&](int rb, int sg) {
             mbar_wait(&ctl->dz_full, sg & 1);
             tc_fence_after();
             const int slot = cta - ntx_first_owner(T, G, key_tiles, rb);
-            float* dst = partial + ((size_t)slot * rows_pad + rb * 128 + row_in_tile) * DP + g * (DP / 2);
-#pragma unroll
-            for (int c = 0; c < DP / 2; c += 32) {
+            float* dst = partial + ((size_t)slot * rows_pad + rb * 128 + row_in_tile) * DP;
+#pragma unroll 1
+            for (int c = g * 32; c < DP; c += NWG * 32) {
                 uint32_t v[32];
-                tmem_ld_32x32(t_lane + g * (DP / 2) + c, v);
+                tmem_ld_32x32(t_lane + c, v);
                 tmem_ld_wait_dep(v);
 #pragma unroll
                 for (int j = 0; j < 32; j += 4)
@@ -416,73 +517,48 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
                 ++seg;
                 const int row = rb * 128 + row_in_tile;
                 row_ok = row < dm.q_rows;
-                alpha = row_ok ? __ldg(coef_q + row) : 0.f;
+                alpha = row_ok ? __ldg(wt.w_q + (size_t)row * wt.w_stride) * wt.w_scale / __ldg(wt.rowsum_q + row)
+                               : 0.f;
             }
-            if ((i & 1) != g) continue;
+            if (i % NWG != g) continue;
 
-            float* bt = ctl->beta[g][mine & 1];
+            // w_c / R_c of this tile's 128 keys -> smem (one buffer per group, fenced on both sides)
+            float* bt = ctl->beta[g];
             {
                 const int c = kt * 128 + tid_g;
-                bt[tid_g] = c < dm.k_rows ? __ldg(coef_k + c) : 0.f;
+                const float b = c < dm.k_rows
+                                    ? __ldg(wt.w_k + (size_t)c * wt.w_stride) * wt.w_scale / __ldg(wt.rowsum_k + c)
+                                    : 0.f;
+                named_bar_sync(2 + g, 128);          // everyone is done with the previous tile's values
+                bt[tid_g] = b;
             }
-            ++mine;
             named_bar_sync(2 + g, 128);
 
-            const int sb = i & 1, pb = i % NP;
-            mbar_wait(&ctl->s_full[sb], (i >> 1) & 1);
+            { NTX_TIC(te_wait); mbar_wait(&ctl->s_full[g], (i / NWG) & 1); NTX_TOC(te_wait); }
             tc_fence_after();
-            mbar_wait(&ctl->p_empty[pb], ((i / NP) & 1) ^ 1);   // GEMM2 that read this P buffer is done
-
-            const uint32_t taddr = t_lane + kSCol + sb * 128;
             const bool edge = edge_tile(rb, kt, dm) || (rb * 128 + 128 > dm.q_rows);
             const int self = ntx_self_col(rb * 128 + row_in_tile, dm.n_local, dm.rank);
-            uint8_t* p_row = p_smem + pb * kPBytes + row_in_tile * 128;
-            uint32_t v[2][32];
-            tmem_ld_32x32(taddr, v[0]);
-#pragma unroll
+#pragma unroll 1
             for (int ch = 0; ch < 4; ++ch) {
-                tmem_ld_wait_dep(v[ch & 1]);
-                if (ch < 3) {
-                    tmem_ld_32x32(taddr + (ch + 1) * 32, v[(ch + 1) & 1]);
-                } else {
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&ctl->s_empty[sb]);
-                }
-#pragma unroll
-                for (int j8 = 0; j8 < 4; ++j8) {           // 8 keys -> one 16-byte swizzled chunk
-                    uint32_t packed[4];
-                    const float4 b0 = *reinterpret_cast<const float4*>(bt + ch * 32 + j8 * 8);
-                    const float4 b1 = *reinterpret_cast<const float4*>(bt + ch * 32 + j8 * 8 + 4);
-                    const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-                    float cv[8];
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        const float e = ex2(fmaf(__uint_as_float(v[ch & 1][j8 * 8 + j]), c1, nc1));
-                        cv[j] = e * (alpha + bb[j]);
-                    }
-                    if (edge) {
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const int col = kt * 128 + ch * 32 + j8 * 8 + j;
-                            if (col == self || col >= dm.k_rows || !row_ok) cv[j] = 0.f;
-                        }
-                    }
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        __nv_bfloat162 h = __floats2bfloat162_rn(cv[2 * j], cv[2 * j + 1]);
-                        packed[j] = *reinterpret_cast<uint32_t*>(&h);
-                    }
-                    const int cg = ch * 4 + j8;             // 16-byte chunk index along the 128 keys
-                    uint8_t* dst = p_row + (cg >> 3) * kBlkBytes + ((((uint32_t)cg & 7u) ^ sw) << 4);
-                    *reinterpret_cast<uint4*>(dst) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
-                }
+                uint32_t v[32], pk[16];
+                tmem_ld_32x32(taddr + ch * 32, v);
+                tmem_ld_wait_dep(v);
+                if (!edge)
+                    coef_chunk<false>(v, pk, bt + ch * 32, alpha, c1, nc1, 0, 0, 0, true);
+                else
+                    coef_chunk<true>(v, pk, bt + ch * 32, alpha, c1, nc1, kt * 128 + ch * 32, self, dm.k_rows,
+                                     row_ok);
+                // bf16 pairs over fp32 columns that were already read: keys [32ch, 32ch+32) -> columns [16ch, +16)
+                tmem_st_32x16(taddr + ch * 16, pk);
             }
-            fence_proxy_async_smem();      // generic-proxy stores -> visible to tcgen05.mma
+            tmem_st_wait();
+            tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&ctl->p_full[pb]);
+            if (lane == 0) mbar_arrive(&ctl->c_full[g]);
         }
         if (cur_rb >= 0) drain(cur_rb, seg);
+        NTX_TOC(te_total);
+        if (threadIdx.x == 0) { NTX_TSAVE(13, te_total); NTX_TSAVE(14, te_wait); }
     }
 
     tc_fence_before();
@@ -535,67 +611,68 @@ template <int NDB> size_t fwd_smem_bytes() {
     return (size_t)(1 + FwdCfg<NDB>::NS) * NDB * kBlkBytes + sizeof(FwdCtl<FwdCfg<NDB>::NS>);
 }
 template <int NDB> size_t bwd_smem_bytes() {
-    return (size_t)(1 + BwdCfg<NDB>::NS) * NDB * kBlkBytes + (size_t)BwdCfg<NDB>::NP * 2 * kBlkBytes +
-           sizeof(BwdCtl<BwdCfg<NDB>::NS>);
+    return (size_t)(1 + BwdCfg<NDB>::NS) * NDB * kBlkBytes + sizeof(BwdCtl<BwdCfg<NDB>::NS, BwdCfg<NDB>::NWG>);
 }
 
 template <int NDB>
 int launch_fwd(const CUtensorMap& mq, const CUtensorMap& mk, const NtxDims& dm, const NtxPlan& plan,
-               float* partial, cudaStream_t st) {
+               float* partial, unsigned int* counter, cudaStream_t st) {
     const size_t smem = fwd_smem_bytes<NDB>();
     NTX_CUDA(cudaFuncSetAttribute(tc_fwd_kernel<NDB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const long long T = (long long)plan.row_blocks * plan.key_tiles;
-    tc_fwd_kernel<NDB><<<plan.grid, kThreads, smem, st>>>(mq, mk, dm, plan.key_tiles, T,
-                                                           plan.row_blocks * plan.tile_rows, partial);
+    tc_fwd_kernel<NDB><<<plan.grid, kFwdThreads, smem, st>>>(mq, mk, dm, plan.key_tiles, T,
+                                                              plan.row_blocks * plan.tile_rows, partial,
+                                                              counter);
     NTX_CUDA(cudaGetLastError());
     return NTX_OK;
 }
 
 template <int NDB>
 int launch_bwd(const CUtensorMap& mq, const CUtensorMap& mk, const NtxDims& dm, const NtxPlan& plan,
-               const float* coef_q, const float* coef_k, float* partial, cudaStream_t st) {
+               const BwdWeights& wt, float* partial, cudaStream_t st) {
     const size_t smem = bwd_smem_bytes<NDB>();
     NTX_CUDA(cudaFuncSetAttribute(tc_bwd_kernel<NDB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const long long T = (long long)plan.row_blocks * plan.key_tiles;
-    // MN-major key-tile descriptor: next 64 features one 16 KB block away, 8-key groups 1 KB apart.
-    uint32_t lbo = kBlkBytes, sbo = 1024;
-    if (const char* e = getenv("NTX_DEBUG_B2_LBO")) lbo = (uint32_t)atoi(e);   // bring-up only
-    if (const char* e = getenv("NTX_DEBUG_B2_SBO")) sbo = (uint32_t)atoi(e);
-    tc_bwd_kernel<NDB><<<plan.grid, kThreads, smem, st>>>(mq, mk, dm, plan.key_tiles, T,
-                                                           plan.row_blocks * plan.tile_rows, coef_q,
-                                                           coef_k, partial, lbo, sbo);
+    tc_bwd_kernel<NDB><<<plan.grid, BwdCfg<NDB>::kThreads, smem, st>>>(
+        mq, mk, dm, plan.key_tiles, T, plan.row_blocks * plan.tile_rows, wt, partial);
     NTX_CUDA(cudaGetLastError());
     return NTX_OK;
 }
 
 }  // namespace
 
+#ifdef NTX_TIMING
+extern "C" int ntx_debug_timers(long long* host_out) {   // 148 x 16 cycle counters
+    return cudaMemcpyFromSymbol(host_out, g_ntx_timers, sizeof(long long) * 148 * 16) == cudaSuccess ? 0 : -3;
+}
+#endif
+
 int ntx_tc_fwd_launch(const __nv_bfloat16* q, const __nv_bfloat16* k, const NtxDims& dm,
-                      const NtxPlan& plan, float* partial, cudaStream_t st) {
+                      const NtxPlan& plan, float* partial, unsigned int* counter, cudaStream_t st) {
     CUtensorMap mq, mk;
     int rc;
     if ((rc = make_rows_tmap(&mq, q, dm.q_rows, dm.ld)) || (rc = make_rows_tmap(&mk, k, dm.k_rows, dm.ld)))
         return rc;
     switch (plan.d_pad) {
-        case 64: return launch_fwd<1>(mq, mk, dm, plan, partial, st);
-        case 128: return launch_fwd<2>(mq, mk, dm, plan, partial, st);
-        case 256: return launch_fwd<4>(mq, mk, dm, plan, partial, st);
+        case 64: return launch_fwd<1>(mq, mk, dm, plan, partial, counter, st);
+        case 128: return launch_fwd<2>(mq, mk, dm, plan, partial, counter, st);
+        case 256: return launch_fwd<4>(mq, mk, dm, plan, partial, counter, st);
     }
     ntx_set_error("tensor-core forward: padded feature dim %d not built", plan.d_pad);
     return NTX_E_UNSUPPORTED;
 }
 
 int ntx_tc_bwd_launch(const __nv_bfloat16* q, const __nv_bfloat16* k, const NtxDims& dm,
-                      const NtxPlan& plan, const float* coef_q, const float* coef_k, float* partial,
-                      cudaStream_t st) {
+                      const NtxPlan& plan, const NtxWeights& w, float* partial, cudaStream_t st) {
     CUtensorMap mq, mk;
     int rc;
     if ((rc = make_rows_tmap(&mq, q, dm.q_rows, dm.ld)) || (rc = make_rows_tmap(&mk, k, dm.k_rows, dm.ld)))
         return rc;
+    BwdWeights wt{w.rowsum_q, w.rowsum_k, w.w_q, w.w_k, w.w_stride, w.w_scale};
     switch (plan.d_pad) {
-        case 64: return launch_bwd<1>(mq, mk, dm, plan, coef_q, coef_k, partial, st);
-        case 128: return launch_bwd<2>(mq, mk, dm, plan, coef_q, coef_k, partial, st);
-        case 256: return launch_bwd<4>(mq, mk, dm, plan, coef_q, coef_k, partial, st);
+        case 64: return launch_bwd<1>(mq, mk, dm, plan, wt, partial, st);
+        case 128: return launch_bwd<2>(mq, mk, dm, plan, wt, partial, st);
+        case 256: return launch_bwd<4>(mq, mk, dm, plan, wt, partial, st);
     }
     ntx_set_error("tensor-core backward: padded feature dim %d not built", plan.d_pad);
     return NTX_E_UNSUPPORTED;

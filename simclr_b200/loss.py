@@ -89,21 +89,26 @@ class NTXentFunction(torch.autograd.Function):
         dev = view0.device
         inv_norm, rowsum = stats[0], stats[1]
         g = grad_out.detach().to(torch.float32).contiguous()
-        wc = torch.empty((2, q_rows), dtype=torch.float32, device=dev)
-        w, coef = wc[0], wc[1]
-        be.bwd_prep(rowsum, g, reduction, w, coef)
+        # row weights w_r of  sum_r w_r * row_loss_r : one upstream gradient (mean / sum) or one per row (none)
+        w_stride = 1 if reduction == "none" else 0
+        w_scale = 1.0 / q_rows if reduction == "mean" else 1.0
+        w_q = g.view(-1)
         if world > 1:
-            coef_k = torch.empty(world * q_rows, dtype=torch.float32, device=dev)
-            dist.all_gather_into_tensor(coef_k, coef, group=group)        # w / rowsum of every key
+            rowsum_k = torch.empty(world * q_rows, dtype=torch.float32, device=dev)
+            dist.all_gather_into_tensor(rowsum_k, rowsum.contiguous(), group=group)
+            w_k = torch.empty(world * q_rows, dtype=torch.float32, device=dev)
+            dist.all_gather_into_tensor(w_k, w_q.expand(q_rows).contiguous(), group=group)
+            if w_stride == 0:      # ranks may hold different upstream gradients: go per row
+                w_q, w_stride = w_k[rank * q_rows:(rank + 1) * q_rows], 1
             q = keys[rank * q_rows:(rank + 1) * q_rows]
         else:
-            coef_k, q = coef, keys
+            rowsum_k, w_k, q = rowsum, w_q, keys
         dview0 = torch.empty_like(view0)
         dview1 = torch.empty_like(view1)
         plan = be.plan(q_rows, keys.shape[0], d, keys.dtype)
         ws = _workspace(dev, max(plan.fwd_ws_bytes, plan.bwd_ws_bytes))
-        be.bwd(q, keys, d, (n, world, rank), temperature, coef, coef_k, w, view0, view1, inv_norm,
-               dview0, dview1, ws)
+        be.bwd(q, keys, d, (n, world, rank), temperature, rowsum, rowsum_k, w_q, w_k, w_stride, w_scale,
+               view0, view1, inv_norm, dview0, dview1, ws)
         return dview0, dview1, None, None, None, None, None, None
 
 

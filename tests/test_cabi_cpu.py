@@ -22,7 +22,7 @@ def declared_symbols():
 def test_library_loads_and_exports_every_declared_symbol():
     lib = _cabi.load()
     names = declared_symbols()
-    assert len(names) >= 9
+    assert len(names) >= 8
     for name in names:
         assert hasattr(lib, name), f"{name} declared in include/ntxent_b200.h but not exported"
     assert set(names) == set(_cabi.EXPORTS)
@@ -71,7 +71,7 @@ def test_plan_partition_is_exact(q_rows, k_rows, d, dtype, sms):
         slots = max(slots, last - first + 1)
     assert p.max_slots == slots
     rows_pad = p.row_blocks * p.tile_rows
-    assert p.fwd_ws_bytes == slots * rows_pad * 4
+    assert p.fwd_ws_bytes == slots * rows_pad * 4 + 16      # + the finalize kernel's ticket
     assert p.bwd_ws_bytes == slots * rows_pad * p.d_pad * 4
     assert p.tensor_cores == (1 if dtype == torch.bfloat16 else 0)
 
@@ -85,8 +85,9 @@ def test_argument_errors_are_reported_without_a_device():
     # rows must be 2 * n_local
     rc = lib.ntx_fwd(16, 16, 10, 10, 8, 8, 0, ctypes.byref(lay), 0.5, 16, 16, 16, 16, 16, 64, None)
     assert rc == -1 and b"q_rows" in lib.ntx_last_error()
-    rc = lib.ntx_bwd_prep(16, 16, 7, 8, 16, 16, None)
-    assert rc == -1 and b"reduction" in lib.ntx_last_error()
+    rc = lib.ntx_bwd(16, 16, 8, 8, 8, 8, 0, ctypes.byref(lay), 0.5, 16, 16, 16, 16, 3, 1.0, 16, 16, 0, 16, 16,
+                     16, 16, 64, None)
+    assert rc == -1 and b"w_stride" in lib.ntx_last_error()
     p = _cabi.NtxPlan()
     assert lib.ntx_plan(16, 16, 512, 1, 148, ctypes.byref(p)) == -4     # bf16 rows wider than a tile
     with pytest.raises(_cabi.NtxError):

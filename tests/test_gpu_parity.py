@@ -182,22 +182,21 @@ def test_sharded_layout_one_gpu(world, dtype, tol, dev):
     keys = torch.cat(rows)                                         # what all_gather_into_tensor builds
     plan = be.plan(q_rows, keys.shape[0], d, dtype)
     ws = torch.empty(max(plan.fwd_ws_bytes, plan.bwd_ws_bytes, 16), dtype=torch.uint8, device=dev)
-    stats, coefs, ws_w = [], [], []
+    stats = []
     for k in range(world):
         st = torch.empty(3, q_rows, device=dev)
         ls = torch.empty(2, device=dev)
         be.fwd(keys[k * q_rows:(k + 1) * q_rows], keys, d, (nl, world, k), c.tau, st[0], st[1], st[2], ls, ws)
-        wc = torch.empty(2, q_rows, device=dev)
-        be.bwd_prep(st[0], torch.ones((), device=dev), "mean", wc[0], wc[1])
-        stats.append((st, ls)); coefs.append(wc[1]); ws_w.append(wc[0])
+        stats.append((st, ls))
     # mean over ranks of the per-rank mean == the reference's global mean
     assert rel_err(np.mean([float(ls[1]) for _, ls in stats]), float(c.loss)) < tol
-    coef_k = torch.cat(coefs)
+    rowsum_k = torch.cat([st[0] for st, _ in stats])              # what the all-gather of rowsum builds
+    one = torch.ones(1, device=dev)
     for k in range(world):
         a, b = views[k]
         d0, d1 = torch.empty_like(a), torch.empty_like(b)
-        be.bwd(keys[k * q_rows:(k + 1) * q_rows], keys, d, (nl, world, k), c.tau, coefs[k], coef_k, ws_w[k],
-               a, b, invs[k], d0, d1, ws)
+        be.bwd(keys[k * q_rows:(k + 1) * q_rows], keys, d, (nl, world, k), c.tau, stats[k][0][0], rowsum_k,
+               one, one, 0, 1.0 / q_rows, a, b, invs[k], d0, d1, ws)
         # each rank's loss is a mean over its own rows: grads are W x the global-mean grads; DDP divides by W
         sl = slice(k * nl, (k + 1) * nl)
         floor = grad_floor(c)

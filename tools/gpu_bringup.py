@@ -48,12 +48,11 @@ def stage(mode, n, d, tau, world=1):
     e_lse = np.abs(lse - ref["lse"]).max()
     e_pos = np.abs(stats[2].cpu().numpy() - ref["pos"]).max()
     e_loss = abs(float(loss_sum[1]) - ref["loss"].mean()) / abs(ref["loss"].mean())
-    gout = torch.ones((), device=dev)
-    wc = torch.empty(2, q_rows, device=dev)
-    be.bwd_prep(stats[1], gout, "mean", wc[0], wc[1])
+    gout = torch.ones(1, device=dev)
     d0 = torch.empty_like(a)
     d1 = torch.empty_like(b)
-    be.bwd(rows, rows, d, (n, 1, 0), tau, wc[1], wc[1], wc[0], a, b, stats[0], d0, d1, ws)
+    be.bwd(rows, rows, d, (n, 1, 0), tau, stats[1], stats[1], gout, gout, 0, 1.0 / q_rows, a, b, stats[0],
+           d0, d1, ws)
     torch.cuda.synchronize()
     scale = max(np.abs(ref["dview0"]).max(), np.abs(ref["dview1"]).max())
     e_g0 = np.abs(d0.float().cpu().numpy() - ref["dview0"]).max() / scale

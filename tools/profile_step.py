@@ -26,13 +26,12 @@ stats = torch.empty(4, q_rows, device=dev)
 loss_sum = torch.empty(2, device=dev)
 plan = be.plan(q_rows, q_rows, d, torch.bfloat16)
 ws = torch.empty(max(plan.fwd_ws_bytes, plan.bwd_ws_bytes), dtype=torch.uint8, device=dev)
-wc = torch.empty(2, q_rows, device=dev)
 g0, g1 = torch.empty_like(v0), torch.empty_like(v1)
-one = torch.ones((), device=dev)
+one = torch.ones(1, device=dev)
 for _ in range(steps):
     be.l2norm(v0, v1, rows, stats[0])
     be.fwd(rows, rows, d, (n, 1, 0), 0.5, stats[1], stats[2], stats[3], loss_sum, ws)
-    be.bwd_prep(stats[1], one, "mean", wc[0], wc[1])
-    be.bwd(rows, rows, d, (n, 1, 0), 0.5, wc[1], wc[1], wc[0], v0, v1, stats[0], g0, g1, ws)
+    be.bwd(rows, rows, d, (n, 1, 0), 0.5, stats[1], stats[1], one, one, 0, 1.0 / q_rows, v0, v1, stats[0],
+           g0, g1, ws)
 torch.cuda.synchronize()
 print("loss", float(loss_sum[1]))

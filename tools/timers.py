@@ -1,0 +1,48 @@
+"""Read the per-CTA cycle counters of the -DNTX_TIMING build after one fwd+bwd step.
+
+    NTXENT_B200_LIB=simclr_b200/libntxent_b200_timing.so python tools/timers.py [n] [d]
+"""
+import ctypes
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from simclr_b200 import _cabi  # noqa: E402
+
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 8192
+d = int(sys.argv[2]) if len(sys.argv) > 2 else 128
+dev = torch.device("cuda:0")
+be = _cabi.Backend()
+g = torch.Generator().manual_seed(7)
+v0 = torch.randn(n, d, generator=g).bfloat16().to(dev)
+v1 = torch.randn(n, d, generator=g).bfloat16().to(dev)
+q_rows = 2 * n
+ld = be.row_pitch(d, torch.bfloat16)
+rows = torch.empty(q_rows, ld, dtype=torch.bfloat16, device=dev)
+stats = torch.empty(4, q_rows, device=dev)
+loss_sum = torch.empty(2, device=dev)
+plan = be.plan(q_rows, q_rows, d, torch.bfloat16)
+ws = torch.empty(max(plan.fwd_ws_bytes, plan.bwd_ws_bytes), dtype=torch.uint8, device=dev)
+g0, g1 = torch.empty_like(v0), torch.empty_like(v1)
+one = torch.ones(1, device=dev)
+for _ in range(3):
+    be.l2norm(v0, v1, rows, stats[0])
+    be.fwd(rows, rows, d, (n, 1, 0), 0.5, stats[1], stats[2], stats[3], loss_sum, ws)
+    be.bwd(rows, rows, d, (n, 1, 0), 0.5, stats[1], stats[1], one, one, 0, 1.0 / q_rows, v0, v1, stats[0], g0, g1, ws)
+torch.cuda.synchronize()
+buf = np.zeros((148, 16), dtype=np.int64)
+rc = _cabi.load().ntx_debug_timers(buf.ctypes.data_as(ctypes.c_void_p))
+assert rc == 0
+m = buf.mean(axis=0)
+tiles = plan.row_blocks * plan.key_tiles / plan.grid
+names = ["fwd mma total", "fwd mma wait k_full", "fwd mma wait s_empty", "fwd mma issue", "fwd epi total",
+         "fwd epi wait s_full", "", "", "bwd mma total", "bwd mma wait k_full", "bwd mma wait buf_free",
+         "bwd gemm2 wait c_full", "bwd gemm1 issue", "bwd epi total", "bwd epi wait s_full", "bwd gemm2 issue"]
+print(f"tiles per CTA {tiles:.1f}")
+for name, v in zip(names, m):
+    if name:
+        print(f"{name:24s} {v:10.0f} cycles  {v / tiles:8.1f} per tile")
