@@ -136,7 +136,9 @@ int ntx_plan(int q_rows, int k_rows, int d, int dtype, int sm_count, NtxPlan* pl
     }
     plan->max_slots = max_slots;
     const uint64_t rows_pad = (uint64_t)plan->row_blocks * plan->tile_rows;
-    plan->fwd_ws_bytes = (uint64_t)max_slots * rows_pad * sizeof(float) + 16;   // + finalize ticket
+    // row-sum partials + finalize ticket + one fp64 block sum per finalize block
+    plan->fwd_ws_bytes = (uint64_t)max_slots * rows_pad * sizeof(float) + 16 +
+                         (uint64_t)ntx_fwd_finalize_blocks(q_rows, ntx_row_pitch(d, dtype)) * 8;
     plan->bwd_ws_bytes = (uint64_t)max_slots * rows_pad * plan->d_pad * sizeof(float);
     return NTX_OK;
 }
@@ -172,7 +174,9 @@ int ntx_fwd(const void* q, const void* k, int q_rows, int k_rows, int d, int ld,
     if ((rc = aligned16(workspace, "workspace"))) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     float* partial = (float*)workspace;
-    unsigned int* counter = (unsigned int*)((char*)workspace + plan.fwd_ws_bytes - 16);
+    const uint64_t partial_bytes = (uint64_t)plan.max_slots * plan.row_blocks * plan.tile_rows * sizeof(float);
+    unsigned int* counter = (unsigned int*)((char*)workspace + partial_bytes);
+    double* block_sums = (double*)((char*)workspace + partial_bytes + 16);
     {
         ProfScope prof(0, st);
         if (plan.tensor_cores)
@@ -182,8 +186,8 @@ int ntx_fwd(const void* q, const void* k, int q_rows, int k_rows, int d, int ld,
             rc = ntx_simt_fwd_launch((const float*)q, (const float*)k, dm, plan, partial, counter, st);
     }
     if (rc) return rc;
-    return ntx_fwd_finalize_launch(q, dtype, dm, plan, partial, counter, rowsum, pos_logit, row_loss,
-                                   loss_sum, st);
+    return ntx_fwd_finalize_launch(q, dtype, dm, plan, partial, counter, block_sums, rowsum, pos_logit,
+                                   row_loss, loss_sum, st);
 }
 
 int ntx_bwd(const void* q, const void* k, int q_rows, int k_rows, int d, int ld, int dtype,

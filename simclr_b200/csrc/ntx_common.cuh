@@ -97,9 +97,11 @@ int ntx_tc_fwd_launch(const __nv_bfloat16* q, const __nv_bfloat16* k, const NtxD
                       const NtxPlan& plan, float* partial, unsigned int* counter, cudaStream_t st);
 int ntx_tc_bwd_launch(const __nv_bfloat16* q, const __nv_bfloat16* k, const NtxDims& dm,
                       const NtxPlan& plan, const NtxWeights& w, float* partial, cudaStream_t st);
+int ntx_fwd_finalize_blocks(int q_rows, int ld);   // grid of the forward finalize (one fp64 block sum each)
 int ntx_fwd_finalize_launch(const void* q, int dtype, const NtxDims& dm, const NtxPlan& plan,
-                            const float* partial, unsigned int* counter, float* rowsum, float* pos_logit,
-                            float* row_loss, float* loss_sum, cudaStream_t st);
+                            const float* partial, unsigned int* counter, double* block_sums,
+                            float* rowsum, float* pos_logit, float* row_loss, float* loss_sum,
+                            cudaStream_t st);
 int ntx_debug_indices_launch(int n_local, int rank, int32_t* self_col, int32_t* pos_col,
                              cudaStream_t st);
 int ntx_bwd_finalize_launch(const NtxDims& dm, const NtxPlan& plan, const float* partial,

@@ -14,7 +14,8 @@
 
 namespace {
 
-constexpr int kThreads = 256;
+constexpr int kThreads = 512;        // backward finalize / generic kernels
+constexpr int kFwdThreads = 1024;    // forward finalize: few blocks -> few serialized tickets
 
 __device__ __forceinline__ float ldf(const float* p, size_t i) { return __ldg(p + i); }
 __device__ __forceinline__ float ldf(const __nv_bfloat16* p, size_t i) { return __bfloat162float(p[i]); }
@@ -47,13 +48,19 @@ __device__ __forceinline__ float group_sum(float v, int width) {
 // ------------------------------------------------------------------ forward finalize
 // `lanes` threads per row (power of two), each covers 4-element groups sub, sub+lanes, ...
 template <typename T>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kFwdThreads)
 fwd_finalize_kernel(const T* __restrict__ q, NtxDims dm, int lanes, int tile_rows, int key_tiles,
                     long long Tt, int G, int rows_pad, const float* __restrict__ partial,
-                    unsigned int* __restrict__ counter, float* __restrict__ rowsum,
-                    float* __restrict__ pos_logit, float* __restrict__ row_loss,
-                    float* __restrict__ loss_sum) {
-    const int rows_per_block = kThreads / lanes;
+                    unsigned int* __restrict__ counter, double* __restrict__ block_sums,
+                    float* __restrict__ rowsum, float* __restrict__ pos_logit,
+                    float* __restrict__ row_loss, float* __restrict__ loss_sum) {
+    // rows of one block share a row block (tile_rows is a multiple of rows_per_block): one slot count
+    __shared__ int ns_sh;
+    if (threadIdx.x == 0)
+        ns_sh = ntx_num_slots(Tt, G, key_tiles, (int)((long long)blockIdx.x * (kFwdThreads / lanes) / tile_rows));
+    __syncthreads();
+    double my_loss = 0.0;
+    const int rows_per_block = kFwdThreads / lanes;
     const int sub = threadIdx.x % lanes;
     const int r_raw = blockIdx.x * rows_per_block + threadIdx.x / lanes;
     const bool live = r_raw < dm.q_rows;
@@ -69,34 +76,45 @@ fwd_finalize_kernel(const T* __restrict__ q, NtxDims dm, int lanes, int tile_row
         }
         dot = group_sum(dot, lanes);
         if (sub == 0 && live) {
-            const int rb = r / tile_rows;
-            const int ns = ntx_num_slots(Tt, G, key_tiles, rb);
+            const int ns = ns_sh;
             float R = 0.f;
             for (int s = 0; s < ns; ++s) R += __ldg(partial + (size_t)s * rows_pad + r);
             const float pos = dot * dm.inv_tau;
+            const float l = logf(R) + dm.inv_tau - pos;
             rowsum[r] = R;
             pos_logit[r] = pos;
-            row_loss[r] = logf(R) + dm.inv_tau - pos;
+            row_loss[r] = l;
+            my_loss = (double)l;
         }
     }
-    // last block standing adds every row loss in index order: deterministic (loss.py:60-65)
+    // Block sums in a fixed order, then the last block standing adds the block sums in block
+    // order: deterministic whichever block finishes last (loss.py:60-65).
     __shared__ bool is_last;
-    __shared__ double part[kThreads / 32];
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) is_last = atomicAdd(counter, 1u) == gridDim.x - 1;
-    __syncthreads();
-    if (!is_last) return;
-    __threadfence();
-    double acc = 0.0;
-    for (int i = threadIdx.x; i < dm.q_rows; i += kThreads) acc += (double)__ldcg(row_loss + i);
+    __shared__ double part[kFwdThreads / 32];
+    double acc = my_loss;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
     if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = acc;
     __syncthreads();
     if (threadIdx.x == 0) {
         double v = 0.0;
-        for (int w = 0; w < kThreads / 32; ++w) v += part[w];
+        for (int w = 0; w < kFwdThreads / 32; ++w) v += part[w];
+        block_sums[blockIdx.x] = v;
+        __threadfence();
+        is_last = atomicAdd(counter, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+    acc = 0.0;
+    for (int i = threadIdx.x; i < (int)gridDim.x; i += kFwdThreads) acc += __ldcg(block_sums + i);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double v = 0.0;
+        for (int w = 0; w < kFwdThreads / 32; ++w) v += part[w];
         loss_sum[0] = (float)v;                              // reduction="sum"
         loss_sum[1] = (float)(v / (double)dm.q_rows);        // reduction="mean": sum / N * 0.5, rows = 2N
         *counter = 0;
@@ -125,13 +143,18 @@ bwd_finalize_vec_kernel(BwdFinArgs A, int lanes, const TIn* __restrict__ view0,
                         const TIn* __restrict__ view1, TIn* __restrict__ dview0, TIn* __restrict__ dview1) {
     const NtxDims& dm = A.dm;
     const int rows_per_block = kThreads / lanes;
+    // rows of one block share a row block (tile_rows is a multiple of rows_per_block): one slot count
+    __shared__ int ns_sh;
+    if (threadIdx.x == 0)
+        ns_sh = ntx_num_slots(A.Tt, A.G, A.key_tiles, (int)((long long)blockIdx.x * rows_per_block / A.tile_rows));
+    __syncthreads();
     const int sub = threadIdx.x % lanes;
     const int r_raw = blockIdx.x * rows_per_block + threadIdx.x / lanes;
     const bool live = r_raw < dm.q_rows;
     const int r = live ? r_raw : dm.q_rows - 1;              // keep every lane in the shuffles
     const int n = dm.n_local, d = dm.d;
     const int p = ntx_pos_row(r, n);
-    const int ns = ntx_num_slots(A.Tt, A.G, A.key_tiles, r / A.tile_rows);
+    const int ns = ns_sh;
     const TIn* zr = r < n ? view0 + (size_t)r * d : view1 + (size_t)(r - n) * d;
     const TIn* zp = p < n ? view0 + (size_t)p * d : view1 + (size_t)(p - n) * d;
     TIn* out = r < n ? dview0 + (size_t)r * d : dview1 + (size_t)(r - n) * d;
@@ -220,8 +243,10 @@ __global__ void debug_indices_kernel(int n_local, int rank, int32_t* __restrict_
     pos_col[r] = ntx_pos_col(r, n_local, rank);
 }
 
-int lanes_for(int groups4) {       // threads per row: power of two covering the row's float4 groups
-    int l = 1;
+// threads per row: power of two covering the row's float4 groups; at least 16 so that the
+// rows of one block (<= 1024 / 16) never straddle a 64-row tile (one slot count per block)
+int lanes_for(int groups4) {
+    int l = 16;
     while (l < groups4 && l < 32) l <<= 1;
     return l;
 }
@@ -263,21 +288,27 @@ int ntx_debug_indices_launch(int n_local, int rank, int32_t* self_col, int32_t* 
     return NTX_OK;
 }
 
+int ntx_fwd_finalize_blocks(int q_rows, int ld) {
+    const int lanes = lanes_for(ld / 4);
+    return (q_rows + kFwdThreads / lanes - 1) / (kFwdThreads / lanes);
+}
+
 int ntx_fwd_finalize_launch(const void* q, int dtype, const NtxDims& dm, const NtxPlan& plan,
-                            const float* partial, unsigned int* counter, float* rowsum, float* pos_logit,
-                            float* row_loss, float* loss_sum, cudaStream_t st) {
+                            const float* partial, unsigned int* counter, double* block_sums,
+                            float* rowsum, float* pos_logit, float* row_loss, float* loss_sum,
+                            cudaStream_t st) {
     const long long T = (long long)plan.row_blocks * plan.key_tiles;
     const int rows_pad = plan.row_blocks * plan.tile_rows;
     const int lanes = lanes_for(dm.ld / 4);
-    const int grid = (dm.q_rows + kThreads / lanes - 1) / (kThreads / lanes);
+    const int grid = ntx_fwd_finalize_blocks(dm.q_rows, dm.ld);
     if (dtype == NTX_F32)
-        fwd_finalize_kernel<float><<<grid, kThreads, 0, st>>>(
+        fwd_finalize_kernel<float><<<grid, kFwdThreads, 0, st>>>(
             (const float*)q, dm, lanes, plan.tile_rows, plan.key_tiles, T, plan.grid, rows_pad, partial,
-            counter, rowsum, pos_logit, row_loss, loss_sum);
+            counter, block_sums, rowsum, pos_logit, row_loss, loss_sum);
     else
-        fwd_finalize_kernel<__nv_bfloat16><<<grid, kThreads, 0, st>>>(
+        fwd_finalize_kernel<__nv_bfloat16><<<grid, kFwdThreads, 0, st>>>(
             (const __nv_bfloat16*)q, dm, lanes, plan.tile_rows, plan.key_tiles, T, plan.grid, rows_pad,
-            partial, counter, rowsum, pos_logit, row_loss, loss_sum);
+            partial, counter, block_sums, rowsum, pos_logit, row_loss, loss_sum);
     NTX_CUDA(cudaGetLastError());
     return NTX_OK;
 }

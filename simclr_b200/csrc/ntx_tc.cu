@@ -55,6 +55,31 @@ __device__ __forceinline__ float ex2(float x) {
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
+// exp2 on the FMA / ALU pipes for a share of the elements: MUFU.EX2 (16 per clock per SM) is the
+// unit that bounds these kernels, the FP32 pipes have slack.  x = n + f, n = round(x) taken from
+// the low mantissa bits of x + 1.5 * 2^23, 2^f by a degree-3 minimax polynomial on [-0.5, 0.5]
+// (max relative error 7.5e-5, mean 5e-6: far inside the bf16 mode's 1e-2), 2^n by adding n to
+// the exponent field.  Valid for x in (-126, 0], which the temperature floor guarantees.
+__device__ __forceinline__ float ex2_poly(float x) {
+    const float t = x + 12582912.f;
+    const float f = x - (t - 12582912.f);
+    float p = fmaf(f, 0.0551716685f, 0.242611125f);
+    p = fmaf(p, f, 0.693260968f);
+    p = fmaf(p, f, 0.999928057f);
+    return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
+}
+#ifndef NTX_FWD_POLY
+#define NTX_FWD_POLY 2      // of every 8 exponentials of the forward epilogue, how many use ex2_poly
+                            // (measured on B200, N=8192 D=128: 0 -> 86.6 us, 1 -> 81.7, 2 -> 78.3, 3 -> 81.4, 4 -> 88.1)
+#endif
+#ifndef NTX_BWD_POLY
+#define NTX_BWD_POLY 0      // same for the backward epilogue
+#endif
+template <int kPolyOf8>
+__device__ __forceinline__ float ex2_mixed(float x, int j) {
+    // spread the polynomial lanes over the 8 so both pipes stay busy: j*kPolyOf8 mod 8 < kPolyOf8
+    return ((j * kPolyOf8) & 7) < kPolyOf8 && kPolyOf8 > 0 ? ex2_poly(x) : ex2(x);
+}
 __device__ __forceinline__ void named_bar_sync(int id, int threads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
 }
@@ -229,7 +254,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + g * 128;
         const float c1 = dm.c1, nc1 = -dm.c1;
         float acc[4] = {0.f, 0.f, 0.f, 0.f};
-        int cur_rb = -1, flushes = 0;
+        int flushes = 0;
         NTX_T(te_wait); NTX_T(te_total); NTX_T(te_ld);
         NTX_TIC(te_total);
 
@@ -249,46 +274,47 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
             acc[0] = acc[1] = acc[2] = acc[3] = 0.f;
         };
 
+        int rb = (int)(t_begin / key_tiles), kt = (int)(t_begin % key_tiles);
+        int own = 0, turn = 0;
         for (int i = 0; i < n_tiles; ++i) {
-            const long long t = t_begin + i;
-            const int rb = (int)(t / key_tiles), kt = (int)(t % key_tiles);
-            if (rb != cur_rb) {
-                if (cur_rb >= 0) flush(cur_rb);
-                cur_rb = rb;
-            }
-            if (i % kFwdWG != g) continue;
-            { NTX_TIC(te_wait); mbar_wait(&ctl->s_full[g], (i / kFwdWG) & 1); NTX_TOC(te_wait); }
-            tc_fence_after();
-            const bool edge = edge_tile(rb, kt, dm);
-            const int self = ntx_self_col(rb * 128 + row_in_tile, dm.n_local, dm.rank);
-            uint32_t v[2][32];
-            tmem_ld_32x32(taddr, v[0]);
+            const bool last_of_seg = (i + 1 == n_tiles) || (kt + 1 == key_tiles);
+            if (turn == g) {
+                { NTX_TIC(te_wait); mbar_wait(&ctl->s_full[g], own & 1); NTX_TOC(te_wait); }
+                ++own;
+                tc_fence_after();
+                const bool edge = edge_tile(rb, kt, dm);
+                const int self = ntx_self_col(rb * 128 + row_in_tile, dm.n_local, dm.rank);
+                uint32_t v[2][32];
+                tmem_ld_32x32(taddr, v[0]);
 #pragma unroll
-            for (int ch = 0; ch < 4; ++ch) {
-                tmem_ld_wait_dep(v[ch & 1]);
-                if (ch < 3) {
-                    tmem_ld_32x32(taddr + (ch + 1) * 32, v[(ch + 1) & 1]);
-                } else {   // the whole tile is in registers: hand the TMEM buffer back
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&ctl->s_empty[g]);
-                }
-                if (!edge) {
+                for (int ch = 0; ch < 4; ++ch) {
+                    tmem_ld_wait_dep(v[ch & 1]);
+                    if (ch < 3) {
+                        tmem_ld_32x32(taddr + (ch + 1) * 32, v[(ch + 1) & 1]);
+                    } else {   // the whole tile is in registers: hand the TMEM buffer back
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&ctl->s_empty[g]);
+                    }
+                    if (!edge) {
 #pragma unroll
-                    for (int j = 0; j < 32; ++j)
-                        acc[j & 3] += ex2(fmaf(__uint_as_float(v[ch & 1][j]), c1, nc1));
-                } else {
+                        for (int j = 0; j < 32; ++j)
+                            acc[j & 3] += ex2_mixed<NTX_FWD_POLY>(fmaf(__uint_as_float(v[ch & 1][j]), c1, nc1), j);
+                    } else {
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        const int col = kt * 128 + ch * 32 + j;
-                        float e = ex2(fmaf(__uint_as_float(v[ch & 1][j]), c1, nc1));
-                        if (col == self || col >= dm.k_rows) e = 0.f;   // mask of loss.py:38,46-47
-                        acc[j & 3] += e;
+                        for (int j = 0; j < 32; ++j) {
+                            const int col = kt * 128 + ch * 32 + j;
+                            float e = ex2(fmaf(__uint_as_float(v[ch & 1][j]), c1, nc1));
+                            if (col == self || col >= dm.k_rows) e = 0.f;   // mask of loss.py:38,46-47
+                            acc[j & 3] += e;
+                        }
                     }
                 }
             }
+            if (last_of_seg) flush(rb);
+            if (++kt == key_tiles) { kt = 0; ++rb; }
+            if (++turn == kFwdWG) turn = 0;
         }
-        if (cur_rb >= 0) flush(cur_rb);
         NTX_TOC(te_total);
         if (threadIdx.x == 0) { NTX_TSAVE(4, te_total); NTX_TSAVE(5, te_wait); }
     }
@@ -336,7 +362,8 @@ __device__ __forceinline__ void coef_chunk(const uint32_t (&v)[32], uint32_t (&p
         float cv[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            const float e = ex2(fmaf(__uint_as_float(v[j4 * 4 + j]), c1, nc1));
+            const float e = kEdge ? ex2(fmaf(__uint_as_float(v[j4 * 4 + j]), c1, nc1))
+                                  : ex2_mixed<NTX_BWD_POLY>(fmaf(__uint_as_float(v[j4 * 4 + j]), c1, nc1), j4 * 4 + j);
             cv[j] = e * (alpha + bb[j]);
             if (kEdge) {
                 const int col = col0 + j4 * 4 + j;
@@ -482,7 +509,6 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         const uint32_t t_lane = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
         const uint32_t taddr = t_lane + kSCol + g * 128;
         const float c1 = dm.c1, nc1 = -dm.c1;
-        int cur_rb = -1, seg = -1;
         float alpha = 0.f;
         bool row_ok = false;
         NTX_T(te_wait); NTX_T(te_total); NTX_T(te_drain);
@@ -508,55 +534,66 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
             if (lane == 0) mbar_arrive(&ctl->dz_empty);
         };
 
+        // w_c / R_c of one key, fetched a whole tile ahead so its latency is off the critical path
+        auto load_beta = [&](int key_tile) {
+            const int c = key_tile * 128 + tid_g;
+            return c < dm.k_rows ? __ldg(wt.w_k + (size_t)c * wt.w_stride) * wt.w_scale / __ldg(wt.rowsum_k + c)
+                                 : 0.f;
+        };
+        int rb = (int)(t_begin / key_tiles), kt = (int)(t_begin % key_tiles);
+        int seg = 0, own = 0, turn = 0;
+        bool new_seg = true;
+        float beta_next = g < n_tiles ? load_beta((kt + g) % key_tiles) : 0.f;
+
         for (int i = 0; i < n_tiles; ++i) {
-            const long long t = t_begin + i;
-            const int rb = (int)(t / key_tiles), kt = (int)(t % key_tiles);
-            if (rb != cur_rb) {
-                if (cur_rb >= 0) drain(cur_rb, seg);
-                cur_rb = rb;
-                ++seg;
+            if (new_seg) {
                 const int row = rb * 128 + row_in_tile;
                 row_ok = row < dm.q_rows;
                 alpha = row_ok ? __ldg(wt.w_q + (size_t)row * wt.w_stride) * wt.w_scale / __ldg(wt.rowsum_q + row)
                                : 0.f;
+                new_seg = false;
             }
-            if (i % NWG != g) continue;
-
-            // w_c / R_c of this tile's 128 keys -> smem (one buffer per group, fenced on both sides)
-            float* bt = ctl->beta[g];
-            {
-                const int c = kt * 128 + tid_g;
-                const float b = c < dm.k_rows
-                                    ? __ldg(wt.w_k + (size_t)c * wt.w_stride) * wt.w_scale / __ldg(wt.rowsum_k + c)
-                                    : 0.f;
+            const bool last_of_seg = (i + 1 == n_tiles) || (kt + 1 == key_tiles);
+            if (turn == g) {
+                float* bt = ctl->beta[g];
+#ifndef NTX_EXP_NOBETA
                 named_bar_sync(2 + g, 128);          // everyone is done with the previous tile's values
-                bt[tid_g] = b;
-            }
-            named_bar_sync(2 + g, 128);
+                bt[tid_g] = beta_next;
+                named_bar_sync(2 + g, 128);
+                if (i + NWG < n_tiles) beta_next = load_beta((kt + NWG) % key_tiles);
+#endif
 
-            { NTX_TIC(te_wait); mbar_wait(&ctl->s_full[g], (i / NWG) & 1); NTX_TOC(te_wait); }
-            tc_fence_after();
-            const bool edge = edge_tile(rb, kt, dm) || (rb * 128 + 128 > dm.q_rows);
-            const int self = ntx_self_col(rb * 128 + row_in_tile, dm.n_local, dm.rank);
+                { NTX_TIC(te_wait); mbar_wait(&ctl->s_full[g], own & 1); NTX_TOC(te_wait); }
+                ++own;
+                tc_fence_after();
+                const bool edge = edge_tile(rb, kt, dm) || (rb * 128 + 128 > dm.q_rows);
+                const int self = ntx_self_col(rb * 128 + row_in_tile, dm.n_local, dm.rank);
 #pragma unroll 1
-            for (int ch = 0; ch < 4; ++ch) {
-                uint32_t v[32], pk[16];
-                tmem_ld_32x32(taddr + ch * 32, v);
-                tmem_ld_wait_dep(v);
-                if (!edge)
-                    coef_chunk<false>(v, pk, bt + ch * 32, alpha, c1, nc1, 0, 0, 0, true);
-                else
-                    coef_chunk<true>(v, pk, bt + ch * 32, alpha, c1, nc1, kt * 128 + ch * 32, self, dm.k_rows,
-                                     row_ok);
-                // bf16 pairs over fp32 columns that were already read: keys [32ch, 32ch+32) -> columns [16ch, +16)
-                tmem_st_32x16(taddr + ch * 16, pk);
+                for (int ch = 0; ch < 4; ++ch) {
+                    uint32_t v[32], pk[16];
+                    tmem_ld_32x32(taddr + ch * 32, v);
+                    tmem_ld_wait_dep(v);
+                    if (!edge)
+                        coef_chunk<false>(v, pk, bt + ch * 32, alpha, c1, nc1, 0, 0, 0, true);
+                    else
+                        coef_chunk<true>(v, pk, bt + ch * 32, alpha, c1, nc1, kt * 128 + ch * 32, self,
+                                         dm.k_rows, row_ok);
+                    // bf16 pairs over fp32 columns already read: keys [32ch, 32ch+32) -> columns [16ch, +16)
+                    tmem_st_32x16(taddr + ch * 16, pk);
+                }
+                tmem_st_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&ctl->c_full[g]);
             }
-            tmem_st_wait();
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&ctl->c_full[g]);
+            if (last_of_seg) {
+                drain(rb, seg);
+                ++seg;
+                new_seg = true;
+            }
+            if (++kt == key_tiles) { kt = 0; ++rb; }
+            if (++turn == NWG) turn = 0;
         }
-        if (cur_rb >= 0) drain(cur_rb, seg);
         NTX_TOC(te_total);
         if (threadIdx.x == 0) { NTX_TSAVE(13, te_total); NTX_TSAVE(14, te_wait); }
     }

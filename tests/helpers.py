@@ -9,16 +9,20 @@ def rel_err(got, want, floor=1e-30):
 
 
 def grad_floor(case):
-    """Scale below which a gradient is rounding noise: 1e-3 * max row weight / temperature.
+    """Size of the terms a gradient is built from: 0.5 * max row weight / (temperature * ||z||).
 
-    Gradients of NT-Xent are O(w / (tau * ||z||)); cases whose exact gradient is 0
-    (identical or all-zero rows) would otherwise be compared against their own noise.
+    d loss / d z is a difference of terms of size w / (tau * ||z||) (softmax part minus one-hot
+    part, through the normalisation Jacobian 1/||z||).  When they cancel exactly (identical rows,
+    N = 1) the result is rounding noise of those terms and has to be compared with their size,
+    not with zero.  For ordinary cases this floor lies below max |gradient| and changes nothing.
     """
     if case.reduction == "none":
         w = float(np.abs(case.grad_out).max())
     else:
         w = 1.0 if case.reduction == "sum" else 0.5 / case.n
-    return 1e-3 * w / case.tau
+    norms = np.linalg.norm(np.concatenate([case.view0, case.view1]).astype(np.float64), axis=1)
+    norm = float(np.median(norms)) or 1.0
+    return 0.5 * w / (case.tau * norm)
 
 
 def grad_err(got, want, case):
