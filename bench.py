@@ -42,15 +42,19 @@ def parse():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graphs", action="store_true",
+                    help="launch every step eagerly instead of replaying CUDA graphs of the module")
     return ap.parse_args()
 
 
-def workload_config(world):
+def workload_config(world, eager=False):
     return {"workload": f"NT-Xent fwd+bwd, global batch {N_GLOBAL} pairs ({2 * N_GLOBAL} views), d={DIM}, "
                         f"tau={TAU}, bf16 (BASELINE configs[3])",
             "global_batch": N_GLOBAL, "d": DIM, "temperature": TAU,
             "parallelism": f"rows sharded over {world} rank(s), keys all-gathered" if world > 1 else "single GPU",
-            "l2": "flushed between timed steps (256 MiB write)"}
+            "l2": "flushed between timed steps (256 MiB write)",
+            "launch": "eager" if eager else "one CUDA graph of the module's forward + backward "
+                                            "(kernels and NCCL gathers), replayed per step"}
 
 
 def synthetic(dtype):
@@ -63,48 +67,66 @@ def synthetic(dtype):
 
 # ----------------------------------------------------------------------------- clocks
 class ClockSampler:
-    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
-              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-              "clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons polled through NVML every ~2 ms while the timed regions run
+    (the regions last tens of milliseconds: `nvidia-smi -lms` is too coarse for them)."""
 
     def __init__(self, index):
-        self.rows, self.proc, self.index = [], None, index
+        self.index, self.samples, self.stop, self.thread, self.max_mhz = index, [], False, None, None
 
     def __enter__(self):
         try:
-            self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-lms", "100",
-                 "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.thread = threading.Thread(target=self._read, daemon=True)
+            import pynvml
+            pynvml.nvmlInit()
+            uuid = None
+            try:
+                import torch
+                uuid = str(torch.cuda.get_device_properties(self.index).uuid)
+            except Exception:  # noqa: BLE001
+                pass
+            handle = None
+            if uuid:
+                try:
+                    handle = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid).encode())
+                except Exception:  # noqa: BLE001
+                    handle = None
+            if handle is None:
+                handle = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(handle, pynvml.NVML_CLOCK_SM))
+
+            def poll():
+                while not self.stop:
+                    try:
+                        mhz = pynvml.nvmlDeviceGetClockInfo(handle, pynvml.NVML_CLOCK_SM)
+                        reasons = pynvml.nvmlDeviceGetCurrentClocksEventReasons(handle)
+                        util = pynvml.nvmlDeviceGetUtilizationRates(handle).gpu
+                        self.samples.append((float(mhz), int(reasons), int(util)))
+                    except Exception:  # noqa: BLE001
+                        pass
+                    time.sleep(0.002)
+            self.thread = threading.Thread(target=poll, daemon=True)
             self.thread.start()
-        except OSError:
-            self.proc = None
+        except Exception:  # noqa: BLE001
+            self.thread = None
         return self
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
-
     def __exit__(self, *exc):
-        if self.proc:
-            self.proc.terminate()
+        self.stop = True
+        if self.thread:
             self.thread.join(timeout=2)
 
     def summary(self):
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
-            try:
-                sm.append(float(r[0])); mx.append(float(r[1]))
-            except (ValueError, IndexError):
-                continue
-            for name, val in zip(names, r[2:6]):
-                if val.lower().startswith("active"):
-                    reasons.add(name)
-        if not sm:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons),
-                "samples": len(sm)}
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "samples": 0}
+        bits = {"hw_slowdown": 0x8, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40,
+                "sw_power_cap": 0x4, "hw_power_brake_slowdown": 0x80}
+        seen = set()
+        for _, r, _ in self.samples:
+            for name, bit in bits.items():
+                if r & bit:
+                    seen.add(name)
+        return {"sm_mhz": statistics.median(m for m, _, _ in self.samples), "sm_max_mhz": self.max_mhz,
+                "sm_min_mhz": min(m for m, _, _ in self.samples), "reasons": sorted(seen),
+                "samples": len(self.samples), "how": "NVML polled every 2 ms across the timed regions"}
 
 
 # ----------------------------------------------------------------------------- CPU arm
@@ -197,46 +219,15 @@ def run_ours(args):
     d1 = host1.to(dev).requires_grad_(True)
     crit = NT_Xent(temperature=TAU, reduction="mean", device=local_rank, gather=world > 1)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-
-    def step(a, b):
-        a.grad = b.grad = None
-        loss = crit(a, b)
-        loss.backward()
-        return loss
+    ctl = dist.new_group(backend="gloo") if world > 1 else None     # control plane: barriers, max over ranks
 
     def barrier():
-        if world > 1:
-            dist.barrier()
         torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier(group=ctl)
 
-    # ---- device-resident timing: per-step CUDA events, L2 flushed between steps
-    for _ in range(W):
-        step(d0, d1)
-    barrier()
-    starts = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
-    stops = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
-    with ClockSampler(local_rank) as clocks:
-        for i in range(K):
-            flush.zero_()
-            starts[i].record()
-            step(d0, d1)
-            stops[i].record()
-        barrier()
-    dev_ms = sum(s.elapsed_time(e) for s, e in zip(starts, stops))
-
-    # ---- end to end: pinned host -> device, module fwd+bwd, loss back to the host
-    def e2e_step():
-        a = host0.to(dev, non_blocking=True).requires_grad_(True)
-        b = host1.to(dev, non_blocking=True).requires_grad_(True)
-        return float(step(a, b).detach())
-    for _ in range(W):
-        e2e_step()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(K):
-        last_loss = e2e_step()
-    barrier()
-    e2e_ms = (time.perf_counter() - t0) * 1e3
+    clocks = ClockSampler(local_rank)
+    clocks.__enter__()                                               # sampled over every timed region below
 
     # ---- dominant kernel alone (tcgen05 backward) through the C ABI, CUDA events on its stream
     be = _cabi.Backend()
@@ -278,9 +269,71 @@ def run_ours(args):
                 kt[1].append(evs[2].elapsed_time(evs[3]))
     fwd_ms, bwd_ms = statistics.mean(kt[0]), statistics.mean(kt[1])
 
+
+    # ---- the step: forward + backward of the public module on static inputs.  By default the whole
+    # step (five kernels + the NCCL gathers) is captured once into a CUDA graph and replayed.
+    # Fresh leaves: they must first be used on the capture side stream, never on the legacy stream.
+    sa = d0.detach().clone().requires_grad_(True)
+    sb = d1.detach().clone().requires_grad_(True)
+
+    def eager_step():
+        sa.grad = sb.grad = None
+        loss = crit(sa, sb)
+        loss.backward()
+        return loss
+
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        for _ in range(W):
+            static_loss = eager_step()
+    torch.cuda.current_stream().wait_stream(side)
+    barrier()
+    if args.no_graphs:
+        def step():
+            nonlocal static_loss
+            static_loss = eager_step()
+    else:
+        graph = torch.cuda.CUDAGraph()
+        sa.grad = sb.grad = None
+        with torch.cuda.graph(graph, capture_error_mode="thread_local"):
+            static_loss = eager_step()
+        step = graph.replay
+    for _ in range(W):
+        step()
+    barrier()
+
+    # ---- device-resident timing: per-step CUDA events, L2 flushed between steps
+    starts = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
+    stops = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
+    for i in range(K):
+        flush.zero_()
+        starts[i].record()
+        step()
+        stops[i].record()
+    barrier()
+    dev_ms = sum(s.elapsed_time(e) for s, e in zip(starts, stops))
+
+    # ---- end to end: pinned host -> device inputs, module fwd+bwd, loss value back on the host
+    def e2e_step():
+        with torch.no_grad():
+            sa.copy_(host0, non_blocking=True)
+            sb.copy_(host1, non_blocking=True)
+        step()
+        return float(static_loss.detach())
+    for _ in range(W):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(K):
+        last_loss = e2e_step()
+    barrier()
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+    clocks.__exit__(None, None, None)
+
     if world > 1:
-        t = torch.tensor([dev_ms, e2e_ms, fwd_ms, bwd_ms], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        t = torch.tensor([dev_ms, e2e_ms, fwd_ms, bwd_ms], dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=ctl)            # max over ranks
         dev_ms, e2e_ms, fwd_ms, bwd_ms = t.tolist()
 
     if rank == 0:
@@ -297,7 +350,7 @@ def run_ours(args):
             "metric": METRIC, "value": N_GLOBAL / (ms_per_step * 1e-3), "unit": UNIT, "n_gpus": world,
             "steps": K, "warmup": W, "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": workload_config(world),
+            "config": workload_config(world, args.no_graphs),
             "e2e": {"value": N_GLOBAL / (e2e_ms / K * 1e-3), "unit": UNIT,
                     "h2d_bytes_per_step": 2 * N_GLOBAL * DIM * 2, "d2h_bytes_per_step": 2 * world,
                     "ms_per_step": e2e_ms / K, "loss": last_loss},
@@ -315,8 +368,9 @@ def run_ours(args):
             line["cpu_baseline"] = cpu_baseline_block()
         print(json.dumps(line), flush=True)
     if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+        dist.barrier(group=ctl)
+        sys.stdout.flush()
+        os._exit(0)          # skip NCCL teardown: nothing left to do and it can stall after graph replays
     return 0
 
 

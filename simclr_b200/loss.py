@@ -23,6 +23,18 @@ from . import _cabi
 
 _backend = _cabi.Backend()          # tests may swap in a stand-in with the same methods
 _workspaces: dict = {}
+_shapes: dict = {}
+
+
+def _shape_info(be, q_rows: int, k_rows: int, d: int, rows_dtype: torch.dtype, dev: torch.device):
+    """(row pitch, scratch bytes) for a problem shape, asked from the library once per shape."""
+    key = (id(be), q_rows, k_rows, d, rows_dtype, dev)
+    info = _shapes.get(key)
+    if info is None:
+        ld = be.row_pitch(d, rows_dtype)
+        plan = be.plan(q_rows, k_rows, d, rows_dtype)
+        info = _shapes[key] = (ld, max(plan.fwd_ws_bytes, plan.bwd_ws_bytes))
+    return info
 
 
 def _workspace(device: torch.device, nbytes: int) -> torch.Tensor:
@@ -52,7 +64,7 @@ class NTXentFunction(torch.autograd.Function):
         n, d = view0.shape
         dev = view0.device
         q_rows = 2 * n
-        ld = be.row_pitch(d, rows_dtype)
+        ld, ws_bytes = _shape_info(be, q_rows, world * q_rows, d, rows_dtype, dev)
         rows = torch.empty((q_rows, ld), dtype=rows_dtype, device=dev)
         stats = torch.empty((4, q_rows), dtype=torch.float32, device=dev)   # inv_norm, rowsum, pos, row loss
         loss_sum = torch.empty(2, dtype=torch.float32, device=dev)
@@ -65,8 +77,7 @@ class NTXentFunction(torch.autograd.Function):
         else:
             keys = q = rows
         layout = (n, world, rank)
-        plan = be.plan(q_rows, keys.shape[0], d, rows_dtype)
-        ws = _workspace(dev, max(plan.fwd_ws_bytes, plan.bwd_ws_bytes))
+        ws = _workspace(dev, ws_bytes)
         be.fwd(q, keys, d, layout, temperature, rowsum, pos_logit, row_loss, loss_sum, ws)
 
         ctx.save_for_backward(view0, view1, keys, stats)
@@ -105,8 +116,8 @@ class NTXentFunction(torch.autograd.Function):
             rowsum_k, w_k, q = rowsum, w_q, keys
         dview0 = torch.empty_like(view0)
         dview1 = torch.empty_like(view1)
-        plan = be.plan(q_rows, keys.shape[0], d, keys.dtype)
-        ws = _workspace(dev, max(plan.fwd_ws_bytes, plan.bwd_ws_bytes))
+        _, ws_bytes = _shape_info(be, q_rows, keys.shape[0], d, keys.dtype, dev)
+        ws = _workspace(dev, ws_bytes)
         be.bwd(q, keys, d, (n, world, rank), temperature, rowsum, rowsum_k, w_q, w_k, w_stride, w_scale,
                view0, view1, inv_norm, dview0, dview1, ws)
         return dview0, dview1, None, None, None, None, None, None

@@ -1,0 +1,111 @@
+"""world_size-2 gloo tests of the multi-rank path: the differentiable row gather and the
+NT_Xent(gather=True) autograd wiring (keys, row sums and row weights gathered; per-rank mean).
+The CUDA kernels are replaced by tests/standin_backend.py here; the same scenario runs on NCCL
+with the real kernels in tests/test_gpu_multi.py."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from conftest import GOLDEN
+
+WORLD = 2
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _init(rank, port):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    from simclr_b200 import distributed_utils as du
+    du.init_ddp({"distributed": {"local_rank": rank, "world_size": WORLD,
+                                 "dist_url": f"tcp://127.0.0.1:{port}"}}, backend="gloo")
+    return du
+
+
+def _worker_gather(rank, port, out):
+    du = _init(rank, port)
+    torch.manual_seed(0)
+    full = torch.randn(WORLD * 3, 4, dtype=torch.float64)
+    mine = full[rank * 3:(rank + 1) * 3].clone().requires_grad_(True)
+    gathered = du.gather_rows_with_grad(mine)
+    assert torch.equal(gathered.detach(), full)                      # rank-major order
+    weight = torch.arange(1, WORLD * 3 * 4 + 1, dtype=torch.float64).view(WORLD * 3, 4) * (rank + 1)
+    (gathered * weight).sum().backward()
+    # SUM reduce-scatter: rank r's rows collect the weights every rank applied to its chunk
+    want = sum(torch.arange(1, WORLD * 3 * 4 + 1, dtype=torch.float64).view(WORLD * 3, 4)[rank * 3:(rank + 1) * 3] * (k + 1)
+               for k in range(WORLD))
+    out[rank] = bool(torch.allclose(mine.grad, want))
+    du.cleanup()
+
+
+def _worker_loss(rank, port, reduction, out):
+    _init(rank, port)
+    import simclr_b200.loss as loss_mod
+    from standin_backend import StandInBackend
+    loss_mod._backend = StandInBackend()                            # test-only: kernels on CPU tensors
+    c = next(g for g in GOLDEN if g.name == "shard_w2")
+    nl = c.n // WORLD
+    sl = slice(rank * nl, (rank + 1) * nl)
+    a = torch.tensor(c.view0[sl], requires_grad=True)
+    b = torch.tensor(c.view1[sl], requires_grad=True)
+    crit = loss_mod.NT_Xent(temperature=c.tau, reduction=reduction, gather=True)
+    loss = crit(a, b)
+    if reduction == "none":
+        g = torch.full((2, nl), 0.5 + rank)                         # ranks hold different upstream gradients
+        loss.backward(g)
+    else:
+        loss.backward()
+    # DDP would average gradients over ranks; the reference gradient is for the GLOBAL mean loss
+    res = {"loss": loss.detach().numpy().copy(), "g0": a.grad.numpy().copy(), "g1": b.grad.numpy().copy()}
+    out[rank] = res
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def _spawn(fn, *args):
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(fn, args=(_free_port(), *args, out), nprocs=WORLD, join=True)
+    return dict(out)
+
+
+def test_gather_rows_forward_and_reduce_scatter_backward():
+    out = _spawn(_worker_gather)
+    assert out == {0: True, 1: True}
+
+
+def test_gathered_loss_matches_reference_on_concatenated_batch():
+    out = _spawn(_worker_loss, "mean")
+    c = next(g for g in GOLDEN if g.name == "shard_w2")
+    nl = c.n // WORLD
+    # mean over ranks of the per-rank mean loss == the reference's loss on the concatenated batch
+    assert abs(np.mean([out[k]["loss"] for k in range(WORLD)]) - float(c.loss)) < 1e-6 * float(c.loss)
+    for k in range(WORLD):
+        sl = slice(k * nl, (k + 1) * nl)
+        scale = np.abs(c.dview0).max()
+        # each rank's loss is a mean over ITS rows -> gradients are W x the global-mean gradients (DDP's 1/W undoes it)
+        assert np.abs(out[k]["g0"] / WORLD - c.dview0[sl]).max() < 1e-5 * scale
+        assert np.abs(out[k]["g1"] / WORLD - c.dview1[sl]).max() < 1e-5 * scale
+
+
+def test_gathered_loss_with_per_rank_row_weights():
+    from oracle import ntxent_oracle as orc
+    out = _spawn(_worker_loss, "none")
+    c = next(g for g in GOLDEN if g.name == "shard_w2")
+    nl = c.n // WORLD
+    w = np.concatenate([np.full((2, nl), 0.5 + k) for k in range(WORLD)], axis=1)       # (2, N) global weights
+    ref = orc.ntxent_rows_fp64(c.view0, c.view1, c.tau, weights=w)
+    for k in range(WORLD):
+        sl = slice(k * nl, (k + 1) * nl)
+        assert np.abs(out[k]["loss"] - ref["loss"][:, sl]).max() < 1e-5
+        scale = np.abs(ref["dview0"]).max()
+        assert np.abs(out[k]["g0"] - ref["dview0"][sl]).max() < 1e-5 * scale
+        assert np.abs(out[k]["g1"] - ref["dview1"][sl]).max() < 1e-5 * scale
