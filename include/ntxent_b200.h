@@ -124,6 +124,27 @@ int ntx_bwd(const void* q_rows_ptr, const void* k_rows_ptr, int q_rows, int k_ro
             const void* view0, const void* view1, int in_dtype, const float* inv_norm, void* dview0,
             void* dview1, void* workspace, size_t workspace_bytes, void* stream);
 
+/* ntx_fwd without a caller-supplied scratch buffer.  This entry point has no counterpart in the
+ * reference.  It is for hosts that hold nothing but their input and output buffers and cannot
+ * obtain device scratch themselves: a plain C / ctypes caller that has no device allocator of
+ * its own, or code running where cudaMalloc is not an option because it synchronises the whole
+ * device and is illegal while a stream is being captured.  The partial row sums, the finalize
+ * ticket and the block sums live in a fixed array inside the library instead
+ * (NTX_STATIC_SCRATCH_BYTES of device memory on every GPU that loads the library, held until
+ * the process exits).  Same arguments, outputs and arithmetic as ntx_fwd.
+ *  - Problems whose scratch need (NtxPlan.fwd_ws_bytes) exceeds NTX_STATIC_SCRATCH_BYTES are
+ *    refused with NTX_E_WORKSPACE and a message naming both numbers; use ntx_fwd for those.
+ *  - The first call on each device looks the array's device address up once (no allocation);
+ *    make that first call before any stream capture begins on that device.
+ *  - All calls on a device share the one array: calls whose kernels can overlap on the GPU
+ *    (different streams, no ordering between them) race on it.  Calls ordered on one stream are
+ *    safe; nothing in the array needs clearing by the caller between calls.
+ *  - Allocates nothing and frees nothing, like every other entry point here. */
+#define NTX_STATIC_SCRATCH_BYTES (1u << 20)
+int ntx_fwd_static(const void* q_rows_ptr, const void* k_rows_ptr, int q_rows, int k_rows, int d, int ld,
+                   int dtype, const NtxLayout* layout, float temperature, float* rowsum,
+                   float* pos_logit, float* row_loss, float* loss_sum, void* stream);
+
 /* Test entry: the self and positive column of every row, computed on the device by
  * the same helper the kernels use (bit-exact contract on loss.py:37-38 indexing). */
 int ntx_debug_indices(const NtxLayout* layout, int32_t* self_col, int32_t* pos_col, void* stream);

@@ -19,7 +19,7 @@ DTYPES = {torch.float32: NTX_F32, torch.bfloat16: NTX_BF16}
 
 EXPORTS = (
     "ntx_version", "ntx_last_error", "ntx_row_pitch", "ntx_plan", "ntx_l2norm", "ntx_fwd",
-    "ntx_bwd", "ntx_debug_indices", "ntx_profile_next",
+    "ntx_bwd", "ntx_debug_indices", "ntx_profile_next", "ntx_fwd_static",
 )
 
 
@@ -56,6 +56,7 @@ def _declare(lib):
     lib.ntx_fwd.argtypes = [vp, vp, i, i, i, i, i, ctypes.POINTER(NtxLayout), f, vp, vp, vp, vp, vp, sz, vp]
     lib.ntx_bwd.argtypes = [vp, vp, i, i, i, i, i, ctypes.POINTER(NtxLayout), f, vp, vp, vp, vp, i, f,
                             vp, vp, i, vp, vp, vp, vp, sz, vp]
+    lib.ntx_fwd_static.argtypes = [vp, vp, i, i, i, i, i, ctypes.POINTER(NtxLayout), f, vp, vp, vp, vp, vp]
     lib.ntx_debug_indices.argtypes = [ctypes.POINTER(NtxLayout), vp, vp, vp]
     lib.ntx_profile_next.argtypes = [i, vp, vp]
     for name in EXPORTS:
@@ -115,6 +116,16 @@ class Backend:
                               pos_logit.data_ptr(), row_loss.data_ptr(), loss_sum.data_ptr(),
                               workspace.data_ptr(), workspace.numel() * workspace.element_size(),
                               _stream(q)))
+
+    def fwd_static(self, q, k, d, layout, temperature, rowsum, pos_logit, row_loss, loss_sum):
+        """ntx_fwd_static: the forward with the library's own fixed scratch array, for callers that
+        cannot provide scratch memory.  Limited to problems needing at most 1 MiB of scratch; calls
+        that may overlap on the GPU race on the shared array."""
+        lay = NtxLayout(*layout)
+        _check(load().ntx_fwd_static(q.data_ptr(), k.data_ptr(), q.shape[0], k.shape[0], d, q.shape[1],
+                                     DTYPES[q.dtype], ctypes.byref(lay), float(temperature),
+                                     rowsum.data_ptr(), pos_logit.data_ptr(), row_loss.data_ptr(),
+                                     loss_sum.data_ptr(), _stream(q)))
 
     def bwd(self, q, k, d, layout, temperature, rowsum_q, rowsum_k, w_q, w_k, w_stride, w_scale, view0,
             view1, inv_norm, dview0, dview1, workspace):

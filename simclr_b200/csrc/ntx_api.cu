@@ -4,6 +4,8 @@
 #include <stdarg.h>
 #include <string.h>
 
+#include <mutex>
+
 #include "ntx_common.cuh"
 
 static thread_local char g_err[512] = "";
@@ -224,6 +226,62 @@ int ntx_bwd(const void* q, const void* k, int q_rows, int k_rows, int d, int ld,
     if (rc) return rc;
     return ntx_bwd_finalize_launch(dm, plan, partial, wt, view0, view1, in_dtype, inv_norm, dview0,
                                    dview1, st);
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// ntx_fwd_static: the forward with its scratch in a fixed device array owned by the library.
+// For callers that cannot hand us scratch memory (no device allocator of their own, or running
+// where cudaMalloc is off limits).  One array per device, shared by every call on that device.
+// ---------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_ntx_static_scratch[NTX_STATIC_SCRATCH_BYTES];
+
+namespace {
+
+// `g_ntx_static_scratch` in host code is only a handle for the runtime, not a device address:
+// the address each device gave the array is looked up once per device, with that device current.
+int static_scratch_ptr(void** out) {
+    static std::mutex mu;
+    static void* ptrs[64] = {};
+    int dev = 0;
+    NTX_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) {
+        ntx_set_error("ntx_fwd_static: device index %d out of range", dev);
+        return NTX_E_UNSUPPORTED;
+    }
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptrs[dev]) {
+        void* p = nullptr;
+        NTX_CUDA(cudaGetSymbolAddress(&p, g_ntx_static_scratch));   // device `dev` is current
+        ptrs[dev] = p;
+    }
+    *out = ptrs[dev];
+    return NTX_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ntx_fwd_static(const void* q, const void* k, int q_rows, int k_rows, int d, int ld, int dtype,
+                   const NtxLayout* layout, float temperature, float* rowsum, float* pos_logit,
+                   float* row_loss, float* loss_sum, void* stream) {
+    NtxPlan plan;
+    int rc = ntx_plan(q_rows, k_rows, d, dtype, 0, &plan);
+    if (rc) return rc;
+    if (plan.fwd_ws_bytes > NTX_STATIC_SCRATCH_BYTES) {
+        ntx_set_error("ntx_fwd_static: this problem needs %llu bytes of scratch but the built-in array "
+                      "holds %u; call ntx_fwd with a caller-provided workspace instead",
+                      (unsigned long long)plan.fwd_ws_bytes, (unsigned)NTX_STATIC_SCRATCH_BYTES);
+        return NTX_E_WORKSPACE;
+    }
+    void* scratch = nullptr;
+    if ((rc = static_scratch_ptr(&scratch))) return rc;
+    // Nothing in the array has to be cleared here: every partial slot that is read was written by
+    // this call's main kernel, which also resets the finalize ticket before the finalize runs.
+    return ntx_fwd(q, k, q_rows, k_rows, d, ld, dtype, layout, temperature, rowsum, pos_logit, row_loss,
+                   loss_sum, scratch, NTX_STATIC_SCRATCH_BYTES, stream);
 }
 
 int ntx_profile_next(int which, void* ev_start, void* ev_stop) {
