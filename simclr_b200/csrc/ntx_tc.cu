@@ -534,16 +534,19 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
             if (lane == 0) mbar_arrive(&ctl->dz_empty);
         };
 
-        // w_c / R_c of one key, fetched a whole tile ahead so its latency is off the critical path
-        auto load_beta = [&](int key_tile) {
+        // w_c and R_c of one key are fetched a whole tile ahead (raw: the division waits until the
+        // values are consumed, so the load latency stays off the critical path)
+        float w_next = 0.f, r_next = 1.f;
+        auto fetch_beta = [&](int key_tile) {
             const int c = key_tile * 128 + tid_g;
-            return c < dm.k_rows ? __ldg(wt.w_k + (size_t)c * wt.w_stride) * wt.w_scale / __ldg(wt.rowsum_k + c)
-                                 : 0.f;
+            const bool ok = c < dm.k_rows;
+            w_next = ok ? __ldg(wt.w_k + (size_t)c * wt.w_stride) : 0.f;
+            r_next = ok ? __ldg(wt.rowsum_k + c) : 1.f;
         };
         int rb = (int)(t_begin / key_tiles), kt = (int)(t_begin % key_tiles);
         int seg = 0, own = 0, turn = 0;
         bool new_seg = true;
-        float beta_next = g < n_tiles ? load_beta((kt + g) % key_tiles) : 0.f;
+        if (g < n_tiles) fetch_beta((kt + g) % key_tiles);
 
         for (int i = 0; i < n_tiles; ++i) {
             if (new_seg) {
@@ -556,12 +559,11 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
             const bool last_of_seg = (i + 1 == n_tiles) || (kt + 1 == key_tiles);
             if (turn == g) {
                 float* bt = ctl->beta[g];
-#ifndef NTX_EXP_NOBETA
+                const float beta = w_next * wt.w_scale / r_next;
                 named_bar_sync(2 + g, 128);          // everyone is done with the previous tile's values
-                bt[tid_g] = beta_next;
+                bt[tid_g] = beta;
                 named_bar_sync(2 + g, 128);
-                if (i + NWG < n_tiles) beta_next = load_beta((kt + NWG) % key_tiles);
-#endif
+                if (i + NWG < n_tiles) fetch_beta((kt + NWG) % key_tiles);
 
                 { NTX_TIC(te_wait); mbar_wait(&ctl->s_full[g], own & 1); NTX_TOC(te_wait); }
                 ++own;
