@@ -68,18 +68,62 @@ __device__ __forceinline__ float ex2_poly(float x) {
     p = fmaf(p, f, 0.999928057f);
     return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
 }
+// Packed fp32x2 arithmetic (Blackwell FFMA2 / FADD2 / FMUL2): two logits per instruction.  The
+// epilogues are bound by instruction issue and MUFU, not by the FP32 datapath, so halving the
+// number of FP32 instructions is what buys time.
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+    f32x2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+    f32x2 d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+    f32x2 d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+// exp2 of a pair: on MUFU, or by the packed form of ex2_poly (3 FADD2-class + 3 FFMA2 + 2 integer ops)
+__device__ __forceinline__ f32x2 ex2_pair_mufu(f32x2 x) {
+    float lo, hi;
+    unpack2(x, lo, hi);
+    return pack2(ex2(lo), ex2(hi));
+}
+__device__ __forceinline__ f32x2 ex2_pair_poly(f32x2 x) {
+    const f32x2 kMagic = pack2(12582912.f, 12582912.f), kNegMagic = pack2(-12582912.f, -12582912.f);
+    const f32x2 kNegOne = pack2(-1.f, -1.f);
+    const f32x2 k3 = pack2(0.0551716685f, 0.0551716685f), k2 = pack2(0.242611125f, 0.242611125f);
+    const f32x2 k1 = pack2(0.693260968f, 0.693260968f), k0 = pack2(0.999928057f, 0.999928057f);
+    const f32x2 t = add2(x, kMagic);
+    const f32x2 f = fma2(add2(t, kNegMagic), kNegOne, x);       // x - round(x)
+    f32x2 p = fma2(f, k3, k2);
+    p = fma2(p, f, k1);
+    p = fma2(p, f, k0);
+    float p0, p1, t0, t1;
+    unpack2(p, p0, p1);
+    unpack2(t, t0, t1);
+    return pack2(__int_as_float(__float_as_int(p0) + (__float_as_int(t0) << 23)),
+                 __int_as_float(__float_as_int(p1) + (__float_as_int(t1) << 23)));
+}
 #ifndef NTX_FWD_POLY
-#define NTX_FWD_POLY 2      // of every 8 exponentials of the forward epilogue, how many use ex2_poly
-                            // (measured on B200, N=8192 D=128: 0 -> 86.6 us, 1 -> 81.7, 2 -> 78.3, 3 -> 81.4, 4 -> 88.1)
+#define NTX_FWD_POLY 1      // of every 4 PAIRS of exponentials in the forward epilogue, how many use the polynomial
+                            // (B200, N=8192 D=128: 1 -> 75.4 us, 2 -> 79.2 us, 3 -> 90.5 us; scalar code without any: 86.6 us)
 #endif
 #ifndef NTX_BWD_POLY
-#define NTX_BWD_POLY 0      // same for the backward epilogue
+#define NTX_BWD_POLY 1      // same (pairs of every 4) for the backward epilogue (0 -> 115.2 us, 1 -> 112.7 us)
 #endif
-template <int kPolyOf8>
-__device__ __forceinline__ float ex2_mixed(float x, int j) {
-    // spread the polynomial lanes over the 8 so both pipes stay busy: j*kPolyOf8 mod 8 < kPolyOf8
-    return ((j * kPolyOf8) & 7) < kPolyOf8 && kPolyOf8 > 0 ? ex2_poly(x) : ex2(x);
-}
 __device__ __forceinline__ void named_bar_sync(int id, int threads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
 }
@@ -253,14 +297,20 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         const int row_in_tile = (warp & 3) * 32 + lane;
         const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + g * 128;
         const float c1 = dm.c1, nc1 = -dm.c1;
-        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+        const f32x2 c1x2 = pack2(c1, c1), nc1x2 = pack2(nc1, nc1);
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};          // edge tiles (scalar, masked)
+        f32x2 pacc[2] = {pack2(0.f, 0.f), pack2(0.f, 0.f)};   // interior tiles (packed pairs)
         int flushes = 0;
         NTX_T(te_wait); NTX_T(te_total); NTX_T(te_ld);
         NTX_TIC(te_total);
 
         // row sums of the groups are added in group order: deterministic
         auto flush = [&](int rb) {
-            float rs = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+            float p0, p1, p2, p3;
+            unpack2(pacc[0], p0, p1);
+            unpack2(pacc[1], p2, p3);
+            float rs = ((acc[0] + acc[1]) + (acc[2] + acc[3])) + ((p0 + p1) + (p2 + p3));
+            pacc[0] = pacc[1] = pack2(0.f, 0.f);
             float (*x)[128] = ctl->xch[flushes & 1];
             if (g > 0) x[g - 1][row_in_tile] = rs;
             named_bar_sync(1, kFwdWG * 128);
@@ -297,9 +347,15 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
                         if (lane == 0) mbar_arrive(&ctl->s_empty[g]);
                     }
                     if (!edge) {
+                        // two logits per instruction: x = s * c1 - c1 (FFMA2), exp2 on MUFU or by the
+                        // polynomial for NTX_FWD_POLY of every 4 pairs, row sums by FADD2
 #pragma unroll
-                        for (int j = 0; j < 32; ++j)
-                            acc[j & 3] += ex2_mixed<NTX_FWD_POLY>(fmaf(__uint_as_float(v[ch & 1][j]), c1, nc1), j);
+                        for (int j = 0; j < 16; ++j) {
+                            const f32x2 x = fma2(pack2(__uint_as_float(v[ch & 1][2 * j]),
+                                                       __uint_as_float(v[ch & 1][2 * j + 1])), c1x2, nc1x2);
+                            const bool poly = NTX_FWD_POLY > 0 && ((j * NTX_FWD_POLY) & 3) < NTX_FWD_POLY;
+                            pacc[j & 1] = add2(pacc[j & 1], poly ? ex2_pair_poly(x) : ex2_pair_mufu(x));
+                        }
                     } else {
 #pragma unroll
                         for (int j = 0; j < 32; ++j) {
@@ -355,25 +411,27 @@ template <bool kEdge>
 __device__ __forceinline__ void coef_chunk(const uint32_t (&v)[32], uint32_t (&pk)[16], const float* bt,
                                            float alpha, float c1, float nc1, int col0, int self, int k_rows,
                                            bool row_ok) {
+    const f32x2 c1x2 = pack2(c1, c1), nc1x2 = pack2(nc1, nc1), alpha2 = pack2(alpha, alpha);
 #pragma unroll
     for (int j4 = 0; j4 < 8; ++j4) {
         const float4 b = *reinterpret_cast<const float4*>(bt + j4 * 4);
-        const float bb[4] = {b.x, b.y, b.z, b.w};
-        float cv[4];
+        const f32x2 beta2[2] = {pack2(b.x, b.y), pack2(b.z, b.w)};
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const float e = kEdge ? ex2(fmaf(__uint_as_float(v[j4 * 4 + j]), c1, nc1))
-                                  : ex2_mixed<NTX_BWD_POLY>(fmaf(__uint_as_float(v[j4 * 4 + j]), c1, nc1), j4 * 4 + j);
-            cv[j] = e * (alpha + bb[j]);
+        for (int h = 0; h < 2; ++h) {        // two keys per instruction (FFMA2, FADD2, FMUL2)
+            const int j = j4 * 4 + h * 2;
+            const f32x2 x = fma2(pack2(__uint_as_float(v[j]), __uint_as_float(v[j + 1])), c1x2, nc1x2);
+            const bool poly = !kEdge && NTX_BWD_POLY > 0 && (((j4 * 2 + h) * NTX_BWD_POLY) & 3) < NTX_BWD_POLY;
+            const f32x2 e = poly ? ex2_pair_poly(x) : ex2_pair_mufu(x);
+            float c0, c1v;
+            unpack2(mul2(e, add2(alpha2, beta2[h])), c0, c1v);
             if (kEdge) {
-                const int col = col0 + j4 * 4 + j;
-                if (col == self || col >= k_rows || !row_ok) cv[j] = 0.f;
+                const int col = col0 + j;
+                if (col == self || col >= k_rows || !row_ok) c0 = 0.f;
+                if (col + 1 == self || col + 1 >= k_rows || !row_ok) c1v = 0.f;
             }
+            __nv_bfloat162 hh = __floats2bfloat162_rn(c0, c1v);
+            pk[j4 * 2 + h] = *reinterpret_cast<uint32_t*>(&hh);
         }
-        __nv_bfloat162 h0 = __floats2bfloat162_rn(cv[0], cv[1]);
-        __nv_bfloat162 h1 = __floats2bfloat162_rn(cv[2], cv[3]);
-        pk[j4 * 2] = *reinterpret_cast<uint32_t*>(&h0);
-        pk[j4 * 2 + 1] = *reinterpret_cast<uint32_t*>(&h1);
     }
 }
 

@@ -105,12 +105,14 @@ class NTXentFunction(torch.autograd.Function):
         w_scale = 1.0 / q_rows if reduction == "mean" else 1.0
         w_q = g.view(-1)
         if world > 1:
-            rowsum_k = torch.empty(world * q_rows, dtype=torch.float32, device=dev)
-            dist.all_gather_into_tensor(rowsum_k, rowsum.contiguous(), group=group)
-            w_k = torch.empty(world * q_rows, dtype=torch.float32, device=dev)
-            dist.all_gather_into_tensor(w_k, w_q.expand(q_rows).contiguous(), group=group)
-            if w_stride == 0:      # ranks may hold different upstream gradients: go per row
-                w_q, w_stride = w_k[rank * q_rows:(rank + 1) * q_rows], 1
+            # one collective for both per-key vectors: every rank contributes [rowsum ; row weights]
+            mine = torch.stack((rowsum, w_q.expand(q_rows)))                       # (2, q_rows)
+            both = torch.empty((world * 2, q_rows), dtype=torch.float32, device=dev)
+            dist.all_gather_into_tensor(both, mine, group=group)
+            both = both.view(world, 2, q_rows)
+            rowsum_k = both[:, 0, :].reshape(-1)                                   # rank-major, like the keys
+            w_k = both[:, 1, :].reshape(-1)
+            w_q, w_stride = w_k[rank * q_rows:(rank + 1) * q_rows], 1              # ranks may hold different upstream gradients
             q = keys[rank * q_rows:(rank + 1) * q_rows]
         else:
             rowsum_k, w_k, q = rowsum, w_q, keys
