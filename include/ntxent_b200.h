@@ -70,8 +70,13 @@ typedef struct NtxPlan {
     int32_t max_slots;     /* most CTAs that share one row block (partials per row) */
     int32_t d_pad;         /* feature dim padded to the kernel's granule */
     int32_t tensor_cores;  /* 1 = tcgen05 path (bf16 rows), 0 = fp32 CUDA-core path */
-    uint64_t fwd_ws_bytes; /* scratch ntx_fwd needs */
+    uint64_t fwd_ws_bytes; /* scratch ntx_fwd wants (enables the symmetric forward when it applies) */
     uint64_t bwd_ws_bytes; /* scratch ntx_bwd needs */
+    uint64_t fwd_ws_bytes_min; /* least scratch ntx_fwd accepts (full-tile forward) */
+    int32_t fwd_symmetric; /* 1: keys == rows, bf16, d_pad <= 128 -> only tiles (rb, kt >= rb) are computed */
+    int32_t fwd_grid;      /* CTAs of the symmetric forward kernel */
+    int32_t fwd_max_slots; /* its row-sum slots per row block */
+    int32_t reserved;
 } NtxPlan;
 
 int ntx_version(void);
@@ -101,7 +106,12 @@ int ntx_l2norm(const void* view0, const void* view1, int n, int d, int in_dtype,
  * Replaces loss.py:36-61: the three similarity GEMMs (:42,43,49), the boolean-mask
  * diagonal removal (:38,46-47), the concatenations (:51-52) and both cross-entropies
  * (:56-61); the 2N x 2N logits are never written to memory.
- * q_rows_ptr/k_rows_ptr: normalised rows ([q_rows x ld], [k_rows x ld]) of `dtype`. */
+ * q_rows_ptr/k_rows_ptr: normalised rows ([q_rows x ld], [k_rows x ld]) of `dtype`.
+ * Scratch: with workspace_bytes >= NtxPlan.fwd_ws_bytes and NtxPlan.fwd_symmetric the kernel exploits
+ * S = S^T (keys are the rows themselves): each off-diagonal tile feeds the row sums of its rows and,
+ * through a ones-vector MMA over the bf16 tile, the row sums of its columns.  With at least
+ * fwd_ws_bytes_min every tile is computed.  Both are deterministic; they differ from each other in the
+ * last bits (bf16 rounding of the column contributions, inside the 1e-2 contract). */
 int ntx_fwd(const void* q_rows_ptr, const void* k_rows_ptr, int q_rows, int k_rows, int d, int ld,
             int dtype, const NtxLayout* layout, float temperature, float* rowsum,
             float* pos_logit, float* row_loss, float* loss_sum, void* workspace,
@@ -132,7 +142,7 @@ int ntx_bwd(const void* q_rows_ptr, const void* k_rows_ptr, int q_rows, int k_ro
  * ticket and the block sums live in a fixed array inside the library instead
  * (NTX_STATIC_SCRATCH_BYTES of device memory on every GPU that loads the library, held until
  * the process exits).  Same arguments, outputs and arithmetic as ntx_fwd.
- *  - Problems whose scratch need (NtxPlan.fwd_ws_bytes) exceeds NTX_STATIC_SCRATCH_BYTES are
+ *  - Problems whose scratch need (NtxPlan.fwd_ws_bytes_min) exceeds NTX_STATIC_SCRATCH_BYTES are
  *    refused with NTX_E_WORKSPACE and a message naming both numbers; use ntx_fwd for those.
  *  - The first call on each device looks the array's device address up once (no allocation);
  *    make that first call before any stream capture begins on that device.

@@ -2,6 +2,7 @@
 // Validates arguments, derives the work partition and enqueues kernels on the
 // caller's stream.  Allocates nothing, never synchronises.
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <mutex>
@@ -139,9 +140,31 @@ int ntx_plan(int q_rows, int k_rows, int d, int dtype, int sm_count, NtxPlan* pl
     plan->max_slots = max_slots;
     const uint64_t rows_pad = (uint64_t)plan->row_blocks * plan->tile_rows;
     // row-sum partials + finalize ticket + one fp64 block sum per finalize block
-    plan->fwd_ws_bytes = (uint64_t)max_slots * rows_pad * sizeof(float) + 16 +
-                         (uint64_t)ntx_fwd_finalize_blocks(q_rows, ntx_row_pitch(d, dtype)) * 8;
+    const uint64_t fin_bytes = 16 + (((uint64_t)ntx_fwd_finalize_blocks(q_rows, ntx_row_pitch(d, dtype)) * 8 + 15) & ~15ull);
+    plan->fwd_ws_bytes_min = (uint64_t)max_slots * rows_pad * sizeof(float) + fin_bytes;
+    plan->fwd_ws_bytes = plan->fwd_ws_bytes_min;
     plan->bwd_ws_bytes = (uint64_t)max_slots * rows_pad * plan->d_pad * sizeof(float);
+
+    // Symmetric forward: the keys are the rows themselves (one rank), so S = S^T and only the tiles
+    // (rb, kt >= rb) need computing.  Needs one column partial per (row block, key) besides the slots.
+    plan->fwd_grid = plan->grid;
+    plan->fwd_max_slots = max_slots;
+    if (plan->tensor_cores && q_rows == k_rows && plan->d_pad <= 128 && plan->row_blocks >= 2 &&
+        getenv("NTXENT_NO_SYMMETRIC_FWD") == nullptr) {
+        const int RB = plan->row_blocks;
+        const long long Tt = (long long)RB * (RB + 1) / 2;
+        plan->fwd_symmetric = 1;
+        plan->fwd_grid = (int)(Tt < ctas ? Tt : ctas);
+        int ms = 1;
+        for (int rb = 0; rb < RB; ++rb) {
+            const int sl = ntx_tri_num_slots(Tt, plan->fwd_grid, RB, rb);
+            if (sl > ms) ms = sl;
+        }
+        plan->fwd_max_slots = ms;
+        plan->fwd_ws_bytes = (uint64_t)ms * rows_pad * sizeof(float) + fin_bytes +
+                             (uint64_t)RB * rows_pad * sizeof(float);
+        if (plan->fwd_ws_bytes < plan->fwd_ws_bytes_min) plan->fwd_ws_bytes = plan->fwd_ws_bytes_min;
+    }
     return NTX_OK;
 }
 
@@ -168,28 +191,36 @@ int ntx_fwd(const void* q, const void* k, int q_rows, int k_rows, int d, int ld,
     NTX_CHECK_ARG(rowsum && pos_logit && row_loss && loss_sum, "NULL output buffer");
     NtxPlan plan;
     if ((rc = ntx_plan(q_rows, k_rows, d, dtype, 0, &plan))) return rc;
-    if (workspace == nullptr || workspace_bytes < plan.fwd_ws_bytes) {
-        ntx_set_error("ntx_fwd needs %llu bytes of workspace, got %llu",
-                      (unsigned long long)plan.fwd_ws_bytes, (unsigned long long)workspace_bytes);
+    if (workspace == nullptr || workspace_bytes < plan.fwd_ws_bytes_min) {
+        ntx_set_error("ntx_fwd needs at least %llu bytes of workspace (%llu for the symmetric forward), got %llu",
+                      (unsigned long long)plan.fwd_ws_bytes_min, (unsigned long long)plan.fwd_ws_bytes,
+                      (unsigned long long)workspace_bytes);
         return NTX_E_WORKSPACE;
     }
     if ((rc = aligned16(workspace, "workspace"))) return rc;
     cudaStream_t st = (cudaStream_t)stream;
+    // the symmetric kernel needs q and k to be the same buffer and the larger scratch
+    const bool sym = plan.fwd_symmetric && q == k && layout->world == 1 && workspace_bytes >= plan.fwd_ws_bytes;
+    const uint64_t rows_pad = (uint64_t)plan.row_blocks * plan.tile_rows;
+    const uint64_t partial_bytes = (uint64_t)(sym ? plan.fwd_max_slots : plan.max_slots) * rows_pad * sizeof(float);
+    const uint64_t fin_bytes = 16 + (((uint64_t)ntx_fwd_finalize_blocks(q_rows, ld) * 8 + 15) & ~15ull);
     float* partial = (float*)workspace;
-    const uint64_t partial_bytes = (uint64_t)plan.max_slots * plan.row_blocks * plan.tile_rows * sizeof(float);
     unsigned int* counter = (unsigned int*)((char*)workspace + partial_bytes);
     double* block_sums = (double*)((char*)workspace + partial_bytes + 16);
+    float* colpart = sym ? (float*)((char*)workspace + partial_bytes + fin_bytes) : nullptr;
     {
         ProfScope prof(0, st);
-        if (plan.tensor_cores)
+        if (sym)
+            rc = ntx_tc_fwd_sym_launch((const __nv_bfloat16*)q, dm, plan, partial, colpart, counter, st);
+        else if (plan.tensor_cores)
             rc = ntx_tc_fwd_launch((const __nv_bfloat16*)q, (const __nv_bfloat16*)k, dm, plan, partial,
                                    counter, st);
         else
             rc = ntx_simt_fwd_launch((const float*)q, (const float*)k, dm, plan, partial, counter, st);
     }
     if (rc) return rc;
-    return ntx_fwd_finalize_launch(q, dtype, dm, plan, partial, counter, block_sums, rowsum, pos_logit,
-                                   row_loss, loss_sum, st);
+    return ntx_fwd_finalize_launch(q, dtype, dm, plan, partial, colpart, counter, block_sums, rowsum,
+                                   pos_logit, row_loss, loss_sum, st);
 }
 
 int ntx_bwd(const void* q, const void* k, int q_rows, int k_rows, int d, int ld, int dtype,
@@ -270,10 +301,10 @@ int ntx_fwd_static(const void* q, const void* k, int q_rows, int k_rows, int d, 
     NtxPlan plan;
     int rc = ntx_plan(q_rows, k_rows, d, dtype, 0, &plan);
     if (rc) return rc;
-    if (plan.fwd_ws_bytes > NTX_STATIC_SCRATCH_BYTES) {
+    if (plan.fwd_ws_bytes_min > NTX_STATIC_SCRATCH_BYTES) {
         ntx_set_error("ntx_fwd_static: this problem needs %llu bytes of scratch but the built-in array "
                       "holds %u; call ntx_fwd with a caller-provided workspace instead",
-                      (unsigned long long)plan.fwd_ws_bytes, (unsigned)NTX_STATIC_SCRATCH_BYTES);
+                      (unsigned long long)plan.fwd_ws_bytes_min, (unsigned)NTX_STATIC_SCRATCH_BYTES);
         return NTX_E_WORKSPACE;
     }
     void* scratch = nullptr;

@@ -63,6 +63,20 @@ NTX_HD int ntx_num_slots(long long T, int G, int key_tiles, int rb) {
            ntx_tile_owner(T, G, (long long)rb * key_tiles) + 1;
 }
 
+// Upper-triangle enumeration used by the symmetric forward (keys == rows, S = S^T): only tiles
+// (rb, kt >= rb) are computed, numbered row-block-major.  Row block rb starts at tile
+// ntx_tri_first(rb) and has key_tiles - rb tiles.
+NTX_HD long long ntx_tri_first(int key_tiles, int rb) {
+    return (long long)rb * key_tiles - (long long)rb * (rb - 1) / 2;
+}
+NTX_HD int ntx_tri_first_owner(long long T, int G, int key_tiles, int rb) {
+    return ntx_tile_owner(T, G, ntx_tri_first(key_tiles, rb));
+}
+NTX_HD int ntx_tri_num_slots(long long T, int G, int key_tiles, int rb) {
+    const long long f = ntx_tri_first(key_tiles, rb);
+    return ntx_tile_owner(T, G, f + (key_tiles - rb) - 1) - ntx_tile_owner(T, G, f) + 1;
+}
+
 // log2(e) / tau and friends live in one place so every kernel shifts identically:
 // e_rc = exp(s_rc - 1/tau) = exp2(dot_rc * c1 - c1),  c1 = log2(e) / tau.
 #define NTX_LOG2E 1.4426950408889634f
@@ -95,13 +109,16 @@ int ntx_simt_bwd_launch(const float* q, const float* k, const NtxDims& dm, const
                         const NtxWeights& w, float* partial, cudaStream_t st);
 int ntx_tc_fwd_launch(const __nv_bfloat16* q, const __nv_bfloat16* k, const NtxDims& dm,
                       const NtxPlan& plan, float* partial, unsigned int* counter, cudaStream_t st);
+int ntx_tc_fwd_sym_launch(const __nv_bfloat16* rows, const NtxDims& dm, const NtxPlan& plan, float* partial,
+                          float* colpart, unsigned int* counter, cudaStream_t st);
 int ntx_tc_bwd_launch(const __nv_bfloat16* q, const __nv_bfloat16* k, const NtxDims& dm,
                       const NtxPlan& plan, const NtxWeights& w, float* partial, cudaStream_t st);
 int ntx_fwd_finalize_blocks(int q_rows, int ld);   // grid of the forward finalize (one fp64 block sum each)
+// colpart != NULL: symmetric forward (upper-triangle partition, column partials added per row)
 int ntx_fwd_finalize_launch(const void* q, int dtype, const NtxDims& dm, const NtxPlan& plan,
-                            const float* partial, unsigned int* counter, double* block_sums,
-                            float* rowsum, float* pos_logit, float* row_loss, float* loss_sum,
-                            cudaStream_t st);
+                            const float* partial, const float* colpart, unsigned int* counter,
+                            double* block_sums, float* rowsum, float* pos_logit, float* row_loss,
+                            float* loss_sum, cudaStream_t st);
 int ntx_debug_indices_launch(int n_local, int rank, int32_t* self_col, int32_t* pos_col,
                              cudaStream_t st);
 int ntx_bwd_finalize_launch(const NtxDims& dm, const NtxPlan& plan, const float* partial,

@@ -51,13 +51,17 @@ template <typename T>
 __global__ void __launch_bounds__(kFwdThreads)
 fwd_finalize_kernel(const T* __restrict__ q, NtxDims dm, int lanes, int tile_rows, int key_tiles,
                     long long Tt, int G, int rows_pad, const float* __restrict__ partial,
-                    unsigned int* __restrict__ counter, double* __restrict__ block_sums,
-                    float* __restrict__ rowsum, float* __restrict__ pos_logit,
-                    float* __restrict__ row_loss, float* __restrict__ loss_sum) {
-    // rows of one block share a row block (tile_rows is a multiple of rows_per_block): one slot count
+                    const float* __restrict__ colpart, unsigned int* __restrict__ counter,
+                    double* __restrict__ block_sums, float* __restrict__ rowsum,
+                    float* __restrict__ pos_logit, float* __restrict__ row_loss,
+                    float* __restrict__ loss_sum) {
+    // rows of one block share a row block (tile_rows is a multiple of rows_per_block): one slot count.
+    // colpart != NULL: the symmetric forward's upper-triangle partition (Tt, G describe that one).
     __shared__ int ns_sh;
-    if (threadIdx.x == 0)
-        ns_sh = ntx_num_slots(Tt, G, key_tiles, (int)((long long)blockIdx.x * (kFwdThreads / lanes) / tile_rows));
+    if (threadIdx.x == 0) {
+        const int rb0 = (int)((long long)blockIdx.x * (kFwdThreads / lanes) / tile_rows);
+        ns_sh = colpart ? ntx_tri_num_slots(Tt, G, key_tiles, rb0) : ntx_num_slots(Tt, G, key_tiles, rb0);
+    }
     __syncthreads();
     double my_loss = 0.0;
     const int rows_per_block = kFwdThreads / lanes;
@@ -75,9 +79,16 @@ fwd_finalize_kernel(const T* __restrict__ q, NtxDims dm, int lanes, int tile_row
             dot = fmaf(x.x, y.x, fmaf(x.y, y.y, fmaf(x.z, y.z, fmaf(x.w, y.w, dot))));
         }
         dot = group_sum(dot, lanes);
+        // symmetric forward: what the tiles ABOVE this row's block saw in this row's column
+        float cs = 0.f;
+        if (colpart) {
+            const int rb = r / tile_rows;
+            for (int rbp = sub; rbp < rb; rbp += lanes) cs += __ldg(colpart + (size_t)rbp * rows_pad + r);
+            cs = group_sum(cs, lanes);
+        }
         if (sub == 0 && live) {
             const int ns = ns_sh;
-            float R = 0.f;
+            float R = cs;
             for (int s = 0; s < ns; ++s) R += __ldg(partial + (size_t)s * rows_pad + r);
             const float pos = dot * dm.inv_tau;
             const float l = logf(R) + dm.inv_tau - pos;
@@ -294,21 +305,23 @@ int ntx_fwd_finalize_blocks(int q_rows, int ld) {
 }
 
 int ntx_fwd_finalize_launch(const void* q, int dtype, const NtxDims& dm, const NtxPlan& plan,
-                            const float* partial, unsigned int* counter, double* block_sums,
-                            float* rowsum, float* pos_logit, float* row_loss, float* loss_sum,
-                            cudaStream_t st) {
-    const long long T = (long long)plan.row_blocks * plan.key_tiles;
+                            const float* partial, const float* colpart, unsigned int* counter,
+                            double* block_sums, float* rowsum, float* pos_logit, float* row_loss,
+                            float* loss_sum, cudaStream_t st) {
+    const long long T = colpart ? (long long)plan.row_blocks * (plan.row_blocks + 1) / 2
+                                : (long long)plan.row_blocks * plan.key_tiles;
+    const int G = colpart ? plan.fwd_grid : plan.grid;
     const int rows_pad = plan.row_blocks * plan.tile_rows;
     const int lanes = lanes_for(dm.ld / 4);
     const int grid = ntx_fwd_finalize_blocks(dm.q_rows, dm.ld);
     if (dtype == NTX_F32)
         fwd_finalize_kernel<float><<<grid, kFwdThreads, 0, st>>>(
-            (const float*)q, dm, lanes, plan.tile_rows, plan.key_tiles, T, plan.grid, rows_pad, partial,
+            (const float*)q, dm, lanes, plan.tile_rows, plan.key_tiles, T, G, rows_pad, partial, colpart,
             counter, block_sums, rowsum, pos_logit, row_loss, loss_sum);
     else
         fwd_finalize_kernel<__nv_bfloat16><<<grid, kFwdThreads, 0, st>>>(
-            (const __nv_bfloat16*)q, dm, lanes, plan.tile_rows, plan.key_tiles, T, plan.grid, rows_pad,
-            partial, counter, block_sums, rowsum, pos_logit, row_loss, loss_sum);
+            (const __nv_bfloat16*)q, dm, lanes, plan.tile_rows, plan.key_tiles, T, G, rows_pad,
+            partial, colpart, counter, block_sums, rowsum, pos_logit, row_loss, loss_sum);
     NTX_CUDA(cudaGetLastError());
     return NTX_OK;
 }

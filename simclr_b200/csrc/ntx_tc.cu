@@ -380,6 +380,335 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     if (warp == kMmaWarp) tmem_dealloc(tmem_base, kTmemCols);
 }
 
+// ============================================================================ symmetric forward
+// One rank, keys == rows: S = S^T, so only the tiles (rb, kt >= rb) are computed.  An off-diagonal
+// tile feeds the row sums of its 128 rows (registers, as in tc_fwd_kernel) AND the row sums of its
+// 128 columns: the epilogue group writes e as a bf16 tile to shared memory and a second, tiny MMA
+// (M = 128 columns x N = 16, A = E^T read MN-major from that tile, B = ones) reduces it over the
+// rows on the tensor core; lane c of the result is the column sum of key c, which the group stores
+// to colpart[rb][c].  Half the exponentials and half the similarity MMAs of the full-tile forward.
+constexpr int kSymWG = 3;                                   // epilogue groups = S buffers = column-sum slots
+constexpr int kSymThreads = kSymWG * 128 + 96;              // + producer, GEMM1 warp, column-sum warp
+constexpr int kSymNS = 2;                                   // key-tile ring; MMA loops unroll by 6 = lcm(ring, groups)
+constexpr uint32_t kSymCsCol = 384;                         // column-sum results: TMEM columns 384 + 32 * g
+struct SymCtl {
+    uint64_t q_full, q_empty, k_full[kSymNS], k_empty[kSymNS], s_full[kSymWG], s_free[kSymWG],
+        e_full[kSymWG], e_free[kSymWG], cs_full[kSymWG], cs_free[kSymWG];
+    uint32_t tmem_base;
+    alignas(16) float xch[2][kSymWG - 1][128];
+};
+
+// walks the upper-triangle tiles in row-block-major order
+struct TriIter {
+    int rb, kt, key_tiles;
+    __device__ __forceinline__ void init(long long t, int kts) {
+        key_tiles = kts;
+        rb = 0;
+        int len = kts;
+        while (t >= len) { t -= len; ++rb; --len; }
+        kt = rb + (int)t;
+    }
+    __device__ __forceinline__ bool last_in_row() const { return kt + 1 == key_tiles; }
+    __device__ __forceinline__ void next() { if (++kt == key_tiles) { ++rb; kt = rb; } }
+};
+
+template <int NDB>
+__global__ void __launch_bounds__(kSymThreads, 1)
+tc_fwd_sym_kernel(const __grid_constant__ CUtensorMap tmap, NtxDims dm, int key_tiles, long long T,
+                  int rows_pad, float* __restrict__ partial, float* __restrict__ colpart,
+                  unsigned int* __restrict__ done_counter) {
+    constexpr int NS = kSymNS;
+    constexpr uint32_t kTileBytes = NDB * kBlkBytes;
+    constexpr uint32_t kEBytes = 2 * kBlkBytes;             // [128 rows x 128 keys] bf16
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = checked_1024(smem_raw);
+    uint8_t* q_smem = smem;
+    uint8_t* k_smem = smem + kTileBytes;
+    uint8_t* e_smem = k_smem + NS * kTileBytes;
+    uint8_t* ones_smem = e_smem + kSymWG * kEBytes;         // [16 x 64] bf16 ones: one 2 KB block serves every K step
+    SymCtl* ctl = reinterpret_cast<SymCtl*>(ones_smem + 2048);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int G = gridDim.x, cta = blockIdx.x;
+    const long long t_begin = ntx_chunk_begin(T, G, cta);
+    const int n_tiles = (int)(ntx_chunk_begin(T, G, cta + 1) - t_begin);
+    constexpr int kProducerWarp = kSymWG * 4, kMmaWarp = kSymWG * 4 + 1, kCsWarp = kSymWG * 4 + 2;
+
+    if (threadIdx.x == 0) {
+        if (cta == 0) *done_counter = 0;                   // ticket of the finalize kernel
+        mbar_init(&ctl->q_full, 1);
+        mbar_init(&ctl->q_empty, 1);
+        for (int s = 0; s < NS; ++s) { mbar_init(&ctl->k_full[s], 1); mbar_init(&ctl->k_empty[s], 1); }
+        for (int b = 0; b < kSymWG; ++b) {
+            mbar_init(&ctl->s_full[b], 1);
+            mbar_init(&ctl->s_free[b], 4);
+            mbar_init(&ctl->cs_full[b], 1);
+            mbar_init(&ctl->cs_free[b], 4);
+        }
+        for (int b = 0; b < kSymWG; ++b) { mbar_init(&ctl->e_full[b], 4); mbar_init(&ctl->e_free[b], 1); }
+        fence_barrier_init();
+    }
+    for (int i = threadIdx.x; i < 2048 / 4; i += kSymThreads)
+        reinterpret_cast<uint32_t*>(ones_smem)[i] = 0x3F803F80u;       // bf16 1.0 pairs
+    fence_proxy_async_smem();
+    if (warp == kMmaWarp) tmem_alloc(&ctl->tmem_base, kTmemCols);
+    if (warp == kProducerWarp && lane == 0) tma_prefetch_desc(&tmap);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (ctl->tmem_base != 0) {
+        if (threadIdx.x == 0) printf("ntxent: unexpected TMEM base %u\n", ctl->tmem_base);
+        __trap();
+    }
+    constexpr uint32_t tmem_base = 0;
+
+    if (warp == kProducerWarp) {
+        if (elect_one()) {
+            TriIter it;
+            it.init(t_begin, key_tiles);
+            int seg = 0;
+            bool new_seg = true;
+            for (int i = 0; i < n_tiles; ++i) {
+                if (new_seg) {
+                    if (seg > 0) mbar_wait(&ctl->q_empty, (seg - 1) & 1);
+                    mbar_expect_tx(&ctl->q_full, kTileBytes);
+#pragma unroll
+                    for (int b = 0; b < NDB; ++b)
+                        tma_load_2d(q_smem + b * kBlkBytes, &tmap, b * 64, it.rb * 128, &ctl->q_full);
+                    new_seg = false;
+                }
+                const int s = i % NS;
+                mbar_wait(&ctl->k_empty[s], ((i / NS) & 1) ^ 1);
+                mbar_expect_tx(&ctl->k_full[s], kTileBytes);
+#pragma unroll
+                for (int b = 0; b < NDB; ++b)
+                    tma_load_2d(k_smem + s * kTileBytes + b * kBlkBytes, &tmap, b * 64, it.kt * 128, &ctl->k_full[s]);
+                if (it.last_in_row()) { ++seg; new_seg = true; }
+                it.next();
+            }
+        }
+    } else if (warp == kMmaWarp) {
+        // GEMM1 issuer; unrolled by 6 so stage (i % 2) and buffer (i % 3) indices are compile-time
+        TriIter it;
+        it.init(t_begin, key_tiles);
+        int seg = 0;
+        bool new_seg = true;
+        NTX_T(tm_k); NTX_T(tm_s); NTX_T(tm_issue); NTX_T(tm_total);
+        NTX_TIC(tm_total);
+        for (int i0 = 0; i0 < n_tiles; i0 += 6) {
+#pragma unroll
+            for (int jj = 0; jj < 6; ++jj) {
+                const int i = i0 + jj;
+                if (i >= n_tiles) break;
+                const int st = jj % NS, j = jj % kSymWG;
+                const bool last_of_seg = (i + 1 == n_tiles) || it.last_in_row();
+                if (new_seg) mbar_wait(&ctl->q_full, seg & 1);
+                new_seg = false;
+                { NTX_TIC(tm_k); mbar_wait(&ctl->k_full[st], (i / NS) & 1); NTX_TOC(tm_k); }
+                { NTX_TIC(tm_s); mbar_wait(&ctl->s_free[j], ((i / kSymWG) & 1) ^ 1); NTX_TOC(tm_s); }
+                tc_fence_after();
+                NTX_TIC(tm_issue);
+                if (elect_one()) {
+                    issue_gemm1<NDB>(tmem_base + j * 128, q_smem, k_smem + st * kTileBytes);
+                    mma_commit(&ctl->k_empty[st]);
+                    mma_commit(&ctl->s_full[j]);
+                    if (last_of_seg) mma_commit(&ctl->q_empty);
+                }
+                __syncwarp();
+                NTX_TOC(tm_issue);
+                if (it.last_in_row()) { ++seg; new_seg = true; }
+                it.next();
+            }
+        }
+        NTX_TOC(tm_total);
+        if (lane == 0) { NTX_TSAVE(0, tm_total); NTX_TSAVE(1, tm_k); NTX_TSAVE(2, tm_s); NTX_TSAVE(3, tm_issue); }
+    } else if (warp == kCsWarp) {
+        // column sums of every off-diagonal tile: D[c][0..15] = sum_r E[r][c] * 1
+        constexpr uint32_t idesc = instr_desc_bf16_ex(128, 16, 1, 0);
+        TriIter it;
+        it.init(t_begin, key_tiles);
+        int uses[kSymWG] = {0, 0, 0};                       // off-diagonal tiles of each group so far
+        for (int i0 = 0; i0 < n_tiles; i0 += kSymWG) {
+#pragma unroll
+            for (int j = 0; j < kSymWG; ++j) {
+                const int i = i0 + j;
+                if (i >= n_tiles) break;
+                if (it.kt != it.rb) {
+                    mbar_wait(&ctl->e_full[j], uses[j] & 1);
+                    mbar_wait(&ctl->cs_free[j], (uses[j] & 1) ^ 1);
+                    tc_fence_after();
+                    if (elect_one()) {
+                        const uint8_t* e_tile = e_smem + j * kEBytes;
+#pragma unroll
+                        for (int kk = 0; kk < 8; ++kk) {
+                            // A = E^T, MN-major: 64 keys per 128 B row, rows 128 B apart, next 64 keys 16 KB away
+                            const uint64_t a = smem_desc_sw128(smem_u32(e_tile + kk * 2048), kBlkBytes, 1024);
+                            const uint64_t b = smem_desc_sw128(smem_u32(ones_smem + (kk & 3) * 32), 16, 1024);
+                            mma_bf16_ss(tmem_base + kSymCsCol + j * 32, a, b, idesc, kk ? 1u : 0u);
+                        }
+                        mma_commit(&ctl->e_free[j]);
+                        mma_commit(&ctl->cs_full[j]);
+                    }
+                    __syncwarp();
+                    ++uses[j];
+                }
+                it.next();
+            }
+        }
+    } else {
+        // ---------------------------------------------------------------- epilogue groups
+        const int g = warp >> 2;
+        const int row_in_tile = (warp & 3) * 32 + lane;
+        const uint32_t t_lane = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
+        const uint32_t taddr = t_lane + g * 128;
+        const float c1 = dm.c1, nc1 = -dm.c1;
+        const f32x2 c1x2 = pack2(c1, c1), nc1x2 = pack2(nc1, nc1);
+        const uint32_t sw = (uint32_t)(row_in_tile & 7);
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+        f32x2 pacc[2] = {pack2(0.f, 0.f), pack2(0.f, 0.f)};
+        int flushes = 0, own = 0, e_uses = 0, cs_uses = 0;
+        bool pending = false;                               // a column-sum result of this group not yet stored
+        int pend_rb = 0, pend_kt = 0;
+        NTX_T(te_total); NTX_T(te_wait); NTX_T(te_ef); NTX_T(te_loop); NTX_T(te_cs);
+        NTX_TIC(te_total);
+
+        auto flush = [&](int rb) {
+            float p0, p1, p2, p3;
+            unpack2(pacc[0], p0, p1);
+            unpack2(pacc[1], p2, p3);
+            float rs = ((acc[0] + acc[1]) + (acc[2] + acc[3])) + ((p0 + p1) + (p2 + p3));
+            pacc[0] = pacc[1] = pack2(0.f, 0.f);
+            float (*x)[128] = ctl->xch[flushes & 1];
+            if (g > 0) x[g - 1][row_in_tile] = rs;
+            named_bar_sync(1, kSymWG * 128);
+            if (g == 0) {
+#pragma unroll
+                for (int o = 0; o < kSymWG - 1; ++o) rs += x[o][row_in_tile];
+                const int slot = cta - ntx_tri_first_owner(T, G, key_tiles, rb);
+                partial[(size_t)slot * rows_pad + rb * 128 + row_in_tile] = rs;
+            }
+            ++flushes;
+            acc[0] = acc[1] = acc[2] = acc[3] = 0.f;
+        };
+        // lane c of the column-sum MMA result = sum over this tile's rows of e[., c]
+        auto store_colsum = [&]() {
+            mbar_wait(&ctl->cs_full[g], cs_uses & 1);
+            ++cs_uses;
+            tc_fence_after();
+            const uint32_t v = tmem_ld_32x1(t_lane + kSymCsCol + g * 32);
+            tmem_ld_wait();
+            colpart[(size_t)pend_rb * rows_pad + pend_kt * 128 + row_in_tile] = __uint_as_float(v);
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&ctl->cs_free[g]);
+            pending = false;
+        };
+
+        TriIter it;
+        it.init(t_begin, key_tiles);
+        int turn = 0;
+        for (int i = 0; i < n_tiles; ++i) {
+            const int rb = it.rb, kt = it.kt;
+            const bool last_of_seg = (i + 1 == n_tiles) || it.last_in_row();
+            const bool offdiag = kt != rb;
+            if (turn == g) {
+                { NTX_TIC(te_cs); if (pending) store_colsum(); NTX_TOC(te_cs); }
+                { NTX_TIC(te_wait); mbar_wait(&ctl->s_full[g], own & 1); NTX_TOC(te_wait); }
+                ++own;
+                tc_fence_after();
+                const bool row_ok = rb * 128 + row_in_tile < dm.q_rows;
+                const bool edge = !offdiag || (kt * 128 + 128 > dm.k_rows) || (rb * 128 + 128 > dm.q_rows);
+                const int self = rb * 128 + row_in_tile;
+                uint8_t* e_row = e_smem + g * kEBytes + row_in_tile * 128;         // this group's own E tile
+                { NTX_TIC(te_ef); if (offdiag) mbar_wait(&ctl->e_free[g], (e_uses & 1) ^ 1); NTX_TOC(te_ef); }   // column-sum MMA that read it is done
+                NTX_TIC(te_loop);
+                uint32_t v[2][32];
+                tmem_ld_32x32(taddr, v[0]);
+#pragma unroll
+                for (int ch = 0; ch < 4; ++ch) {
+                    tmem_ld_wait_dep(v[ch & 1]);
+                    if (ch < 3) {
+                        tmem_ld_32x32(taddr + (ch + 1) * 32, v[(ch + 1) & 1]);
+                    } else {   // the whole tile is in registers: hand the S buffer back
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&ctl->s_free[g]);
+                    }
+                    if (!edge) {
+                        // interior off-diagonal tile: packed arithmetic, no masks, E tile always written
+#pragma unroll
+                        for (int j8 = 0; j8 < 4; ++j8) {       // 8 keys -> one 16-byte chunk of the E tile
+                            uint32_t packed[4];
+#pragma unroll
+                            for (int h = 0; h < 4; ++h) {
+                                const int j = j8 * 8 + h * 2;
+                                const f32x2 x = fma2(pack2(__uint_as_float(v[ch & 1][j]),
+                                                           __uint_as_float(v[ch & 1][j + 1])), c1x2, nc1x2);
+                                const bool poly = NTX_FWD_POLY > 0 && (((j8 * 4 + h) * NTX_FWD_POLY) & 3) < NTX_FWD_POLY;
+                                const f32x2 e = poly ? ex2_pair_poly(x) : ex2_pair_mufu(x);
+                                pacc[h & 1] = add2(pacc[h & 1], e);
+                                float e0, e1;
+                                unpack2(e, e0, e1);
+                                __nv_bfloat162 hh = __floats2bfloat162_rn(e0, e1);
+                                packed[h] = *reinterpret_cast<uint32_t*>(&hh);
+                            }
+                            const int cg = ch * 4 + j8;         // 16-byte chunk index along the 128 keys
+                            uint8_t* dst = e_row + (cg >> 3) * kBlkBytes + ((((uint32_t)cg & 7u) ^ sw) << 4);
+                            *reinterpret_cast<uint4*>(dst) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+                        }
+                    } else {
+                        // diagonal tile (self column, no E tile) or a tile with rows / keys past the end
+#pragma unroll
+                        for (int j8 = 0; j8 < 4; ++j8) {
+                            uint32_t packed[4];
+#pragma unroll
+                            for (int h = 0; h < 4; ++h) {
+                                const int j = j8 * 8 + h * 2;
+                                const int col = kt * 128 + ch * 32 + j;
+                                float e0 = ex2(fmaf(__uint_as_float(v[ch & 1][j]), c1, nc1));
+                                float e1 = ex2(fmaf(__uint_as_float(v[ch & 1][j + 1]), c1, nc1));
+                                if (col == self || col >= dm.k_rows || !row_ok) e0 = 0.f;   // mask of loss.py:38,46-47
+                                if (col + 1 == self || col + 1 >= dm.k_rows || !row_ok) e1 = 0.f;
+                                acc[h] += e0 + e1;
+                                __nv_bfloat162 hh = __floats2bfloat162_rn(e0, e1);
+                                packed[h] = *reinterpret_cast<uint32_t*>(&hh);
+                            }
+                            if (offdiag) {
+                                const int cg = ch * 4 + j8;
+                                uint8_t* dst = e_row + (cg >> 3) * kBlkBytes + ((((uint32_t)cg & 7u) ^ sw) << 4);
+                                *reinterpret_cast<uint4*>(dst) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+                            }
+                        }
+                    }
+                }
+                NTX_TOC(te_loop);
+                if (offdiag) {
+                    fence_proxy_async_smem();       // generic-proxy stores -> visible to tcgen05.mma
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&ctl->e_full[g]);
+                    ++e_uses;
+                    pending = true;
+                    pend_rb = rb;
+                    pend_kt = kt;
+                }
+            }
+            if (last_of_seg) flush(rb);
+            it.next();
+            if (++turn == kSymWG) turn = 0;
+        }
+        if (pending) store_colsum();
+        NTX_TOC(te_total);
+        if (threadIdx.x == 0) {
+            NTX_TSAVE(4, te_total); NTX_TSAVE(5, te_wait); NTX_TSAVE(6, te_ef); NTX_TSAVE(7, te_loop);
+            NTX_TSAVE(8, te_cs);
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == kMmaWarp) tmem_dealloc(tmem_base, kTmemCols);
+}
+
 // ============================================================================ backward
 // NDB = 1, 2 (d_pad 64, 128): dZ in TMEM columns [0, 128), three S/C buffers, three groups.
 // NDB = 4       (d_pad 256) : dZ in TMEM columns [0, 256), two S/C buffers, two groups.
@@ -757,6 +1086,31 @@ int ntx_tc_fwd_launch(const __nv_bfloat16* q, const __nv_bfloat16* k, const NtxD
     }
     ntx_set_error("tensor-core forward: padded feature dim %d not built", plan.d_pad);
     return NTX_E_UNSUPPORTED;
+}
+
+int ntx_tc_fwd_sym_launch(const __nv_bfloat16* rows, const NtxDims& dm, const NtxPlan& plan, float* partial,
+                          float* colpart, unsigned int* counter, cudaStream_t st) {
+    CUtensorMap m;
+    int rc = make_rows_tmap(&m, rows, dm.q_rows, dm.ld);
+    if (rc) return rc;
+    const long long T = (long long)plan.row_blocks * (plan.row_blocks + 1) / 2;
+    const int rows_pad = plan.row_blocks * plan.tile_rows;
+    if (plan.d_pad == 64) {
+        const size_t smem = (size_t)(1 + kSymNS) * 1 * kBlkBytes + kSymWG * 2 * kBlkBytes + 2048 + sizeof(SymCtl);
+        NTX_CUDA(cudaFuncSetAttribute(tc_fwd_sym_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        tc_fwd_sym_kernel<1><<<plan.fwd_grid, kSymThreads, smem, st>>>(m, dm, plan.row_blocks, T, rows_pad, partial,
+                                                                       colpart, counter);
+    } else if (plan.d_pad == 128) {
+        const size_t smem = (size_t)(1 + kSymNS) * 2 * kBlkBytes + kSymWG * 2 * kBlkBytes + 2048 + sizeof(SymCtl);
+        NTX_CUDA(cudaFuncSetAttribute(tc_fwd_sym_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        tc_fwd_sym_kernel<2><<<plan.fwd_grid, kSymThreads, smem, st>>>(m, dm, plan.row_blocks, T, rows_pad, partial,
+                                                                       colpart, counter);
+    } else {
+        ntx_set_error("symmetric forward: padded feature dim %d not built", plan.d_pad);
+        return NTX_E_UNSUPPORTED;
+    }
+    NTX_CUDA(cudaGetLastError());
+    return NTX_OK;
 }
 
 int ntx_tc_bwd_launch(const __nv_bfloat16* q, const __nv_bfloat16* k, const NtxDims& dm,

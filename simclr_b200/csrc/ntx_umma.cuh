@@ -176,4 +176,15 @@ __host__ __device__ constexpr uint32_t instr_desc_bf16(int m, int n, int b_mn_ma
            ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 
+// same with an MN-major A operand (A read from a [K][M] row-major smem tile)
+__host__ __device__ constexpr uint32_t instr_desc_bf16_ex(int m, int n, int a_mn_major, int b_mn_major) {
+    return instr_desc_bf16(m, n, b_mn_major) | ((uint32_t)a_mn_major << 15);
+}
+// 32 lanes x 1 column: thread i of the warp gets lane (base + i)
+__device__ __forceinline__ uint32_t tmem_ld_32x1(uint32_t taddr) {
+    uint32_t r;
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(r) : "r"(taddr) : "memory");
+    return r;
+}
+
 }  // namespace umma
