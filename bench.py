@@ -42,6 +42,9 @@ def parse():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="c4", choices=["c4", "c5"],
+                    help="c4 = BASELINE configs[3] (the metric's config, default); c5 = configs[4]: "
+                         "global batch 32768, d=256 (documentation runs only)")
     ap.add_argument("--no-graphs", action="store_true",
                     help="launch every step eagerly instead of replaying CUDA graphs of the module")
     return ap.parse_args()
@@ -49,7 +52,7 @@ def parse():
 
 def workload_config(world, eager=False):
     return {"workload": f"NT-Xent fwd+bwd, global batch {N_GLOBAL} pairs ({2 * N_GLOBAL} views), d={DIM}, "
-                        f"tau={TAU}, bf16 (BASELINE configs[3])",
+                        f"tau={TAU}, bf16 (BASELINE configs[{3 if N_GLOBAL == 8192 else 4}])",
             "global_batch": N_GLOBAL, "d": DIM, "temperature": TAU,
             "parallelism": f"rows sharded over {world} rank(s), keys all-gathered" if world > 1 else "single GPU",
             "l2": "flushed between timed steps (256 MiB write)",
@@ -355,11 +358,11 @@ def run_ours(args):
                     "h2d_bytes_per_step": 2 * N_GLOBAL * DIM * 2, "d2h_bytes_per_step": 2 * world,
                     "ms_per_step": e2e_ms / K, "loss": last_loss},
             "gpu_launches": KERNELS_PER_STEP * K,
-            "roofline": {"bound": "tensor", "kernel": "tc_bwd_kernel<2>", "achieved": achieved, "peak": peak,
+            "roofline": {"bound": "tensor", "kernel": f"tc_bwd_kernel<{DIM // 64}>", "achieved": achieved, "peak": peak,
                          "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
                          "peak_source": peak_src, "algorithmic_flops_per_launch": bwd_flops,
                          "kernel_ms": bwd_ms,
-                         "fwd_kernel": {"kernel": "tc_fwd_kernel<2>", "kernel_ms": fwd_ms,
+                         "fwd_kernel": {"kernel": ("tc_fwd_sym_kernel" if world == 1 and DIM <= 128 else "tc_fwd_kernel") + f"<{DIM // 64}>", "kernel_ms": fwd_ms,
                                         "achieved": fwd_flops / (fwd_ms * 1e-3) / 1e12},
                          "whole_step_frac": 18.0 * N_GLOBAL * N_GLOBAL * DIM / world / (ms_per_step * 1e-3) / 1e12 / peak},
             "clocks": clocks.summary(),
@@ -376,4 +379,6 @@ def run_ours(args):
 
 if __name__ == "__main__":
     a = parse()
+    if a.workload == "c5":
+        N_GLOBAL, DIM = 32768, 256
     sys.exit(run_reference(a) if a.impl == "reference" else run_ours(a))
