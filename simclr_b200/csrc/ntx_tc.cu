@@ -121,6 +121,9 @@ __device__ __forceinline__ f32x2 ex2_pair_poly(f32x2 x) {
 #define NTX_FWD_POLY 1      // of every 4 PAIRS of exponentials in the forward epilogue, how many use the polynomial
                             // (B200, N=8192 D=128: 1 -> 75.4 us, 2 -> 79.2 us, 3 -> 90.5 us; scalar code without any: 86.6 us)
 #endif
+#ifndef NTX_SYM_POLY
+#define NTX_SYM_POLY 0      // same for the symmetric forward, whose FMA pipe also packs the bf16 tile (0 -> 67.9 us, 1 -> 72.4 us, 2 -> 82.6 us)
+#endif
 #ifndef NTX_BWD_POLY
 #define NTX_BWD_POLY 1      // same (pairs of every 4) for the backward epilogue (0 -> 115.2 us, 1 -> 112.7 us)
 #endif
@@ -644,7 +647,7 @@ tc_fwd_sym_kernel(const __grid_constant__ CUtensorMap tmap, NtxDims dm, int key_
                                 const int j = j8 * 8 + h * 2;
                                 const f32x2 x = fma2(pack2(__uint_as_float(v[ch & 1][j]),
                                                            __uint_as_float(v[ch & 1][j + 1])), c1x2, nc1x2);
-                                const bool poly = NTX_FWD_POLY > 0 && (((j8 * 4 + h) * NTX_FWD_POLY) & 3) < NTX_FWD_POLY;
+                                const bool poly = NTX_SYM_POLY > 0 && (((j8 * 4 + h) * NTX_SYM_POLY) & 3) < NTX_SYM_POLY;
                                 const f32x2 e = poly ? ex2_pair_poly(x) : ex2_pair_mufu(x);
                                 pacc[h & 1] = add2(pacc[h & 1], e);
                                 float e0, e1;
