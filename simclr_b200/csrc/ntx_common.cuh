@@ -64,10 +64,15 @@ NTX_HD int ntx_num_slots(long long T, int G, int key_tiles, int rb) {
 }
 
 // Upper-triangle enumeration used by the symmetric forward (keys == rows, S = S^T): only tiles
-// (rb, kt >= rb) are computed, numbered row-block-major.  Row block rb starts at tile
-// ntx_tri_first(rb) and has key_tiles - rb tiles.
+// (rb, kt >= rb) are computed.  Row block rb has key_tiles - rb of them, so the long rows are paired with
+// the short ones: the order is 0, n-1, 1, n-2, ... and every pair holds n + 1 tiles.  An equal share of
+// the tile list then also holds an equal share of row-block changes and diagonal tiles for every CTA
+// (numbered 0, 1, 2, ... the last CTA got all the short rows: ~10 row-block changes against ~1).
+// Row block rb starts at tile ntx_tri_first(rb); its tiles are contiguous.
 NTX_HD long long ntx_tri_first(int key_tiles, int rb) {
-    return (long long)rb * key_tiles - (long long)rb * (rb - 1) / 2;
+    const int partner = key_tiles - 1 - rb;
+    return rb <= partner ? (long long)rb * (key_tiles + 1)                                   // first of its pair
+                         : (long long)partner * (key_tiles + 1) + (key_tiles - partner);     // after its partner
 }
 NTX_HD int ntx_tri_first_owner(long long T, int G, int key_tiles, int rb) {
     return ntx_tile_owner(T, G, ntx_tri_first(key_tiles, rb));

@@ -401,18 +401,23 @@ struct SymCtl {
     alignas(16) float xch[2][kSymWG - 1][128];
 };
 
-// walks the upper-triangle tiles in row-block-major order
+// walks the upper-triangle tiles in the paired order of ntx_tri_first
 struct TriIter {
     int rb, kt, key_tiles;
     __device__ __forceinline__ void init(long long t, int kts) {
         key_tiles = kts;
-        rb = 0;
-        int len = kts;
-        while (t >= len) { t -= len; ++rb; --len; }
-        kt = rb + (int)t;
+        const int v = (int)(t / (kts + 1)), off = (int)(t - (long long)v * (kts + 1));   // pair, offset in the pair
+        if (off < kts - v) { rb = v; kt = v + off; }
+        else { rb = kts - 1 - v; kt = rb + off - (kts - v); }
     }
     __device__ __forceinline__ bool last_in_row() const { return kt + 1 == key_tiles; }
-    __device__ __forceinline__ void next() { if (++kt == key_tiles) { ++rb; kt = rb; } }
+    __device__ __forceinline__ void next() {
+        if (++kt == key_tiles) {            // next row block in the order 0, n-1, 1, n-2, ...
+            const int partner = key_tiles - 1 - rb;
+            rb = rb < partner ? partner : partner + 1;
+            kt = rb;
+        }
+    }
 };
 
 template <int NDB>
