@@ -262,3 +262,40 @@ def test_training_step_call_pattern(dev):
         opt.step()                                                           # main.py:116
         losses.append(float(loss.detach()))
     assert all(np.isfinite(losses))
+
+
+@pytest.mark.parametrize("n,d,tau", [(192, 64, 0.5), (320, 128, 0.2), (1100, 96, 0.1), (129, 128, 0.5),
+                                      (4032, 128, 0.07)])
+def test_symmetric_forward_matches_full_tile_forward_and_oracle(n, d, tau, dev):
+    """The symmetric forward (upper-triangle tiles, long and short row blocks paired, column sums by a
+    ones-vector MMA) against the full-tile forward on the same rows, and both against the fp64 oracle:
+    odd and even numbers of row blocks, ragged last blocks, two row blocks only."""
+    from simclr_b200 import _cabi
+    be = _cabi.Backend()
+    g = torch.Generator().manual_seed(1000 + n)
+    a = torch.randn(n, d, generator=g).bfloat16()
+    b = (torch.randn(n, d, generator=g) + 0.3 * a.float()).bfloat16()
+    q_rows = 2 * n
+    ld = be.row_pitch(d, torch.bfloat16)
+    plan = be.plan(q_rows, q_rows, d, torch.bfloat16)
+    assert plan.fwd_symmetric == 1 and plan.fwd_ws_bytes > plan.fwd_ws_bytes_min
+    rows = torch.empty(q_rows, ld, dtype=torch.bfloat16, device=dev)
+    inv = torch.empty(q_rows, device=dev)
+    be.l2norm(a.to(dev), b.to(dev), rows, inv)
+    outs = []
+    for ws_bytes in (plan.fwd_ws_bytes, plan.fwd_ws_bytes_min):          # symmetric, then every tile
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        out = torch.full((3, q_rows), float("nan"), device=dev)
+        out_sum = torch.full((2,), float("nan"), device=dev)
+        be.fwd(rows, rows, d, (n, 1, 0), tau, out[0], out[1], out[2], out_sum, ws)
+        torch.cuda.synchronize()
+        outs.append((out.cpu().numpy(), out_sum.cpu().numpy()))
+    (sym, sym_sum), (full, full_sum) = outs
+    assert np.isfinite(sym).all() and np.isfinite(full).all()
+    assert np.array_equal(sym[1], full[1])                                # positive logits: same arithmetic
+    assert rel_err(sym[0], full[0]) < 4e-3                                # row sums: bf16 column contributions
+    assert rel_err(sym[2], full[2]) < 4e-3
+    ref = orc.ntxent_rows_fp64(a.float().numpy(), b.float().numpy(), tau, weights=orc.weights_for("mean", n))
+    assert rel_err(sym[2].reshape(2, n), ref["loss"]) < BF16_TOL
+    assert rel_err(full[2].reshape(2, n), ref["loss"]) < BF16_TOL
+    assert abs(sym_sum[1] - ref["loss"].mean()) < BF16_TOL * abs(ref["loss"].mean())
