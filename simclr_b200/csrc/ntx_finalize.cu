@@ -65,6 +65,22 @@ fwd_finalize_kernel(const T* __restrict__ q, NtxDims dm, int lanes, int tile_row
     __syncthreads();
     double my_loss = 0.0;
     const int rows_per_block = kFwdThreads / lanes;
+    // Row sums first, with the block laid out rows-fastest so that a warp reads 32 consecutive rows of one
+    // slot (or of one row block's column partials): thread t adds the terms part, part + lanes, ... of row
+    // t % rows_per_block; the `lanes` parts of a row are then added in part order.
+    __shared__ float rs_sh[kFwdThreads];
+    {
+        const int row_local = threadIdx.x % rows_per_block, part = threadIdx.x / rows_per_block;
+        const int r2 = min(blockIdx.x * rows_per_block + row_local, dm.q_rows - 1);
+        float c = 0.f;
+        if (colpart) {          // symmetric forward: what the tiles ABOVE this row's block saw in this row's column
+            const int rb = r2 / tile_rows;
+            for (int rbp = part; rbp < rb; rbp += lanes) c += __ldg(colpart + (size_t)rbp * rows_pad + r2);
+        }
+        for (int sl = part; sl < ns_sh; sl += lanes) c += __ldg(partial + (size_t)sl * rows_pad + r2);
+        rs_sh[part * rows_per_block + row_local] = c;
+    }
+    __syncthreads();
     const int sub = threadIdx.x % lanes;
     const int r_raw = blockIdx.x * rows_per_block + threadIdx.x / lanes;
     const bool live = r_raw < dm.q_rows;
@@ -79,17 +95,9 @@ fwd_finalize_kernel(const T* __restrict__ q, NtxDims dm, int lanes, int tile_row
             dot = fmaf(x.x, y.x, fmaf(x.y, y.y, fmaf(x.z, y.z, fmaf(x.w, y.w, dot))));
         }
         dot = group_sum(dot, lanes);
-        // symmetric forward: what the tiles ABOVE this row's block saw in this row's column
-        float cs = 0.f;
-        if (colpart) {
-            const int rb = r / tile_rows;
-            for (int rbp = sub; rbp < rb; rbp += lanes) cs += __ldg(colpart + (size_t)rbp * rows_pad + r);
-            cs = group_sum(cs, lanes);
-        }
         if (sub == 0 && live) {
-            const int ns = ns_sh;
-            float R = cs;
-            for (int s = 0; s < ns; ++s) R += __ldg(partial + (size_t)s * rows_pad + r);
+            float R = 0.f;
+            for (int part = 0; part < lanes; ++part) R += rs_sh[part * rows_per_block + threadIdx.x / lanes];
             const float pos = dot * dm.inv_tau;
             const float l = logf(R) + dm.inv_tau - pos;
             rowsum[r] = R;
