@@ -11,6 +11,14 @@
 
 static thread_local char g_err[512] = "";
 
+bool ntx_pdl_enabled() {
+    static const bool on = [] {
+        const char* e = getenv("NTXENT_NO_PDL");
+        return !(e && e[0] && e[0] != '0');
+    }();
+    return on;
+}
+
 void ntx_set_error(const char* fmt, ...) {
     va_list ap;
     va_start(ap, fmt);

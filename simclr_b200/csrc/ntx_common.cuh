@@ -82,6 +82,32 @@ NTX_HD int ntx_tri_num_slots(long long T, int G, int key_tiles, int rb) {
     return ntx_tile_owner(T, G, f + (key_tiles - rb) - 1) - ntx_tile_owner(T, G, f) + 1;
 }
 
+// Programmatic dependent launch: a kernel launched through ntx_launch_dep may start while the previous kernel
+// on the stream is still running; it does its set-up (barriers, TMEM, descriptor prefetch), then ntx_dep_wait()
+// returns once that previous kernel has completed and its writes are visible.  Every kernel launched this way
+// calls ntx_dep_wait() before it touches global memory, and ntx_dep_trigger() right at its start so that the
+// kernel after it can be staged early.  NTXENT_NO_PDL=1 in the environment turns the launch attribute off.
+#ifdef __CUDACC__
+__device__ __forceinline__ void ntx_dep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void ntx_dep_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+bool ntx_pdl_enabled();
+template <typename... KArgs, typename... Args>
+inline cudaError_t ntx_launch_dep(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                  Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = ntx_pdl_enabled() ? 1 : 0;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#endif
+
 // log2(e) / tau and friends live in one place so every kernel shifts identically:
 // e_rc = exp(s_rc - 1/tau) = exp2(dot_rc * c1 - c1),  c1 = log2(e) / tau.
 #define NTX_LOG2E 1.4426950408889634f

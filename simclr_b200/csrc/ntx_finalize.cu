@@ -55,6 +55,8 @@ fwd_finalize_kernel(const T* __restrict__ q, NtxDims dm, int lanes, int tile_row
                     double* __restrict__ block_sums, float* __restrict__ rowsum,
                     float* __restrict__ pos_logit, float* __restrict__ row_loss,
                     float* __restrict__ loss_sum) {
+    ntx_dep_trigger();
+    ntx_dep_wait();
     // rows of one block share a row block (tile_rows is a multiple of rows_per_block): one slot count.
     // colpart != NULL: the symmetric forward's upper-triangle partition (Tt, G describe that one).
     __shared__ int ns_sh;
@@ -160,6 +162,8 @@ template <typename TIn, int kMaxV>
 __global__ void __launch_bounds__(kThreads)
 bwd_finalize_vec_kernel(BwdFinArgs A, int lanes, const TIn* __restrict__ view0,
                         const TIn* __restrict__ view1, TIn* __restrict__ dview0, TIn* __restrict__ dview1) {
+    ntx_dep_trigger();
+    ntx_dep_wait();
     const NtxDims& dm = A.dm;
     const int rows_per_block = kThreads / lanes;
     // rows of one block share a row block (tile_rows is a multiple of rows_per_block): one slot count
@@ -281,14 +285,14 @@ int launch_bwd_finalize(const BwdFinArgs& A, const void* view0, const void* view
         const int lanes = lanes_for(d / 4);
         const int grid = (A.dm.q_rows + kThreads / lanes - 1) / (kThreads / lanes);
         if (d <= 128)
-            bwd_finalize_vec_kernel<TIn, 1><<<grid, kThreads, 0, st>>>(A, lanes, (const TIn*)view0, (const TIn*)view1,
-                                                                       (TIn*)dview0, (TIn*)dview1);
+            NTX_CUDA(ntx_launch_dep(bwd_finalize_vec_kernel<TIn, 1>, grid, kThreads, 0, st, A, lanes, (const TIn*)view0,
+                                    (const TIn*)view1, (TIn*)dview0, (TIn*)dview1));
         else if (d <= 256)
-            bwd_finalize_vec_kernel<TIn, 2><<<grid, kThreads, 0, st>>>(A, lanes, (const TIn*)view0, (const TIn*)view1,
-                                                                       (TIn*)dview0, (TIn*)dview1);
+            NTX_CUDA(ntx_launch_dep(bwd_finalize_vec_kernel<TIn, 2>, grid, kThreads, 0, st, A, lanes, (const TIn*)view0,
+                                    (const TIn*)view1, (TIn*)dview0, (TIn*)dview1));
         else
-            bwd_finalize_vec_kernel<TIn, 8><<<grid, kThreads, 0, st>>>(A, lanes, (const TIn*)view0, (const TIn*)view1,
-                                                                       (TIn*)dview0, (TIn*)dview1);
+            NTX_CUDA(ntx_launch_dep(bwd_finalize_vec_kernel<TIn, 8>, grid, kThreads, 0, st, A, lanes, (const TIn*)view0,
+                                    (const TIn*)view1, (TIn*)dview0, (TIn*)dview1));
     } else {
         const int grid = (A.dm.q_rows + kThreads / 32 - 1) / (kThreads / 32);
         bwd_finalize_kernel<TIn><<<grid, kThreads, 0, st>>>(A, (const TIn*)view0, (const TIn*)view1, (TIn*)dview0,
@@ -323,14 +327,13 @@ int ntx_fwd_finalize_launch(const void* q, int dtype, const NtxDims& dm, const N
     const int lanes = lanes_for(dm.ld / 4);
     const int grid = ntx_fwd_finalize_blocks(dm.q_rows, dm.ld);
     if (dtype == NTX_F32)
-        fwd_finalize_kernel<float><<<grid, kFwdThreads, 0, st>>>(
-            (const float*)q, dm, lanes, plan.tile_rows, plan.key_tiles, T, G, rows_pad, partial, colpart,
-            counter, block_sums, rowsum, pos_logit, row_loss, loss_sum);
+        NTX_CUDA(ntx_launch_dep(fwd_finalize_kernel<float>, grid, kFwdThreads, 0, st, (const float*)q, dm, lanes,
+                                plan.tile_rows, plan.key_tiles, T, G, rows_pad, partial, colpart, counter,
+                                block_sums, rowsum, pos_logit, row_loss, loss_sum));
     else
-        fwd_finalize_kernel<__nv_bfloat16><<<grid, kFwdThreads, 0, st>>>(
-            (const __nv_bfloat16*)q, dm, lanes, plan.tile_rows, plan.key_tiles, T, G, rows_pad,
-            partial, colpart, counter, block_sums, rowsum, pos_logit, row_loss, loss_sum);
-    NTX_CUDA(cudaGetLastError());
+        NTX_CUDA(ntx_launch_dep(fwd_finalize_kernel<__nv_bfloat16>, grid, kFwdThreads, 0, st,
+                                (const __nv_bfloat16*)q, dm, lanes, plan.tile_rows, plan.key_tiles, T, G, rows_pad,
+                                partial, colpart, counter, block_sums, rowsum, pos_logit, row_loss, loss_sum));
     return NTX_OK;
 }
 

@@ -62,6 +62,8 @@ template <typename TIn, typename TOut, bool kVector>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 l2norm_kernel(const TIn* __restrict__ view0, const TIn* __restrict__ view1, int n, int d,
               TOut* __restrict__ rows, int ld, float* __restrict__ inv_norm, int lanes) {
+    ntx_dep_trigger();
+    ntx_dep_wait();
     const int sub = threadIdx.x % lanes;
     const int rows_per_block = kWarpsPerBlock * 32 / lanes;
     const int r_raw = blockIdx.x * rows_per_block + threadIdx.x / lanes;
@@ -122,12 +124,11 @@ int launch(const void* v0, const void* v1, int n, int d, void* rows, int ld, flo
     const int rows_per_block = kWarpsPerBlock * 32 / lanes;
     const int grid = (2 * n + rows_per_block - 1) / rows_per_block;
     if (vec)
-        l2norm_kernel<TIn, TOut, true><<<grid, kWarpsPerBlock * 32, 0, st>>>(
-            (const TIn*)v0, (const TIn*)v1, n, d, (TOut*)rows, ld, inv_norm, lanes);
+        NTX_CUDA(ntx_launch_dep(l2norm_kernel<TIn, TOut, true>, grid, kWarpsPerBlock * 32, 0, st, (const TIn*)v0,
+                                (const TIn*)v1, n, d, (TOut*)rows, ld, inv_norm, lanes));
     else
-        l2norm_kernel<TIn, TOut, false><<<grid, kWarpsPerBlock * 32, 0, st>>>(
-            (const TIn*)v0, (const TIn*)v1, n, d, (TOut*)rows, ld, inv_norm, lanes);
-    NTX_CUDA(cudaGetLastError());
+        NTX_CUDA(ntx_launch_dep(l2norm_kernel<TIn, TOut, false>, grid, kWarpsPerBlock * 32, 0, st, (const TIn*)v0,
+                                (const TIn*)v1, n, d, (TOut*)rows, ld, inv_norm, lanes));
     return NTX_OK;
 }
 

@@ -212,6 +212,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     constexpr int NS = FwdCfg<NDB>::NS;
     constexpr uint32_t kTileBytes = NDB * kBlkBytes;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
+    ntx_dep_trigger();
     uint8_t* smem = checked_1024(smem_raw);
     uint8_t* q_smem = smem;
     uint8_t* k_smem = smem + kTileBytes;
@@ -224,7 +225,6 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     constexpr int kProducerWarp = kFwdWG * 4, kMmaWarp = kFwdWG * 4 + 1;   // MMA warps: kMmaWarp, kMmaWarp + 1
 
     if (threadIdx.x == 0) {
-        if (cta == 0) *done_counter = 0;                   // ticket of the finalize kernel
         mbar_init(&ctl->q_full, 1);
         mbar_init(&ctl->q_empty, 2);                       // both MMA warps release the Q tile
         for (int s = 0; s < NS; ++s) { mbar_init(&ctl->k_full[s], 1); mbar_init(&ctl->k_empty[s], 1); }
@@ -243,6 +243,9 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         __trap();
     }
     constexpr uint32_t tmem_base = 0;
+    // everything above overlapped the tail of the previous kernel on the stream; from here on its results are read
+    ntx_dep_wait();
+    if (threadIdx.x == 0 && cta == 0) *done_counter = 0;    // ticket of the finalize kernel
 
     if (warp == kProducerWarp) {
         if (elect_one())
@@ -429,6 +432,7 @@ tc_fwd_sym_kernel(const __grid_constant__ CUtensorMap tmap, NtxDims dm, int key_
     constexpr uint32_t kTileBytes = NDB * kBlkBytes;
     constexpr uint32_t kEBytes = 2 * kBlkBytes;             // [128 rows x 128 keys] bf16
     extern __shared__ __align__(1024) uint8_t smem_raw[];
+    ntx_dep_trigger();
     uint8_t* smem = checked_1024(smem_raw);
     uint8_t* q_smem = smem;
     uint8_t* k_smem = smem + kTileBytes;
@@ -443,7 +447,6 @@ tc_fwd_sym_kernel(const __grid_constant__ CUtensorMap tmap, NtxDims dm, int key_
     constexpr int kProducerWarp = kSymWG * 4, kMmaWarp = kSymWG * 4 + 1, kCsWarp = kSymWG * 4 + 2;
 
     if (threadIdx.x == 0) {
-        if (cta == 0) *done_counter = 0;                   // ticket of the finalize kernel
         mbar_init(&ctl->q_full, 1);
         mbar_init(&ctl->q_empty, 1);
         for (int s = 0; s < NS; ++s) { mbar_init(&ctl->k_full[s], 1); mbar_init(&ctl->k_empty[s], 1); }
@@ -469,6 +472,9 @@ tc_fwd_sym_kernel(const __grid_constant__ CUtensorMap tmap, NtxDims dm, int key_
         __trap();
     }
     constexpr uint32_t tmem_base = 0;
+    // everything above overlapped the tail of the previous kernel on the stream; from here on its results are read
+    ntx_dep_wait();
+    if (threadIdx.x == 0 && cta == 0) *done_counter = 0;    // ticket of the finalize kernel
 
     if (warp == kProducerWarp) {
         if (elect_one()) {
@@ -782,6 +788,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     constexpr uint32_t kSCol = Cfg::kSCol;
     constexpr uint32_t kTileBytes = NDB * kBlkBytes;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
+    ntx_dep_trigger();
     uint8_t* smem = checked_1024(smem_raw);
     uint8_t* q_smem = smem;
     uint8_t* k_smem = smem + kTileBytes;
@@ -818,6 +825,8 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         __trap();
     }
     constexpr uint32_t tmem_base = 0;
+    // everything above overlapped the tail of the previous kernel on the stream; from here on its results are read
+    ntx_dep_wait();
 
     if (warp == kProducerWarp) {
         if (elect_one())
@@ -1054,10 +1063,8 @@ int launch_fwd(const CUtensorMap& mq, const CUtensorMap& mk, const NtxDims& dm, 
     const size_t smem = fwd_smem_bytes<NDB>();
     NTX_CUDA(cudaFuncSetAttribute(tc_fwd_kernel<NDB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const long long T = (long long)plan.row_blocks * plan.key_tiles;
-    tc_fwd_kernel<NDB><<<plan.grid, kFwdThreads, smem, st>>>(mq, mk, dm, plan.key_tiles, T,
-                                                              plan.row_blocks * plan.tile_rows, partial,
-                                                              counter);
-    NTX_CUDA(cudaGetLastError());
+    NTX_CUDA(ntx_launch_dep(tc_fwd_kernel<NDB>, plan.grid, kFwdThreads, smem, st, mq, mk, dm, plan.key_tiles, T,
+                            plan.row_blocks * plan.tile_rows, partial, counter));
     return NTX_OK;
 }
 
@@ -1067,9 +1074,8 @@ int launch_bwd(const CUtensorMap& mq, const CUtensorMap& mk, const NtxDims& dm, 
     const size_t smem = bwd_smem_bytes<NDB>();
     NTX_CUDA(cudaFuncSetAttribute(tc_bwd_kernel<NDB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const long long T = (long long)plan.row_blocks * plan.key_tiles;
-    tc_bwd_kernel<NDB><<<plan.grid, BwdCfg<NDB>::kThreads, smem, st>>>(
-        mq, mk, dm, plan.key_tiles, T, plan.row_blocks * plan.tile_rows, wt, partial);
-    NTX_CUDA(cudaGetLastError());
+    NTX_CUDA(ntx_launch_dep(tc_bwd_kernel<NDB>, plan.grid, BwdCfg<NDB>::kThreads, smem, st, mq, mk, dm,
+                            plan.key_tiles, T, plan.row_blocks * plan.tile_rows, wt, partial));
     return NTX_OK;
 }
 
@@ -1106,13 +1112,13 @@ int ntx_tc_fwd_sym_launch(const __nv_bfloat16* rows, const NtxDims& dm, const Nt
     if (plan.d_pad == 64) {
         const size_t smem = (size_t)(1 + kSymNS) * 1 * kBlkBytes + kSymWG * 2 * kBlkBytes + 2048 + sizeof(SymCtl);
         NTX_CUDA(cudaFuncSetAttribute(tc_fwd_sym_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        tc_fwd_sym_kernel<1><<<plan.fwd_grid, kSymThreads, smem, st>>>(m, dm, plan.row_blocks, T, rows_pad, partial,
-                                                                       colpart, counter);
+        NTX_CUDA(ntx_launch_dep(tc_fwd_sym_kernel<1>, plan.fwd_grid, kSymThreads, smem, st, m, dm, plan.row_blocks, T,
+                                rows_pad, partial, colpart, counter));
     } else if (plan.d_pad == 128) {
         const size_t smem = (size_t)(1 + kSymNS) * 2 * kBlkBytes + kSymWG * 2 * kBlkBytes + 2048 + sizeof(SymCtl);
         NTX_CUDA(cudaFuncSetAttribute(tc_fwd_sym_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        tc_fwd_sym_kernel<2><<<plan.fwd_grid, kSymThreads, smem, st>>>(m, dm, plan.row_blocks, T, rows_pad, partial,
-                                                                       colpart, counter);
+        NTX_CUDA(ntx_launch_dep(tc_fwd_sym_kernel<2>, plan.fwd_grid, kSymThreads, smem, st, m, dm, plan.row_blocks, T,
+                                rows_pad, partial, colpart, counter));
     } else {
         ntx_set_error("symmetric forward: padded feature dim %d not built", plan.d_pad);
         return NTX_E_UNSUPPORTED;
