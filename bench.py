@@ -45,19 +45,27 @@ def parse():
     ap.add_argument("--workload", default="c4", choices=["c4", "c5"],
                     help="c4 = BASELINE configs[3] (the metric's config, default); c5 = configs[4]: "
                          "global batch 32768, d=256 (documentation runs only)")
+    ap.add_argument("--gather-backend", default="peer", choices=["peer", "nccl"],
+                    help="multi-GPU exchange: kernels store into every rank's buffers over NVLink peer memory "
+                         "(falls back to NCCL all-gathers when symmetric memory cannot be set up), or NCCL")
     ap.add_argument("--no-graphs", action="store_true",
                     help="launch every step eagerly instead of replaying CUDA graphs of the module")
     return ap.parse_args()
+
+
+GATHER_BACKEND = "nccl"
 
 
 def workload_config(world, eager=False):
     return {"workload": f"NT-Xent fwd+bwd, global batch {N_GLOBAL} pairs ({2 * N_GLOBAL} views), d={DIM}, "
                         f"tau={TAU}, bf16 (BASELINE configs[{3 if N_GLOBAL == 8192 else 4}])",
             "global_batch": N_GLOBAL, "d": DIM, "temperature": TAU,
-            "parallelism": f"rows sharded over {world} rank(s), keys all-gathered" if world > 1 else "single GPU",
+            "parallelism": (f"rows sharded over {world} rank(s), keys gathered by "
+                            + ("peer-memory stores from the normalise kernel + barrier kernel (NVLink)"
+                               if GATHER_BACKEND == "peer" else "NCCL all-gather")) if world > 1 else "single GPU",
             "l2": "flushed between timed steps (256 MiB write)",
             "launch": "eager" if eager else "one CUDA graph of the module's forward + backward "
-                                            "(kernels and NCCL gathers), replayed per step"}
+                                            "(kernels and cross-rank gathers), replayed per step"}
 
 
 def synthetic(dtype):
@@ -220,7 +228,24 @@ def run_ours(args):
     host0, host1 = v0_all[sl].contiguous().pin_memory(), v1_all[sl].contiguous().pin_memory()
     d0 = host0.to(dev).requires_grad_(True)
     d1 = host1.to(dev).requires_grad_(True)
-    crit = NT_Xent(temperature=TAU, reduction="mean", device=local_rank, gather=world > 1)
+    global GATHER_BACKEND
+    GATHER_BACKEND = args.gather_backend if world > 1 else "nccl"
+    if GATHER_BACKEND == "peer":
+        # every rank must take the same branch: agree on whether symmetric memory can be set up
+        from simclr_b200 import peer_exchange
+        ok = torch.tensor([1 if peer_exchange.available() and world <= peer_exchange.MAX_PEERS else 0], device=dev)
+        if ok.item():
+            try:
+                ld = _cabi.Backend().row_pitch(DIM, torch.bfloat16)
+                peer_exchange.exchange_for(None, 2 * n_local, ld, torch.bfloat16, dev)
+            except Exception as e:  # noqa: BLE001
+                print(f"[bench] rank {rank}: peer-memory gather unavailable ({e!r}); using NCCL", file=sys.stderr)
+                ok.zero_()
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if not ok.item():
+            GATHER_BACKEND = "nccl"
+    crit = NT_Xent(temperature=TAU, reduction="mean", device=local_rank, gather=world > 1,
+                   gather_backend=GATHER_BACKEND)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     ctl = dist.new_group(backend="gloo") if world > 1 else None     # control plane: barriers, max over ranks
 
@@ -341,10 +366,15 @@ def run_ours(args):
 
     if rank == 0:
         peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        peak_sustained = None
         if os.path.exists(peaks_path):
-            peak, peak_src = json.load(open(peaks_path))["bf16_tflops"], "measured (MEASURED_PEAKS.json bf16_tflops, burst)"
+            peaks = json.load(open(peaks_path))
+            peak, peak_src = peaks["bf16_tflops"], "measured (MEASURED_PEAKS.json bf16_tflops, burst)"
+            peak_sustained = peaks.get("bf16_tflops_sustained")
         else:
             peak, peak_src = FALLBACK_TFLOPS, "fallback (B200_PROFILING.md)"
+        # what the kernel actually issues: S is recomputed, and both GEMMs run over all (2N)^2 logits
+        bwd_executed = 16.0 * N_GLOBAL * N_GLOBAL * DIM / world
         bwd_flops = 12.0 * N_GLOBAL * N_GLOBAL * DIM / world      # algorithmic, SURVEY.md 8a row a8
         fwd_flops = 6.0 * N_GLOBAL * N_GLOBAL * DIM / world
         achieved = bwd_flops / (bwd_ms * 1e-3) / 1e12
@@ -362,6 +392,11 @@ def run_ours(args):
                          "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
                          "peak_source": peak_src, "algorithmic_flops_per_launch": bwd_flops,
                          "kernel_ms": bwd_ms,
+                         "executed_flops_per_launch": bwd_executed,
+                         "executed_tflops": bwd_executed / (bwd_ms * 1e-3) / 1e12,
+                         "peak_sustained": peak_sustained,
+                         "executed_frac_of_sustained": (bwd_executed / (bwd_ms * 1e-3) / 1e12 / peak_sustained
+                                                        if peak_sustained else None),
                          "fwd_kernel": {"kernel": ("tc_fwd_sym_kernel" if world == 1 and DIM <= 128 else "tc_fwd_kernel") + f"<{DIM // 64}>", "kernel_ms": fwd_ms,
                                         "achieved": fwd_flops / (fwd_ms * 1e-3) / 1e12},
                          "whole_step_frac": 18.0 * N_GLOBAL * N_GLOBAL * DIM / world / (ms_per_step * 1e-3) / 1e12 / peak},

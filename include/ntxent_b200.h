@@ -97,6 +97,21 @@ int ntx_plan(int q_rows, int k_rows, int d, int dtype, int sm_count, NtxPlan* pl
 int ntx_l2norm(const void* view0, const void* view1, int n, int d, int in_dtype,
                void* rows, int ld, int rows_dtype, float* inv_norm, void* stream);
 
+/* Multi-rank gather without a collective library call (one node, NVLink / NVSwitch peer memory).
+ * ntx_l2norm_peers is ntx_l2norm whose output goes straight into every rank's key buffer: peer_keys[p] is the
+ * address, mapped into this process, of rank p's [world*2n x ld] key buffer (peer_keys[rank] is this rank's own);
+ * the 2n normalised rows land in rows [rank*2n, (rank+1)*2n) of each.  Replaces F.normalize (loss.py:33-34)
+ * followed by the all-gather of distributed_utils.py (GatherLayer.forward).  world <= 8.
+ * ntx_scatter_peers copies `bytes` bytes from src to peer_dst[p] + dst_offset for every p (the row sums and row
+ * weights the backward needs from every rank).  Both only enqueue stores; the caller orders them against the
+ * readers with a cross-rank barrier on the stream (simclr_b200/peer_exchange.py uses torch's symmetric-memory
+ * barrier) and owns the peer mappings. */
+#define NTX_MAX_PEERS 8
+int ntx_l2norm_peers(const void* view0, const void* view1, int n, int d, int in_dtype, void* const* peer_keys,
+                     int world, int rank, int ld, int rows_dtype, float* inv_norm, void* stream);
+int ntx_scatter_peers(const void* src, size_t bytes, void* const* peer_dst, int world, size_t dst_offset,
+                      void* stream);
+
 /* Forward.  For each of this rank's q_rows = 2*n_local rows:
  *   rowsum[r]   = sum over keys c != self of exp(s_rc - 1/tau),  s = <row r, key c> / tau
  *   pos_logit[r]= s at the positive column

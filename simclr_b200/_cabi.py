@@ -19,7 +19,8 @@ DTYPES = {torch.float32: NTX_F32, torch.bfloat16: NTX_BF16}
 
 EXPORTS = (
     "ntx_version", "ntx_last_error", "ntx_row_pitch", "ntx_plan", "ntx_l2norm", "ntx_fwd",
-    "ntx_bwd", "ntx_debug_indices", "ntx_profile_next", "ntx_fwd_static",
+    "ntx_bwd", "ntx_debug_indices", "ntx_profile_next", "ntx_fwd_static", "ntx_l2norm_peers",
+    "ntx_scatter_peers",
 )
 
 
@@ -59,6 +60,8 @@ def _declare(lib):
     lib.ntx_bwd.argtypes = [vp, vp, i, i, i, i, i, ctypes.POINTER(NtxLayout), f, vp, vp, vp, vp, i, f,
                             vp, vp, i, vp, vp, vp, vp, sz, vp]
     lib.ntx_fwd_static.argtypes = [vp, vp, i, i, i, i, i, ctypes.POINTER(NtxLayout), f, vp, vp, vp, vp, vp]
+    lib.ntx_l2norm_peers.argtypes = [vp, vp, i, i, i, ctypes.POINTER(vp), i, i, i, i, vp, vp]
+    lib.ntx_scatter_peers.argtypes = [vp, sz, ctypes.POINTER(vp), i, sz, vp]
     lib.ntx_debug_indices.argtypes = [ctypes.POINTER(NtxLayout), vp, vp, vp]
     lib.ntx_profile_next.argtypes = [i, vp, vp]
     for name in EXPORTS:
@@ -110,6 +113,21 @@ class Backend:
         _check(load().ntx_l2norm(view0.data_ptr(), view1.data_ptr(), n, d, DTYPES[view0.dtype],
                                  rows.data_ptr(), rows.shape[1], DTYPES[rows.dtype],
                                  inv_norm.data_ptr(), _stream(rows)))
+
+    def l2norm_peers(self, view0, view1, peer_ptrs, rank, ld, rows_dtype, inv_norm):
+        """ntx_l2norm_peers: normalised rows written into rows [rank*2n, (rank+1)*2n) of every rank's
+        key buffer; ``peer_ptrs`` are the buffers' addresses in this process (peer memory)."""
+        n, d = view0.shape
+        table = (ctypes.c_void_p * len(peer_ptrs))(*peer_ptrs)
+        _check(load().ntx_l2norm_peers(view0.data_ptr(), view1.data_ptr(), n, d, DTYPES[view0.dtype], table,
+                                       len(peer_ptrs), rank, ld, DTYPES[rows_dtype], inv_norm.data_ptr(),
+                                       _stream(view0)))
+
+    def scatter_peers(self, src, peer_ptrs, dst_offset_bytes):
+        """ntx_scatter_peers: the bytes of ``src`` to the same offset of every rank's buffer."""
+        table = (ctypes.c_void_p * len(peer_ptrs))(*peer_ptrs)
+        _check(load().ntx_scatter_peers(src.data_ptr(), src.numel() * src.element_size(), table,
+                                        len(peer_ptrs), dst_offset_bytes, _stream(src)))
 
     def fwd(self, q, k, d, layout, temperature, rowsum, pos_logit, row_loss, loss_sum, workspace):
         lay = NtxLayout(*layout)

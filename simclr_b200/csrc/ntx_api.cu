@@ -185,8 +185,55 @@ int ntx_l2norm(const void* view0, const void* view1, int n, int d, int in_dtype,
                   rows_dtype);
     NTX_CHECK_ARG(ld >= ntx_row_pitch(d, rows_dtype) && ld % (rows_dtype == NTX_BF16 ? 64 : 4) == 0,
                   "ld=%d too small or misaligned for d=%d", ld, d);
-    return ntx_l2norm_launch(view0, view1, n, d, in_dtype, rows, ld, rows_dtype, inv_norm,
-                             (cudaStream_t)stream);
+    NtxPeers dst{};
+    dst.base[0] = rows;
+    dst.count = 1;
+    return ntx_l2norm_launch(view0, view1, n, d, in_dtype, dst, 0, ld, rows_dtype, inv_norm, (cudaStream_t)stream);
+}
+
+static int fill_peers(NtxPeers* out, void* const* peers, int world, const char* who) {
+    if (world < 1 || world > NTX_MAX_PEERS) {
+        ntx_set_error("%s: world=%d outside [1, %d] (peer memory spans one node)", who, world, NTX_MAX_PEERS);
+        return NTX_E_ARG;
+    }
+    if (!peers) { ntx_set_error("%s: NULL peer table", who); return NTX_E_ARG; }
+    for (int p = 0; p < world; ++p) {
+        if (!peers[p]) { ntx_set_error("%s: peer buffer %d is NULL", who, p); return NTX_E_ARG; }
+        out->base[p] = peers[p];
+    }
+    out->count = world;
+    return NTX_OK;
+}
+
+int ntx_l2norm_peers(const void* view0, const void* view1, int n, int d, int in_dtype, void* const* peer_keys,
+                     int world, int rank, int ld, int rows_dtype, float* inv_norm, void* stream) {
+    NTX_CHECK_ARG(n >= 1 && d >= 1, "bad sizes n=%d d=%d", n, d);
+    NTX_CHECK_ARG(view0 && view1 && inv_norm, "NULL buffer");
+    NTX_CHECK_ARG(in_dtype == NTX_F32 || in_dtype == NTX_BF16, "view dtype %d not supported", in_dtype);
+    NTX_CHECK_ARG(rows_dtype == NTX_F32 || rows_dtype == NTX_BF16, "rows dtype %d not supported",
+                  rows_dtype);
+    NTX_CHECK_ARG(ld >= ntx_row_pitch(d, rows_dtype) && ld % (rows_dtype == NTX_BF16 ? 64 : 4) == 0,
+                  "ld=%d too small or misaligned for d=%d", ld, d);
+    NTX_CHECK_ARG(rank >= 0 && rank < world, "rank %d outside world %d", rank, world);
+    NtxPeers dst{};
+    int rc = fill_peers(&dst, peer_keys, world, "ntx_l2norm_peers");
+    if (rc) return rc;
+    return ntx_l2norm_launch(view0, view1, n, d, in_dtype, dst, (size_t)rank * 2 * (size_t)n, ld, rows_dtype,
+                             inv_norm, (cudaStream_t)stream);
+}
+
+int ntx_scatter_peers(const void* src, size_t bytes, void* const* peer_dst, int world, size_t dst_offset,
+                      void* stream) {
+    NTX_CHECK_ARG(src != nullptr, "NULL source");
+    NTX_CHECK_ARG(reinterpret_cast<uintptr_t>(src) % 16 == 0 && dst_offset % 16 == 0,
+                  "source and destination offset must be 16-byte aligned");
+    NtxPeers dst{};
+    int rc = fill_peers(&dst, peer_dst, world, "ntx_scatter_peers");
+    if (rc) return rc;
+    for (int p = 0; p < world; ++p)
+        NTX_CHECK_ARG(reinterpret_cast<uintptr_t>(dst.base[p]) % 16 == 0, "peer buffer %d not 16-byte aligned", p);
+    if (bytes == 0) return NTX_OK;
+    return ntx_scatter_launch(src, bytes, dst, dst_offset, (cudaStream_t)stream);
 }
 
 int ntx_fwd(const void* q, const void* k, int q_rows, int k_rows, int d, int ld, int dtype,

@@ -132,8 +132,16 @@ struct NtxWeights {
 };
 
 // launch helpers implemented per translation unit
-int ntx_l2norm_launch(const void* v0, const void* v1, int n, int d, int in_dtype, void* rows, int ld,
-                      int rows_dtype, float* inv_norm, cudaStream_t st);
+// Destinations of a kernel that writes the same rows into the buffers of several ranks (peer memory mapped
+// into this process; one node, at most NTX_MAX_PEERS ranks).  count == 1 is the ordinary local case.
+#define NTX_MAX_PEERS 8
+struct NtxPeers {
+    void* base[NTX_MAX_PEERS];
+    int count;
+};
+int ntx_l2norm_launch(const void* v0, const void* v1, int n, int d, int in_dtype, const NtxPeers& rows,
+                      size_t row_offset, int ld, int rows_dtype, float* inv_norm, cudaStream_t st);
+int ntx_scatter_launch(const void* src, size_t bytes, const NtxPeers& dst, size_t dst_offset, cudaStream_t st);
 int ntx_simt_fwd_launch(const float* q, const float* k, const NtxDims& dm, const NtxPlan& plan,
                         float* partial, unsigned int* counter, cudaStream_t st);
 int ntx_simt_bwd_launch(const float* q, const float* k, const NtxDims& dm, const NtxPlan& plan,

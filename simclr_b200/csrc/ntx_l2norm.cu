@@ -61,7 +61,7 @@ __device__ __forceinline__ void storev(__nv_bfloat16* p, const float (&v)[N]) {
 template <typename TIn, typename TOut, bool kVector>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 l2norm_kernel(const TIn* __restrict__ view0, const TIn* __restrict__ view1, int n, int d,
-              TOut* __restrict__ rows, int ld, float* __restrict__ inv_norm, int lanes) {
+              NtxPeers rows, size_t row_offset, int ld, float* __restrict__ inv_norm, int lanes) {
     ntx_dep_trigger();
     ntx_dep_wait();
     const int sub = threadIdx.x % lanes;
@@ -70,7 +70,7 @@ l2norm_kernel(const TIn* __restrict__ view0, const TIn* __restrict__ view1, int 
     const bool live = r_raw < 2 * n;
     const int r = live ? r_raw : 2 * n - 1;                   // keep every lane in the shuffles
     const TIn* src = (r < n) ? view0 + (size_t)r * d : view1 + (size_t)(r - n) * d;
-    TOut* dst = rows + (size_t)r * ld;
+    const size_t dst_off = (row_offset + (size_t)r) * ld;     // same place in every destination buffer
     constexpr int V = Vec<TIn>::N;
 
     float ss = 0.f;
@@ -103,21 +103,28 @@ l2norm_kernel(const TIn* __restrict__ view0, const TIn* __restrict__ view1, int 
 #pragma unroll
                 for (int i = 0; i < V; ++i) v[i] = 0.f;
             }
-            storev<V>(dst + c, v);
+            for (int p = 0; p < rows.count; ++p) storev<V>(static_cast<TOut*>(rows.base[p]) + dst_off + c, v);
         }
     } else {
-        for (int c = sub; c < ld; c += lanes) store1(dst + c, c < d ? to_f32(src[c]) / denom : 0.f);
+        for (int c = sub; c < ld; c += lanes) {
+            const float x = c < d ? to_f32(src[c]) / denom : 0.f;
+            for (int p = 0; p < rows.count; ++p) store1(static_cast<TOut*>(rows.base[p]) + dst_off + c, x);
+        }
     }
 }
 
 template <typename TIn, typename TOut>
-int launch(const void* v0, const void* v1, int n, int d, void* rows, int ld, float* inv_norm,
-           cudaStream_t st) {
+int launch(const void* v0, const void* v1, int n, int d, const NtxPeers& rows, size_t row_offset, int ld,
+           float* inv_norm, cudaStream_t st) {
     constexpr int V = Vec<TIn>::N;
     const bool vec = (d % V == 0) && (ld % V == 0) &&
                      (reinterpret_cast<uintptr_t>(v0) % 16 == 0) &&
                      (reinterpret_cast<uintptr_t>(v1) % 16 == 0) &&
-                     (reinterpret_cast<uintptr_t>(rows) % 16 == 0);
+                     [&] {
+                         for (int p = 0; p < rows.count; ++p)
+                             if (reinterpret_cast<uintptr_t>(rows.base[p]) % 16 != 0) return false;
+                         return true;
+                     }();
     const int work = vec ? (ld + V - 1) / V : ld;
     int lanes = 1;
     while (lanes < work && lanes < 32) lanes <<= 1;
@@ -125,25 +132,48 @@ int launch(const void* v0, const void* v1, int n, int d, void* rows, int ld, flo
     const int grid = (2 * n + rows_per_block - 1) / rows_per_block;
     if (vec)
         NTX_CUDA(ntx_launch_dep(l2norm_kernel<TIn, TOut, true>, grid, kWarpsPerBlock * 32, 0, st, (const TIn*)v0,
-                                (const TIn*)v1, n, d, (TOut*)rows, ld, inv_norm, lanes));
+                                (const TIn*)v1, n, d, rows, row_offset, ld, inv_norm, lanes));
     else
         NTX_CUDA(ntx_launch_dep(l2norm_kernel<TIn, TOut, false>, grid, kWarpsPerBlock * 32, 0, st, (const TIn*)v0,
-                                (const TIn*)v1, n, d, (TOut*)rows, ld, inv_norm, lanes));
+                                (const TIn*)v1, n, d, rows, row_offset, ld, inv_norm, lanes));
     return NTX_OK;
 }
 
 }  // namespace
 
-int ntx_l2norm_launch(const void* v0, const void* v1, int n, int d, int in_dtype, void* rows, int ld,
-                      int rows_dtype, float* inv_norm, cudaStream_t st) {
+// the same bytes to the same offset of every destination buffer (16-byte units; the tail in bytes)
+__global__ void __launch_bounds__(256) ntx_scatter_kernel(const uint8_t* __restrict__ src, size_t bytes, NtxPeers dst,
+                                                      size_t dst_offset) {
+    ntx_dep_trigger();
+    ntx_dep_wait();
+    const size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 16;
+    if (i + 16 <= bytes) {
+        const uint4 v = *reinterpret_cast<const uint4*>(src + i);
+        for (int p = 0; p < dst.count; ++p)
+            *reinterpret_cast<uint4*>(static_cast<uint8_t*>(dst.base[p]) + dst_offset + i) = v;
+    } else {
+        for (size_t b = i; b < bytes; ++b)
+            for (int p = 0; p < dst.count; ++p) static_cast<uint8_t*>(dst.base[p])[dst_offset + b] = src[b];
+    }
+}
+
+int ntx_scatter_launch(const void* src, size_t bytes, const NtxPeers& dst, size_t dst_offset, cudaStream_t st) {
+    const size_t units = (bytes + 15) / 16;
+    NTX_CUDA(ntx_launch_dep(ntx_scatter_kernel, (unsigned)((units + 255) / 256), 256, 0, st, (const uint8_t*)src, bytes,
+                            dst, dst_offset));
+    return NTX_OK;
+}
+
+int ntx_l2norm_launch(const void* v0, const void* v1, int n, int d, int in_dtype, const NtxPeers& rows,
+                      size_t row_offset, int ld, int rows_dtype, float* inv_norm, cudaStream_t st) {
     if (in_dtype == NTX_F32 && rows_dtype == NTX_F32)
-        return launch<float, float>(v0, v1, n, d, rows, ld, inv_norm, st);
+        return launch<float, float>(v0, v1, n, d, rows, row_offset, ld, inv_norm, st);
     if (in_dtype == NTX_F32 && rows_dtype == NTX_BF16)
-        return launch<float, __nv_bfloat16>(v0, v1, n, d, rows, ld, inv_norm, st);
+        return launch<float, __nv_bfloat16>(v0, v1, n, d, rows, row_offset, ld, inv_norm, st);
     if (in_dtype == NTX_BF16 && rows_dtype == NTX_BF16)
-        return launch<__nv_bfloat16, __nv_bfloat16>(v0, v1, n, d, rows, ld, inv_norm, st);
+        return launch<__nv_bfloat16, __nv_bfloat16>(v0, v1, n, d, rows, row_offset, ld, inv_norm, st);
     if (in_dtype == NTX_BF16 && rows_dtype == NTX_F32)
-        return launch<__nv_bfloat16, float>(v0, v1, n, d, rows, ld, inv_norm, st);
+        return launch<__nv_bfloat16, float>(v0, v1, n, d, rows, row_offset, ld, inv_norm, st);
     ntx_set_error("ntx_l2norm: unsupported dtype pair (%d -> %d)", in_dtype, rows_dtype);
     return NTX_E_ARG;
 }

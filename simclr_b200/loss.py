@@ -19,7 +19,7 @@ import os
 import torch
 import torch.distributed as dist
 
-from . import _cabi
+from . import _cabi, peer_exchange
 
 _backend = _cabi.Backend()          # tests may swap in a stand-in with the same methods
 _workspaces: dict = {}
@@ -59,29 +59,37 @@ class NTXentFunction(torch.autograd.Function):
     """
 
     @staticmethod
-    def forward(ctx, view0, view1, temperature, reduction, rows_dtype, group, world, rank):
+    def forward(ctx, view0, view1, temperature, reduction, rows_dtype, group, world, rank, peer=False):
         be = _backend
         n, d = view0.shape
         dev = view0.device
         q_rows = 2 * n
         ld, ws_bytes = _shape_info(be, q_rows, world * q_rows, d, rows_dtype, dev)
-        rows = torch.empty((q_rows, ld), dtype=rows_dtype, device=dev)
         stats = torch.empty((4, q_rows), dtype=torch.float32, device=dev)   # inv_norm, rowsum, pos, row loss
         loss_sum = torch.empty(2, dtype=torch.float32, device=dev)
         inv_norm, rowsum, pos_logit, row_loss = stats[0], stats[1], stats[2], stats[3]
-        be.l2norm(view0, view1, rows, inv_norm)
-        if world > 1:
+        exchange = None
+        if world > 1 and peer:
+            # the normalise kernel stores straight into every rank's key buffer (NVLink peer memory)
+            exchange = peer_exchange.exchange_for(group, q_rows, ld, rows_dtype, dev)
+            keys = exchange.gather_rows(be, view0, view1, inv_norm)
+            q = keys[rank * q_rows:(rank + 1) * q_rows]
+        elif world > 1:
+            rows = torch.empty((q_rows, ld), dtype=rows_dtype, device=dev)
+            be.l2norm(view0, view1, rows, inv_norm)
             keys = torch.empty((world * q_rows, ld), dtype=rows_dtype, device=dev)
             dist.all_gather_into_tensor(keys, rows, group=group)          # rank-major key buffer
             q = keys[rank * q_rows:(rank + 1) * q_rows]
         else:
+            rows = torch.empty((q_rows, ld), dtype=rows_dtype, device=dev)
+            be.l2norm(view0, view1, rows, inv_norm)
             keys = q = rows
         layout = (n, world, rank)
         ws = _workspace(dev, ws_bytes)
         be.fwd(q, keys, d, layout, temperature, rowsum, pos_logit, row_loss, loss_sum, ws)
 
         ctx.save_for_backward(view0, view1, keys, stats)
-        ctx.meta = (temperature, reduction, group, world, rank, d)
+        ctx.meta = (temperature, reduction, group, world, rank, d, exchange)
         if reduction == "none":
             out = row_loss.view(2, n).clone()                              # loss.py:55-58
         elif reduction == "sum":
@@ -94,7 +102,7 @@ class NTXentFunction(torch.autograd.Function):
     def backward(ctx, grad_out):
         be = _backend
         view0, view1, keys, stats = ctx.saved_tensors
-        temperature, reduction, group, world, rank, d = ctx.meta
+        temperature, reduction, group, world, rank, d, exchange = ctx.meta
         n = view0.shape[0]
         q_rows = 2 * n
         dev = view0.device
@@ -107,9 +115,12 @@ class NTXentFunction(torch.autograd.Function):
         if world > 1:
             # one collective for both per-key vectors: every rank contributes [rowsum ; row weights]
             mine = torch.stack((rowsum, w_q.expand(q_rows)))                       # (2, q_rows)
-            both = torch.empty((world * 2, q_rows), dtype=torch.float32, device=dev)
-            dist.all_gather_into_tensor(both, mine, group=group)
-            both = both.view(world, 2, q_rows)
+            if exchange is not None:
+                both = exchange.gather_vectors(be, mine)                           # peer stores + barrier
+            else:
+                both = torch.empty((world * 2, q_rows), dtype=torch.float32, device=dev)
+                dist.all_gather_into_tensor(both, mine, group=group)
+                both = both.view(world, 2, q_rows)
             rowsum_k = both[:, 0, :].reshape(-1)                                   # rank-major, like the keys
             w_k = both[:, 1, :].reshape(-1)
             w_q, w_stride = w_k[rank * q_rows:(rank + 1) * q_rows], 1              # ranks may hold different upstream gradients
@@ -122,7 +133,7 @@ class NTXentFunction(torch.autograd.Function):
         ws = _workspace(dev, ws_bytes)
         be.bwd(q, keys, d, (n, world, rank), temperature, rowsum, rowsum_k, w_q, w_k, w_stride, w_scale,
                view0, view1, inv_norm, dview0, dview1, ws)
-        return dview0, dview1, None, None, None, None, None, None
+        return dview0, dview1, None, None, None, None, None, None, None
 
 
 class NT_Xent(torch.nn.Module):
@@ -136,7 +147,8 @@ class NT_Xent(torch.nn.Module):
 
     def __init__(self, temperature: float = 0.1, reduction: str = "mean",
                  device: torch.device = torch.device("cpu"), *, gather: bool | None = None,
-                 process_group=None, compute_dtype: torch.dtype | None = None) -> None:
+                 process_group=None, compute_dtype: torch.dtype | None = None,
+                 gather_backend: str | None = None) -> None:
         """
         :param temperature: Temperature parameter. The value must be positive.
         :param reduction: Same to PyTorch's `reduction` in losses.
@@ -145,6 +157,9 @@ class NT_Xent(torch.nn.Module):
             None = take it from the environment variable NTXENT_GATHER (default off, which
             is the reference's behaviour: each rank's loss sees only its local batch).
         :param process_group: keyword-only, group used when gathering (default: world).
+        :param gather_backend: keyword-only. "nccl" (all-gather collectives, any topology) or "peer" (the
+            kernels store into every rank's buffers over NVLink peer memory; one node, at most 8 ranks,
+            forward and backward calls alternating). None = NTXENT_GATHER_BACKEND, default "nccl".
         :param compute_dtype: keyword-only. dtype of the normalised rows: torch.float32 (CUDA-core
             kernels, 1e-5 parity), torch.bfloat16 (tcgen05 kernels) or None = the input dtype
             (NTXENT_COMPUTE_DTYPE=bf16 overrides None).
@@ -158,6 +173,10 @@ class NT_Xent(torch.nn.Module):
         self.device = device
         self.gather = _env_flag("NTXENT_GATHER") if gather is None else bool(gather)
         self.process_group = process_group
+        gather_backend = gather_backend or os.environ.get("NTXENT_GATHER_BACKEND", "nccl").lower()
+        if gather_backend not in ("nccl", "peer"):
+            raise ValueError(f"gather_backend must be 'nccl' or 'peer', got {gather_backend!r}")
+        self.gather_backend = gather_backend
         if compute_dtype is None and os.environ.get("NTXENT_COMPUTE_DTYPE", "").lower() in ("bf16", "bfloat16"):
             compute_dtype = torch.bfloat16
         if compute_dtype not in (None, torch.float32, torch.bfloat16):
@@ -193,7 +212,8 @@ class NT_Xent(torch.nn.Module):
             world, rank = dist.get_world_size(group), dist.get_rank(group)
         rows_dtype = self.compute_dtype or view0.dtype
         return NTXentFunction.apply(view0.contiguous(), view1.contiguous(), float(self.temperature),
-                                    self.reduction, rows_dtype, group, world, rank)
+                                    self.reduction, rows_dtype, group, world, rank,
+                                    world > 1 and self.gather_backend == "peer")
 
     def extra_repr(self) -> str:
         return (f"temperature={self.temperature}, reduction={self.reduction!r}, gather={self.gather}, "

@@ -299,3 +299,37 @@ def test_symmetric_forward_matches_full_tile_forward_and_oracle(n, d, tau, dev):
     assert rel_err(sym[2].reshape(2, n), ref["loss"]) < BF16_TOL
     assert rel_err(full[2].reshape(2, n), ref["loss"]) < BF16_TOL
     assert abs(sym_sum[1] - ref["loss"].mean()) < BF16_TOL * abs(ref["loss"].mean())
+
+
+@pytest.mark.parametrize("in_dtype,rows_dtype", [(torch.float32, torch.float32), (torch.bfloat16, torch.bfloat16)])
+def test_peer_entry_points_with_local_buffers(in_dtype, rows_dtype, dev):
+    """ntx_l2norm_peers / ntx_scatter_peers through the C ABI, with two buffers of this one GPU standing in
+    for two ranks' key buffers: both receive the rows ntx_l2norm writes, at the rank's row offset, and
+    nothing else is touched; the scatter lands the same bytes at the same offset of both buffers."""
+    from simclr_b200 import _cabi
+    be = _cabi.Backend()
+    n, d, world, rank = 37, 96, 2, 1
+    g = torch.Generator().manual_seed(5)
+    a = torch.randn(n, d, generator=g).to(in_dtype).to(dev)
+    b = torch.randn(n, d, generator=g).to(in_dtype).to(dev)
+    q_rows = 2 * n
+    ld = be.row_pitch(d, rows_dtype)
+    want = torch.empty(q_rows, ld, dtype=rows_dtype, device=dev)
+    inv_want = torch.empty(q_rows, device=dev)
+    be.l2norm(a, b, want, inv_want)
+    bufs = [torch.full((world * q_rows, ld), 7.0, dtype=rows_dtype, device=dev) for _ in range(world)]
+    inv = torch.empty(q_rows, device=dev)
+    be.l2norm_peers(a, b, [t.data_ptr() for t in bufs], rank, ld, rows_dtype, inv)
+    torch.cuda.synchronize()
+    for t in bufs:
+        assert torch.equal(t[rank * q_rows:(rank + 1) * q_rows], want)
+        assert bool((t[:rank * q_rows] == 7.0).all())
+    assert torch.equal(inv, inv_want)
+    src = torch.arange(2 * q_rows, dtype=torch.float32, device=dev).view(2, q_rows)
+    vecs = [torch.zeros(world, 2, q_rows, device=dev) for _ in range(world)]
+    be.scatter_peers(src, [t.data_ptr() for t in vecs], rank * 2 * q_rows * 4)
+    torch.cuda.synchronize()
+    for t in vecs:
+        assert torch.equal(t[rank], src) and float(t[0].abs().sum()) == 0.0
+    with pytest.raises(_cabi.NtxError, match="world"):
+        be.scatter_peers(src, [vecs[0].data_ptr()] * 9, 0)
