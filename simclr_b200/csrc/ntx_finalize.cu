@@ -266,13 +266,10 @@ __global__ void debug_indices_kernel(int n_local, int rank, int32_t* __restrict_
     pos_col[r] = ntx_pos_col(r, n_local, rank);
 }
 
-// threads per row: power of two covering the row's float4 groups; at least 16 so that the
-// rows of one block (<= 1024 / 16) never straddle a 64-row tile (one slot count per block)
-int lanes_for(int groups4) {
-    int l = 16;
-    while (l < groups4 && l < 32) l <<= 1;
-    return l;
-}
+// (16 or more, so that the rows of one block, <= 1024 / 16, never straddle a 64-row tile: one slot count per block)
+// threads per row: 16 up to 256 features (64 four-element groups), so that a block covers enough rows for the
+// whole grid to be resident at once (these kernels are latency-bound: one wave, not two), 32 beyond
+int lanes_for(int groups4) { return groups4 <= 64 ? 16 : 32; }
 
 template <typename TIn>
 int launch_bwd_finalize(const BwdFinArgs& A, const void* view0, const void* view1, void* dview0,
@@ -284,15 +281,15 @@ int launch_bwd_finalize(const BwdFinArgs& A, const void* view0, const void* view
     if (vec) {
         const int lanes = lanes_for(d / 4);
         const int grid = (A.dm.q_rows + kThreads / lanes - 1) / (kThreads / lanes);
-        if (d <= 128)
-            NTX_CUDA(ntx_launch_dep(bwd_finalize_vec_kernel<TIn, 1>, grid, kThreads, 0, st, A, lanes, (const TIn*)view0,
-                                    (const TIn*)view1, (TIn*)dview0, (TIn*)dview1));
-        else if (d <= 256)
-            NTX_CUDA(ntx_launch_dep(bwd_finalize_vec_kernel<TIn, 2>, grid, kThreads, 0, st, A, lanes, (const TIn*)view0,
-                                    (const TIn*)view1, (TIn*)dview0, (TIn*)dview1));
-        else
-            NTX_CUDA(ntx_launch_dep(bwd_finalize_vec_kernel<TIn, 8>, grid, kThreads, 0, st, A, lanes, (const TIn*)view0,
-                                    (const TIn*)view1, (TIn*)dview0, (TIn*)dview1));
+        const int per_thread = (d / 4 + lanes - 1) / lanes;          // float4 groups each thread covers
+#define NTX_BWD_FIN(V)                                                                                        \
+    NTX_CUDA(ntx_launch_dep(bwd_finalize_vec_kernel<TIn, V>, grid, kThreads, 0, st, A, lanes, (const TIn*)view0, \
+                            (const TIn*)view1, (TIn*)dview0, (TIn*)dview1))
+        if (per_thread <= 1) NTX_BWD_FIN(1);
+        else if (per_thread <= 2) NTX_BWD_FIN(2);
+        else if (per_thread <= 4) NTX_BWD_FIN(4);
+        else NTX_BWD_FIN(8);
+#undef NTX_BWD_FIN
     } else {
         const int grid = (A.dm.q_rows + kThreads / 32 - 1) / (kThreads / 32);
         bwd_finalize_kernel<TIn><<<grid, kThreads, 0, st>>>(A, (const TIn*)view0, (const TIn*)view1, (TIn*)dview0,

@@ -993,7 +993,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
                 if (lane == 0) mbar_arrive(&ctl->c_full[g]);
             }
             if (last_of_seg) {
-                drain(rb, seg);
+                { NTX_TIC(te_drain); drain(rb, seg); NTX_TOC(te_drain); }
                 ++seg;
                 new_seg = true;
             }
@@ -1001,7 +1001,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
             if (++turn == NWG) turn = 0;
         }
         NTX_TOC(te_total);
-        if (threadIdx.x == 0) { NTX_TSAVE(13, te_total); NTX_TSAVE(14, te_wait); }
+        if (threadIdx.x == 0) { NTX_TSAVE(13, te_total); NTX_TSAVE(14, te_wait); NTX_TSAVE(7, te_drain); }
     }
 
     tc_fence_before();

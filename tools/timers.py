@@ -40,7 +40,7 @@ assert rc == 0
 m = buf.mean(axis=0)
 tiles = plan.row_blocks * plan.key_tiles / plan.grid
 names = ["fwd mma total", "fwd mma wait k_full", "fwd mma wait s_empty", "fwd mma issue", "fwd epi total",
-         "fwd epi wait s_full", "", "", "bwd mma total", "bwd mma wait k_full", "bwd mma wait buf_free",
+         "fwd epi wait s_full", "", "bwd epi drain (wait + store)", "bwd mma total", "bwd mma wait k_full", "bwd mma wait buf_free",
          "bwd gemm2 wait c_full", "bwd gemm1 issue", "bwd epi total", "bwd epi wait s_full", "bwd gemm2 issue"]
 print(f"tiles per CTA {tiles:.1f}")
 for name, v in zip(names, m):
