@@ -101,7 +101,8 @@ int ntx_l2norm(const void* view0, const void* view1, int n, int d, int in_dtype,
  * ntx_l2norm_peers is ntx_l2norm whose output goes straight into every rank's key buffer: peer_keys[p] is the
  * address, mapped into this process, of rank p's [world*2n x ld] key buffer (peer_keys[rank] is this rank's own);
  * the 2n normalised rows land in rows [rank*2n, (rank+1)*2n) of each.  Replaces F.normalize (loss.py:33-34)
- * followed by the all-gather of distributed_utils.py (GatherLayer.forward).  world <= 8.
+ * followed by the cross-rank embedding gather of BASELINE.json's north_star (the reference itself has no gather:
+ * distributed_utils.py:8-24 is only init_ddp / cleanup).  world <= 8.
  * ntx_scatter_peers copies `bytes` bytes from src to peer_dst[p] + dst_offset for every p (the row sums and row
  * weights the backward needs from every rank).  Both only enqueue stores; the caller orders them against the
  * readers with a cross-rank barrier on the stream (simclr_b200/peer_exchange.py uses torch's symmetric-memory

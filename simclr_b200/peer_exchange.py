@@ -1,7 +1,8 @@
 """Cross-rank exchange over NVLink peer memory for the gathered NT-Xent (one node, <= 8 ranks).
 
-The reference gathers embeddings with ``torch.distributed.all_gather`` (distributed_utils.py,
-``GatherLayer``).  Here every rank's key buffer lives in symmetric memory (the same allocation made
+The reference has no cross-rank gather (distributed_utils.py:8-24 is only init_ddp / cleanup); the one
+BASELINE.json's north_star asks for is an all-gather of the normalised rows.  Here every rank's key
+buffer lives in symmetric memory (the same allocation made
 on every rank and mapped into every process, ``torch.distributed._symmetric_memory``); the normalise
 kernel stores its rows directly into all of them (``ntx_l2norm_peers``), the per-row vectors of the
 backward go out the same way (``ntx_scatter_peers``), and one cross-rank barrier kernel on the stream
