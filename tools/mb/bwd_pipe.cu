@@ -16,7 +16,13 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
-constexpr int NS = 5, NB = 3, MAXE = 8;
+#ifndef NB_
+#define NB_ 3
+#endif
+#ifndef KEYS_
+#define KEYS_ 128       // keys per tile: 128 (3 buffers of 128 TMEM columns) or 96 (4 buffers of 96)
+#endif
+constexpr int NS = 5, NB = NB_, KEYS = KEYS_, MAXE = 8;
 struct Ctl { uint64_t k_full[NS], k_empty[NS], s_full[NB], c_full[NB], c_half[NB], buf_free[NB]; uint32_t tmem_slot; };
 
 // variant bits: 1 = GEMM1 and GEMM2 issued by ONE warp in the order G1(i), G2(i - lag)
@@ -42,13 +48,13 @@ __global__ void __launch_bounds__(640, 1) k(long long* out, const uint8_t* src, 
     tc_fence_after();
     uint8_t* q = smem;
     uint8_t* ring = smem + 32768;
-    constexpr uint32_t idesc1 = instr_desc_bf16(128, 128, 0), idesc2 = instr_desc_bf16(128, 128, 1);
+    constexpr uint32_t idesc1 = instr_desc_bf16(128, KEYS, 0), idesc2 = instr_desc_bf16(128, 128, 1);
     auto lock = [&]() { if (variant & 128) while (atomicCAS(&pipe_lock, 0, 1) != 0) {} };
     auto unlock = [&]() { if (variant & 128) atomicExch(&pipe_lock, 0); };
     auto gemm1 = [&](int i) {
         lock();
         const uint8_t* kt = ring + (i % NS) * 32768;
-        const uint32_t d = 128 + (i % NB) * 128;
+        const uint32_t d = 128 + (i % NB) * KEYS;
 #pragma unroll
         for (int b = 0; b < 2; ++b)
 #pragma unroll
@@ -69,9 +75,9 @@ __global__ void __launch_bounds__(640, 1) k(long long* out, const uint8_t* src, 
     auto gemm2 = [&](int i) {
         lock();
         const uint8_t* kt = ring + (i % NS) * 32768;
-        const uint32_t c = 128 + (i % NB) * 128;
+        const uint32_t c = 128 + (i % NB) * KEYS;
 #pragma unroll
-        for (int kk = 0; kk < 8; ++kk)
+        for (int kk = 0; kk < KEYS / 16; ++kk)
             mma_bf16_ts(0, c + kk * 8, smem_desc_sw128(smem_u32(kt + kk * 2048), 16384, 1024), idesc2, 1u);
         mma_commit(&ctl.k_empty[i % NS]);
         mma_commit(&ctl.buf_free[i % NB]);
@@ -212,8 +218,8 @@ int main() {
     const int tiles = 600;
     const int Es[] = {0, 500, 1000, 1500, 2000, 2500, 3000};
     const struct { int variant, NE, lag; const char* name; } runs[] = {
-        {2, 3, 1, "no lock, 3 groups x 4 warps           "}, {130, 3, 1, "issue lock, 3 groups x 4 warps        "},
-        {130, 2, 1, "issue lock, 2 groups x 4 warps        "}, {194, 3, 1, "issue lock, two GEMM1 warps, 3 groups "}};
+        {2, 3, 1, "two issuers, 3 groups x 4 warps "}, {2, 4, 1, "two issuers, 4 groups x 4 warps "}};
+    printf("NB = %d buffers, %d keys per tile (E is per tile of that size)\n", NB, KEYS);
     for (auto& r : runs) {
         printf("%s:", r.name);
         for (int E : Es) {
