@@ -784,6 +784,9 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
               NtxDims dm, int key_tiles, long long T, int rows_pad, BwdWeights wt,
               float* __restrict__ partial) {
     using Cfg = BwdCfg<NDB>;
+#ifdef NTX_TIMELINE
+    const long long t_entry = clock64();
+#endif
     constexpr int NS = Cfg::NS, NWG = Cfg::NWG, DP = Cfg::DP;
     constexpr uint32_t kSCol = Cfg::kSCol;
     constexpr uint32_t kTileBytes = NDB * kBlkBytes;
@@ -970,6 +973,9 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
                 if (i + NWG < n_tiles) fetch_beta((kt + NWG) % key_tiles);
 
                 { NTX_TIC(te_wait); mbar_wait(&ctl->s_full[g], own & 1); NTX_TOC(te_wait); }
+#ifdef NTX_TIMELINE
+                if (own == 0 && threadIdx.x == 0) g_ntx_timers[blockIdx.x % 148][0] = clock64() - t_entry;
+#endif
                 ++own;
                 tc_fence_after();
                 const bool edge = edge_tile(rb, kt, dm) || (rb * 128 + 128 > dm.q_rows);
@@ -993,6 +999,9 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
                 if (lane == 0) mbar_arrive(&ctl->c_full[g]);
             }
             if (last_of_seg) {
+#ifdef NTX_TIMELINE
+                if (i + 1 == n_tiles && threadIdx.x == 0) g_ntx_timers[blockIdx.x % 148][1] = clock64() - t_entry;
+#endif
                 { NTX_TIC(te_drain); drain(rb, seg); NTX_TOC(te_drain); }
                 ++seg;
                 new_seg = true;
@@ -1002,6 +1011,9 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         }
         NTX_TOC(te_total);
         if (threadIdx.x == 0) { NTX_TSAVE(13, te_total); NTX_TSAVE(14, te_wait); NTX_TSAVE(7, te_drain); }
+#ifdef NTX_TIMELINE
+        if (threadIdx.x == 0) g_ntx_timers[blockIdx.x % 148][2] = clock64() - t_entry;
+#endif
     }
 
     tc_fence_before();

@@ -68,11 +68,12 @@ class NTXentFunction(torch.autograd.Function):
         stats = torch.empty((4, q_rows), dtype=torch.float32, device=dev)   # inv_norm, rowsum, pos, row loss
         loss_sum = torch.empty(2, dtype=torch.float32, device=dev)
         inv_norm, rowsum, pos_logit, row_loss = stats[0], stats[1], stats[2], stats[3]
-        exchange = None
+        exchange, key_slot = None, 0
         if world > 1 and peer:
             # the normalise kernel stores straight into every rank's key buffer (NVLink peer memory)
             exchange = peer_exchange.exchange_for(group, q_rows, ld, rows_dtype, dev)
-            keys = exchange.gather_rows(be, view0, view1, inv_norm)
+            needs_grad = any(ctx.needs_input_grad[:2])
+            keys, key_slot = exchange.gather_rows(be, view0, view1, inv_norm, hold=needs_grad)
             q = keys[rank * q_rows:(rank + 1) * q_rows]
         elif world > 1:
             rows = torch.empty((q_rows, ld), dtype=rows_dtype, device=dev)
@@ -89,7 +90,7 @@ class NTXentFunction(torch.autograd.Function):
         be.fwd(q, keys, d, layout, temperature, rowsum, pos_logit, row_loss, loss_sum, ws)
 
         ctx.save_for_backward(view0, view1, keys, stats)
-        ctx.meta = (temperature, reduction, group, world, rank, d, exchange)
+        ctx.meta = (temperature, reduction, group, world, rank, d, exchange, key_slot)
         if reduction == "none":
             out = row_loss.view(2, n).clone()                              # loss.py:55-58
         elif reduction == "sum":
@@ -102,7 +103,7 @@ class NTXentFunction(torch.autograd.Function):
     def backward(ctx, grad_out):
         be = _backend
         view0, view1, keys, stats = ctx.saved_tensors
-        temperature, reduction, group, world, rank, d, exchange = ctx.meta
+        temperature, reduction, group, world, rank, d, exchange, key_slot = ctx.meta
         n = view0.shape[0]
         q_rows = 2 * n
         dev = view0.device
@@ -133,6 +134,8 @@ class NTXentFunction(torch.autograd.Function):
         ws = _workspace(dev, ws_bytes)
         be.bwd(q, keys, d, (n, world, rank), temperature, rowsum, rowsum_k, w_q, w_k, w_stride, w_scale,
                view0, view1, inv_norm, dview0, dview1, ws)
+        if exchange is not None:
+            exchange.release(key_slot)          # the key buffer may be written again two forward calls from now
         return dview0, dview1, None, None, None, None, None, None, None
 
 

@@ -14,6 +14,9 @@ Hazards and how they are closed (all on the caller's stream, so the whole step c
    has passed the barrier of step t+1, i.e. has finished the backward of step t.
  * the per-row vectors are written after the forward of step t+1, i.e. after that step's first
    barrier, which every rank passes only once its backward of step t is done: one buffer is enough.
+ * inside a CUDA graph capture the buffer choice is frozen into the graph, so every replay writes the
+   same key buffer; there an extra barrier before the stores makes every rank finish its previous
+   backward first (three barrier kernels per step instead of two).
 """
 from __future__ import annotations
 
@@ -54,14 +57,29 @@ class PeerExchange:
         self.vec_hdl = symm_mem.rendezvous(self.vec, group=name)
         self.vec_ptrs = [int(p) for p in self.vec_hdl.buffer_ptrs]
         self.step = 0
+        self.held = [False, False]          # key buffer saved for a backward that has not run yet
 
-    def gather_rows(self, be, view0, view1, inv_norm) -> torch.Tensor:
-        """Normalise this rank's rows into every rank's key buffer; returns the local (complete) key buffer."""
+    def gather_rows(self, be, view0, view1, inv_norm, hold: bool):
+        """Normalise this rank's rows into every rank's key buffer.  Returns (the local, complete key buffer,
+        its index); ``hold`` marks it as saved for a backward call, which must ``release`` it."""
         which = self.step & 1
+        if self.held[which]:
+            raise RuntimeError(
+                "NT_Xent(gather_backend='peer') keeps two key buffers and the one due now is still saved for a "
+                "backward call that has not run: at most two forward calls may be outstanding. Use "
+                "gather_backend='nccl' for other call patterns.")
         self.step += 1
+        self.held[which] = hold
+        if torch.cuda.is_current_stream_capturing():
+            # a replayed graph writes the SAME buffer every step, so the alternation cannot protect a slow
+            # rank that still reads it in its previous backward: wait until every rank has got here
+            self.key_hdl[which].barrier(channel=2)
         be.l2norm_peers(view0, view1, self.key_ptrs[which], self.rank, self.ld, self.rows_dtype, inv_norm)
         self.key_hdl[which].barrier(channel=0)
-        return self.keys[which]
+        return self.keys[which], which
+
+    def release(self, which: int) -> None:
+        self.held[which] = False
 
     def gather_vectors(self, be, mine: torch.Tensor) -> torch.Tensor:
         """``mine`` = (2, q_rows) [row sums ; row weights] of this rank -> (world, 2, q_rows) of every rank."""

@@ -46,3 +46,7 @@ print(f"tiles per CTA {tiles:.1f}")
 for name, v in zip(names, m):
     if name:
         print(f"{name:24s} {v:10.0f} cycles  {v / tiles:8.1f} per tile")
+
+if os.environ.get("NTX_TIMELINE"):
+    print(f"bwd timeline (cycles from kernel entry, mean / max over CTAs): first S tile ready {m[0]:.0f} / {buf[:,0].max()}, "
+          f"last own tile of group 0 done {m[1]:.0f} / {buf[:,1].max()}, after the final drain {m[2]:.0f} / {buf[:,2].max()}")
