@@ -626,18 +626,19 @@ tc_fwd_sym_kernel(const __grid_constant__ CUtensorMap tmap, NtxDims dm, int key_
             const bool last_of_seg = (i + 1 == n_tiles) || it.last_in_row();
             const bool offdiag = kt != rb;
             if (turn == g) {
-                { NTX_TIC(te_cs); if (pending) store_colsum(); NTX_TOC(te_cs); }
                 { NTX_TIC(te_wait); mbar_wait(&ctl->s_full[g], own & 1); NTX_TOC(te_wait); }
                 ++own;
                 tc_fence_after();
+                uint32_t v[2][32];
+                tmem_ld_32x32(taddr, v[0]);
+                // the previous tile's column sums are read out behind the first S load: one TMEM round trip for both
+                { NTX_TIC(te_cs); if (pending) store_colsum(); NTX_TOC(te_cs); }
                 const bool row_ok = rb * 128 + row_in_tile < dm.q_rows;
                 const bool edge = !offdiag || (kt * 128 + 128 > dm.k_rows) || (rb * 128 + 128 > dm.q_rows);
                 const int self = rb * 128 + row_in_tile;
                 uint8_t* e_row = e_smem + g * kEBytes + row_in_tile * 128;         // this group's own E tile
                 { NTX_TIC(te_ef); if (offdiag) mbar_wait(&ctl->e_free[g], (e_uses & 1) ^ 1); NTX_TOC(te_ef); }   // column-sum MMA that read it is done
                 NTX_TIC(te_loop);
-                uint32_t v[2][32];
-                tmem_ld_32x32(taddr, v[0]);
 #pragma unroll
                 for (int ch = 0; ch < 4; ++ch) {
                     tmem_ld_wait_dep(v[ch & 1]);
