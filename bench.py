@@ -33,7 +33,10 @@ sys.path.insert(0, ROOT)
 N_GLOBAL, DIM, TAU, SEED = 8192, 128, 0.5, 7
 METRIC, UNIT = "ntxent_fwd_bwd_pairs_per_sec", "pairs/s"
 FALLBACK_TFLOPS = 1590.0          # B200_PROFILING.md fallback when MEASURED_PEAKS.json is absent
-KERNELS_PER_STEP = 5              # l2norm, fwd, fwd_finalize, bwd, bwd_finalize
+KERNELS_PER_STEP = 5              # l2norm, fwd, fwd_finalize, bwd, bwd_finalize (+ the scatter kernel with peer gather)
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE tc_bwd_kernel<2> launch at config 4 on one GPU, from the
+# committed `ncu --set full` capture (profiles/r01b_all_kernels_ncu_full_summary.csv): the keys once, nothing else
+BWD_TRAFFIC_BYTES_C4_1GPU = 4328192
 
 
 def parse():
@@ -442,9 +445,11 @@ def run_ours(args):
                            "copy of step k+1 overlaps step k), module forward + backward, loss read on the host",
                     "serial_ms_per_step": e2e_serial_ms / K,
                     "serial_value": N_GLOBAL / (e2e_serial_ms / K * 1e-3)},
-            "gpu_launches": KERNELS_PER_STEP * K,
+            "gpu_launches": (KERNELS_PER_STEP + (1 if GATHER_BACKEND == "peer" else 0)) * K,
             "roofline": {"bound": "tensor", "kernel": f"tc_bwd_kernel<{DIM // 64}>", "achieved": achieved, "peak": peak,
-                         "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
+                         "unit": "TFLOP/s", "frac": achieved / peak,
+                         "traffic": BWD_TRAFFIC_BYTES_C4_1GPU if (world == 1 and N_GLOBAL == 8192 and DIM == 128) else None,
+                         "traffic_source": "ncu --set full, profiles/r01b_all_kernels_ncu_full_summary.csv (bytes per launch)",
                          "peak_source": peak_src, "algorithmic_flops_per_launch": bwd_flops,
                          "kernel_ms": bwd_ms,
                          "executed_flops_per_launch": bwd_executed,
