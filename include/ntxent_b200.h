@@ -97,6 +97,15 @@ int ntx_plan(int q_rows, int k_rows, int d, int dtype, int sm_count, NtxPlan* pl
 int ntx_l2norm(const void* view0, const void* view1, int n, int d, int in_dtype,
                void* rows, int ld, int rows_dtype, float* inv_norm, void* stream);
 
+/* ntx_l2norm with the projection head's last layer in front of it:
+ *   rows = normalize([h0 ; h1] . weight^T),  h0/h1: (n x hdim) bf16, weight: (d x hdim) bf16 as nn.Linear stores it.
+ * Replaces Linear(h -> d, bias=False) of the reference's head (model.py:69) followed by the two F.normalize calls
+ * (loss.py:33-34); the (2n x d) projections are never written, only their normalised bf16 rows ([2n x ld],
+ * ld = ntx_row_pitch(d, NTX_BF16)) and inv_norm.  hdim must be a multiple of 64, d <= 256.  One tcgen05 GEMM tile
+ * per 128 rows with the normalisation as its epilogue. */
+int ntx_project_l2norm(const void* h0, const void* h1, const void* weight, int n, int hdim, int d, void* rows,
+                       int ld, float* inv_norm, void* stream);
+
 /* Multi-rank gather without a collective library call (one node, NVLink / NVSwitch peer memory).
  * ntx_l2norm_peers is ntx_l2norm whose output goes straight into every rank's key buffer: peer_keys[p] is the
  * address, mapped into this process, of rank p's [world*2n x ld] key buffer (peer_keys[rank] is this rank's own);

@@ -20,7 +20,7 @@ DTYPES = {torch.float32: NTX_F32, torch.bfloat16: NTX_BF16}
 EXPORTS = (
     "ntx_version", "ntx_last_error", "ntx_row_pitch", "ntx_plan", "ntx_l2norm", "ntx_fwd",
     "ntx_bwd", "ntx_debug_indices", "ntx_profile_next", "ntx_fwd_static", "ntx_l2norm_peers",
-    "ntx_scatter_peers",
+    "ntx_scatter_peers", "ntx_project_l2norm",
 )
 
 
@@ -62,6 +62,7 @@ def _declare(lib):
     lib.ntx_fwd_static.argtypes = [vp, vp, i, i, i, i, i, ctypes.POINTER(NtxLayout), f, vp, vp, vp, vp, vp]
     lib.ntx_l2norm_peers.argtypes = [vp, vp, i, i, i, ctypes.POINTER(vp), i, i, i, i, vp, vp]
     lib.ntx_scatter_peers.argtypes = [vp, sz, ctypes.POINTER(vp), i, sz, vp]
+    lib.ntx_project_l2norm.argtypes = [vp, vp, vp, i, i, i, vp, i, vp, vp]
     lib.ntx_debug_indices.argtypes = [ctypes.POINTER(NtxLayout), vp, vp, vp]
     lib.ntx_profile_next.argtypes = [i, vp, vp]
     for name in EXPORTS:
@@ -113,6 +114,12 @@ class Backend:
         _check(load().ntx_l2norm(view0.data_ptr(), view1.data_ptr(), n, d, DTYPES[view0.dtype],
                                  rows.data_ptr(), rows.shape[1], DTYPES[rows.dtype],
                                  inv_norm.data_ptr(), _stream(rows)))
+
+    def project_l2norm(self, h0, h1, weight, rows, inv_norm):
+        """ntx_project_l2norm: rows = normalize([h0 ; h1] @ weight.T) (bf16), the projections never stored."""
+        n, hdim = h0.shape
+        _check(load().ntx_project_l2norm(h0.data_ptr(), h1.data_ptr(), weight.data_ptr(), n, hdim, weight.shape[0],
+                                         rows.data_ptr(), rows.shape[1], inv_norm.data_ptr(), _stream(rows)))
 
     def l2norm_peers(self, view0, view1, peer_ptrs, rank, ld, rows_dtype, inv_norm):
         """ntx_l2norm_peers: normalised rows written into rows [rank*2n, (rank+1)*2n) of every rank's

@@ -191,6 +191,20 @@ int ntx_l2norm(const void* view0, const void* view1, int n, int d, int in_dtype,
     return ntx_l2norm_launch(view0, view1, n, d, in_dtype, dst, 0, ld, rows_dtype, inv_norm, (cudaStream_t)stream);
 }
 
+int ntx_project_l2norm(const void* h0, const void* h1, const void* weight, int n, int hdim, int d, void* rows,
+                       int ld, float* inv_norm, void* stream) {
+    NTX_CHECK_ARG(n >= 1 && d >= 1 && hdim >= 64, "bad sizes n=%d hdim=%d d=%d", n, hdim, d);
+    NTX_CHECK_ARG(hdim % 64 == 0, "hidden size %d must be a multiple of 64 (one 128-byte TMA row of bf16)", hdim);
+    NTX_CHECK_ARG(h0 && h1 && weight && rows && inv_norm, "NULL buffer");
+    NTX_CHECK_ARG(d <= 256, "bf16 rows support d <= 256 (got %d)", d);
+    NTX_CHECK_ARG(ld == ntx_row_pitch(d, NTX_BF16), "ld=%d must be ntx_row_pitch(d=%d, bf16)=%d", ld, d,
+                  ntx_row_pitch(d, NTX_BF16));
+    NTX_CHECK_ARG(reinterpret_cast<uintptr_t>(h0) % 16 == 0 && reinterpret_cast<uintptr_t>(h1) % 16 == 0 &&
+                      reinterpret_cast<uintptr_t>(weight) % 16 == 0 && reinterpret_cast<uintptr_t>(rows) % 16 == 0,
+                  "buffers must be 16-byte aligned");
+    return ntx_project_launch(h0, h1, weight, n, hdim, d, rows, ld, inv_norm, (cudaStream_t)stream);
+}
+
 static int fill_peers(NtxPeers* out, void* const* peers, int world, const char* who) {
     if (world < 1 || world > NTX_MAX_PEERS) {
         ntx_set_error("%s: world=%d outside [1, %d] (peer memory spans one node)", who, world, NTX_MAX_PEERS);

@@ -142,6 +142,9 @@ struct NtxPeers {
 int ntx_l2norm_launch(const void* v0, const void* v1, int n, int d, int in_dtype, const NtxPeers& rows,
                       size_t row_offset, int ld, int rows_dtype, float* inv_norm, cudaStream_t st);
 int ntx_scatter_launch(const void* src, size_t bytes, const NtxPeers& dst, size_t dst_offset, cudaStream_t st);
+int ntx_make_rows_tmap(void* map, const void* base, int rows, int ld, int box_rows);      // map = CUtensorMap*
+int ntx_project_launch(const void* h0, const void* h1, const void* weight, int n, int hdim, int d, void* rows, int ld,
+                       float* inv_norm, cudaStream_t st);
 int ntx_simt_fwd_launch(const float* q, const float* k, const NtxDims& dm, const NtxPlan& plan,
                         float* partial, unsigned int* counter, cudaStream_t st);
 int ntx_simt_bwd_launch(const float* q, const float* k, const NtxDims& dm, const NtxPlan& plan,

@@ -1045,13 +1045,13 @@ int get_encode_fn(EncodeTiledFn* out) {
 }
 
 // [rows x ld] bf16 row buffer -> tiles of 128 rows x 64 features, 128B swizzle, zero OOB fill
-int make_rows_tmap(CUtensorMap* m, const __nv_bfloat16* base, int rows, int ld) {
+int make_rows_tmap(CUtensorMap* m, const __nv_bfloat16* base, int rows, int ld, int box_rows = 128) {
     EncodeTiledFn enc;
     int rc = get_encode_fn(&enc);
     if (rc) return rc;
     const cuuint64_t dims[2] = {(cuuint64_t)ld, (cuuint64_t)rows};
     const cuuint64_t strides[1] = {(cuuint64_t)ld * sizeof(__nv_bfloat16)};
-    const cuuint32_t box[2] = {64, 128};
+    const cuuint32_t box[2] = {64, (cuuint32_t)box_rows};
     const cuuint32_t estr[2] = {1, 1};
     CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, (void*)base, dims, strides, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
@@ -1093,6 +1093,11 @@ int launch_bwd(const CUtensorMap& mq, const CUtensorMap& mk, const NtxDims& dm, 
 }
 
 }  // namespace
+
+// [rows x ld] bf16 row-major -> TMA map with boxes of box_rows rows x 64 columns, 128B swizzle (for ntx_project.cu)
+int ntx_make_rows_tmap(void* map, const void* base, int rows, int ld, int box_rows) {
+    return make_rows_tmap(static_cast<CUtensorMap*>(map), static_cast<const __nv_bfloat16*>(base), rows, ld, box_rows);
+}
 
 #ifdef NTX_TIMING
 extern "C" int ntx_debug_timers(long long* host_out) {   // 148 x 16 cycle counters

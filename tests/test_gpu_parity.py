@@ -333,3 +333,28 @@ def test_peer_entry_points_with_local_buffers(in_dtype, rows_dtype, dev):
         assert torch.equal(t[rank], src) and float(t[0].abs().sum()) == 0.0
     with pytest.raises(_cabi.NtxError, match="world"):
         be.scatter_peers(src, [vecs[0].data_ptr()] * 9, 0)
+
+
+@pytest.mark.parametrize("n,hdim,d", [(8192, 512, 128), (300, 512, 128), (77, 2048, 128), (130, 64, 64),
+                                       (64, 128, 200), (5, 512, 100)])
+def test_project_l2norm_matches_linear_then_normalize(n, hdim, d, dev):
+    """ntx_project_l2norm = F.normalize(Linear(h -> d, bias=False)(h)) of model.py:69 + loss.py:33-34, computed
+    in fp32 from the same bf16 inputs: rows within bf16 rounding, inv_norm to 2e-3, padding columns zero,
+    tiles that end inside a view, hidden sizes of 1, 2, 8 and 32 TMA blocks."""
+    from simclr_b200 import _cabi
+    be = _cabi.Backend()
+    g = torch.Generator().manual_seed(n + hdim + d)
+    h0 = torch.randn(n, hdim, generator=g).bfloat16().to(dev)
+    h1 = torch.randn(n, hdim, generator=g).bfloat16().to(dev)
+    w = (torch.randn(d, hdim, generator=g) / hdim ** 0.5).bfloat16().to(dev)
+    ld = be.row_pitch(d, torch.bfloat16)
+    rows = torch.full((2 * n, ld), 9.0, dtype=torch.bfloat16, device=dev)
+    inv = torch.empty(2 * n, device=dev)
+    be.project_l2norm(h0, h1, w, rows, inv)
+    torch.cuda.synchronize()
+    z = torch.cat([h0, h1]).float() @ w.float().T                            # fp32 reference on the bf16 inputs
+    want = torch.nn.functional.normalize(z, p=2, dim=1)
+    assert (rows[:, :d].float() - want).abs().max().item() <= 4e-3
+    if ld > d:
+        assert rows[:, d:].float().abs().max().item() == 0.0
+    assert torch.allclose(inv, 1.0 / z.norm(dim=1).clamp_min(1e-12), rtol=2e-3)
