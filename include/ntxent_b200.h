@@ -159,6 +159,16 @@ int ntx_bwd(const void* q_rows_ptr, const void* k_rows_ptr, int q_rows, int k_ro
             const void* view0, const void* view1, int in_dtype, const float* inv_norm, void* dview0,
             void* dview1, void* workspace, size_t workspace_bytes, void* stream);
 
+/* ntx_bwd for callers that hold no un-normalised inputs (the rows came from ntx_project_l2norm): the gradient
+ * with respect to the projections z = [h0 ; h1] . W^T, as one (q_rows x d) matrix dz in the rows' dtype.  The
+ * normalisation Jacobian is taken from the normalised rows and inv_norm:
+ *   dz_r = inv_norm_r * (g_r - zhat_r <zhat_r, g_r>),  g = d loss / d zhat.
+ * The caller finishes the layer with two library GEMMs: dh = dz . W, dW = dz^T . [h0 ; h1]. */
+int ntx_bwd_rows(const void* q_rows_ptr, const void* k_rows_ptr, int q_rows, int k_rows, int d, int ld, int dtype,
+                 const NtxLayout* layout, float temperature, const float* rowsum_q, const float* rowsum_k,
+                 const float* w_q, const float* w_k, int w_stride, float w_scale, const float* inv_norm, void* dz,
+                 void* workspace, size_t workspace_bytes, void* stream);
+
 /* ntx_fwd without a caller-supplied scratch buffer.  This entry point has no counterpart in the
  * reference.  It is for hosts that hold nothing but their input and output buffers and cannot
  * obtain device scratch themselves: a plain C / ctypes caller that has no device allocator of

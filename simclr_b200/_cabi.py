@@ -20,7 +20,7 @@ DTYPES = {torch.float32: NTX_F32, torch.bfloat16: NTX_BF16}
 EXPORTS = (
     "ntx_version", "ntx_last_error", "ntx_row_pitch", "ntx_plan", "ntx_l2norm", "ntx_fwd",
     "ntx_bwd", "ntx_debug_indices", "ntx_profile_next", "ntx_fwd_static", "ntx_l2norm_peers",
-    "ntx_scatter_peers", "ntx_project_l2norm",
+    "ntx_scatter_peers", "ntx_project_l2norm", "ntx_bwd_rows",
 )
 
 
@@ -63,6 +63,8 @@ def _declare(lib):
     lib.ntx_l2norm_peers.argtypes = [vp, vp, i, i, i, ctypes.POINTER(vp), i, i, i, i, vp, vp]
     lib.ntx_scatter_peers.argtypes = [vp, sz, ctypes.POINTER(vp), i, sz, vp]
     lib.ntx_project_l2norm.argtypes = [vp, vp, vp, i, i, i, vp, i, vp, vp]
+    lib.ntx_bwd_rows.argtypes = [vp, vp, i, i, i, i, i, ctypes.POINTER(NtxLayout), f, vp, vp, vp, vp, i, f, vp, vp,
+                                 vp, sz, vp]
     lib.ntx_debug_indices.argtypes = [ctypes.POINTER(NtxLayout), vp, vp, vp]
     lib.ntx_profile_next.argtypes = [i, vp, vp]
     for name in EXPORTS:
@@ -164,6 +166,16 @@ class Backend:
                               inv_norm.data_ptr(), dview0.data_ptr(), dview1.data_ptr(),
                               workspace.data_ptr(), workspace.numel() * workspace.element_size(),
                               _stream(q)))
+
+    def bwd_rows(self, q, k, d, layout, temperature, rowsum_q, rowsum_k, w_q, w_k, w_stride, w_scale, inv_norm, dz,
+                 workspace):
+        """ntx_bwd_rows: gradient with respect to the un-normalised projections, from the normalised rows."""
+        lay = NtxLayout(*layout)
+        _check(load().ntx_bwd_rows(q.data_ptr(), k.data_ptr(), q.shape[0], k.shape[0], d, q.shape[1],
+                                   DTYPES[q.dtype], ctypes.byref(lay), float(temperature), rowsum_q.data_ptr(),
+                                   rowsum_k.data_ptr(), w_q.data_ptr(), w_k.data_ptr(), int(w_stride),
+                                   float(w_scale), inv_norm.data_ptr(), dz.data_ptr(), workspace.data_ptr(),
+                                   workspace.numel() * workspace.element_size(), _stream(q)))
 
     def profile_next(self, which: int, ev_start: "torch.cuda.Event", ev_stop: "torch.cuda.Event"):
         """Arm the measurement hook: the next fwd (0) / bwd (1) call on this thread brackets its

@@ -292,11 +292,11 @@ int ntx_fwd(const void* q, const void* k, int q_rows, int k_rows, int d, int ld,
                                    pos_logit, row_loss, loss_sum, st);
 }
 
-int ntx_bwd(const void* q, const void* k, int q_rows, int k_rows, int d, int ld, int dtype,
-            const NtxLayout* layout, float temperature, const float* rowsum_q, const float* rowsum_k,
-            const float* w_q, const float* w_k, int w_stride, float w_scale, const void* view0,
-            const void* view1, int in_dtype, const float* inv_norm, void* dview0, void* dview1,
-            void* workspace, size_t workspace_bytes, void* stream) {
+static int bwd_impl(const void* q, const void* k, int q_rows, int k_rows, int d, int ld, int dtype,
+                    const NtxLayout* layout, float temperature, const float* rowsum_q, const float* rowsum_k,
+                    const float* w_q, const float* w_k, int w_stride, float w_scale, const void* view0,
+                    const void* view1, int in_dtype, int in_ld, int normalised, const float* inv_norm,
+                    void* dview0, void* dview1, void* workspace, size_t workspace_bytes, void* stream) {
     NtxDims dm;
     int rc = make_dims(q_rows, k_rows, d, ld, dtype, layout, temperature, &dm);
     if (rc) return rc;
@@ -325,7 +325,34 @@ int ntx_bwd(const void* q, const void* k, int q_rows, int k_rows, int d, int ld,
     }
     if (rc) return rc;
     return ntx_bwd_finalize_launch(dm, plan, partial, wt, view0, view1, in_dtype, inv_norm, dview0,
-                                   dview1, st);
+                                   dview1, st, in_ld, normalised);
+}
+
+int ntx_bwd(const void* q, const void* k, int q_rows, int k_rows, int d, int ld, int dtype,
+            const NtxLayout* layout, float temperature, const float* rowsum_q, const float* rowsum_k,
+            const float* w_q, const float* w_k, int w_stride, float w_scale, const void* view0,
+            const void* view1, int in_dtype, const float* inv_norm, void* dview0, void* dview1,
+            void* workspace, size_t workspace_bytes, void* stream) {
+    return bwd_impl(q, k, q_rows, k_rows, d, ld, dtype, layout, temperature, rowsum_q, rowsum_k, w_q, w_k, w_stride,
+                    w_scale, view0, view1, in_dtype, 0, 0, inv_norm, dview0, dview1, workspace, workspace_bytes,
+                    stream);
+}
+
+int ntx_bwd_rows(const void* q, const void* k, int q_rows, int k_rows, int d, int ld, int dtype,
+                 const NtxLayout* layout, float temperature, const float* rowsum_q, const float* rowsum_k,
+                 const float* w_q, const float* w_k, int w_stride, float w_scale, const float* inv_norm, void* dz,
+                 void* workspace, size_t workspace_bytes, void* stream) {
+    NTX_CHECK_ARG(q != nullptr && dz != nullptr && layout != nullptr, "NULL buffer");
+    NTX_CHECK_ARG(dtype == NTX_F32 || dtype == NTX_BF16, "rows dtype %d not supported", dtype);
+    const size_t esz = dtype == NTX_BF16 ? 2 : 4;
+    const int n = layout->n_local;
+    NTX_CHECK_ARG((size_t)n * d * esz % 16 == 0, "n_local * d * sizeof(element) must be a multiple of 16");
+    // the normalised rows of this rank stand in for the views: rows [0, n) and [n, 2n), pitch ld
+    const char* qb = static_cast<const char*>(q);
+    char* out = static_cast<char*>(dz);
+    return bwd_impl(q, k, q_rows, k_rows, d, ld, dtype, layout, temperature, rowsum_q, rowsum_k, w_q, w_k, w_stride,
+                    w_scale, qb, qb + (size_t)n * ld * esz, dtype, ld, 1, inv_norm, out, out + (size_t)n * d * esz,
+                    workspace, workspace_bytes, stream);
 }
 
 }  // extern "C"

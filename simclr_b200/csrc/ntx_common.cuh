@@ -165,4 +165,5 @@ int ntx_debug_indices_launch(int n_local, int rank, int32_t* self_col, int32_t* 
                              cudaStream_t st);
 int ntx_bwd_finalize_launch(const NtxDims& dm, const NtxPlan& plan, const float* partial,
                             const NtxWeights& w, const void* view0, const void* view1, int in_dtype,
-                            const float* inv_norm, void* dview0, void* dview1, cudaStream_t st);
+                            const float* inv_norm, void* dview0, void* dview1, cudaStream_t st, int in_ld = 0,
+                            int normalised = 0);

@@ -150,6 +150,8 @@ struct BwdFinArgs {
     const float* partial;
     NtxWeights w;
     const float* inv_norm;
+    int in_ld;          // elements between consecutive input rows (d for the caller's views)
+    int normalised;     // 1: view0/view1 hold the NORMALISED rows (ntx_bwd_rows), 0: the raw inputs
 };
 
 __device__ __forceinline__ float pair_weight(const NtxWeights& w, int r, int p) {
@@ -178,10 +180,11 @@ bwd_finalize_vec_kernel(BwdFinArgs A, int lanes, const TIn* __restrict__ view0,
     const int n = dm.n_local, d = dm.d;
     const int p = ntx_pos_row(r, n);
     const int ns = ns_sh;
-    const TIn* zr = r < n ? view0 + (size_t)r * d : view1 + (size_t)(r - n) * d;
-    const TIn* zp = p < n ? view0 + (size_t)p * d : view1 + (size_t)(p - n) * d;
+    const TIn* zr = r < n ? view0 + (size_t)r * A.in_ld : view1 + (size_t)(r - n) * A.in_ld;
+    const TIn* zp = p < n ? view0 + (size_t)p * A.in_ld : view1 + (size_t)(p - n) * A.in_ld;
     TIn* out = r < n ? dview0 + (size_t)r * d : dview1 + (size_t)(r - n) * d;
     const float inr = __ldg(A.inv_norm + r), inp = __ldg(A.inv_norm + p);
+    const float sr = A.normalised ? 1.f : inr, sp = A.normalised ? 1.f : inp;   // input rows -> unit rows
     const float wpair = pair_weight(A.w, r, p);
     const float* part = A.partial + (size_t)r * A.d_pad;
     const size_t slot_stride = (size_t)A.rows_pad * A.d_pad;
@@ -198,10 +201,10 @@ bwd_finalize_vec_kernel(BwdFinArgs A, int lanes, const TIn* __restrict__ view0,
                 acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
             }
             const float4 zpv = ld4(zp + c), zrv = ld4(zr + c);
-            const float k = wpair * inp, it = dm.inv_tau;
+            const float k = wpair * sp, it = dm.inv_tau;
             g[v] = make_float4((acc.x - k * zpv.x) * it, (acc.y - k * zpv.y) * it, (acc.z - k * zpv.z) * it,
                                (acc.w - k * zpv.w) * it);
-            zh[v] = make_float4(zrv.x * inr, zrv.y * inr, zrv.z * inr, zrv.w * inr);
+            zh[v] = make_float4(zrv.x * sr, zrv.y * sr, zrv.z * sr, zrv.w * sr);
             proj = fmaf(zh[v].x, g[v].x, fmaf(zh[v].y, g[v].y, fmaf(zh[v].z, g[v].z, fmaf(zh[v].w, g[v].w, proj))));
         }
     }
@@ -235,10 +238,11 @@ bwd_finalize_kernel(BwdFinArgs A, const TIn* __restrict__ view0, const TIn* __re
     const int n = dm.n_local, d = dm.d;
     const int p = ntx_pos_row(r, n);
     const int ns = ntx_num_slots(A.Tt, A.G, A.key_tiles, r / A.tile_rows);
-    const TIn* zr = r < n ? view0 + (size_t)r * d : view1 + (size_t)(r - n) * d;
-    const TIn* zp = p < n ? view0 + (size_t)p * d : view1 + (size_t)(p - n) * d;
+    const TIn* zr = r < n ? view0 + (size_t)r * A.in_ld : view1 + (size_t)(r - n) * A.in_ld;
+    const TIn* zp = p < n ? view0 + (size_t)p * A.in_ld : view1 + (size_t)(p - n) * A.in_ld;
     TIn* out = r < n ? dview0 + (size_t)r * d : dview1 + (size_t)(r - n) * d;
     const float inr = __ldg(A.inv_norm + r), inp = __ldg(A.inv_norm + p);
+    const float sr = A.normalised ? 1.f : inr, sp = A.normalised ? 1.f : inp;
     const float wpair = pair_weight(A.w, r, p);
     const float* part = A.partial + (size_t)r * A.d_pad;
     const size_t slot_stride = (size_t)A.rows_pad * A.d_pad;
@@ -246,15 +250,15 @@ bwd_finalize_kernel(BwdFinArgs A, const TIn* __restrict__ view0, const TIn* __re
     auto dzhat = [&](int c) {
         float acc = 0.f;
         for (int s = 0; s < ns; ++s) acc += __ldg(part + s * slot_stride + c);
-        return (acc - wpair * (ldf(zp, c) * inp)) * dm.inv_tau;
+        return (acc - wpair * (ldf(zp, c) * sp)) * dm.inv_tau;
     };
     float proj = 0.f;
-    for (int c = lane; c < d; c += 32) proj = fmaf(ldf(zr, c) * inr, dzhat(c), proj);
+    for (int c = lane; c < d; c += 32) proj = fmaf(ldf(zr, c) * sr, dzhat(c), proj);
     proj = group_sum(proj, 32);
     const bool clamped = inr >= 1e12f;
     for (int c = lane; c < d; c += 32) {
         const float g = dzhat(c);
-        stf(out, c, clamped ? g * inr : (g - ldf(zr, c) * inr * proj) * inr);
+        stf(out, c, clamped ? g * inr : (g - ldf(zr, c) * sr * proj) * inr);
     }
 }
 
@@ -275,7 +279,7 @@ template <typename TIn>
 int launch_bwd_finalize(const BwdFinArgs& A, const void* view0, const void* view1, void* dview0,
                         void* dview1, cudaStream_t st) {
     const int d = A.dm.d;
-    const bool vec = d % 4 == 0 && d <= 1024 &&
+    const bool vec = d % 4 == 0 && d <= 1024 && A.in_ld % 4 == 0 &&
                      reinterpret_cast<uintptr_t>(view0) % 16 == 0 && reinterpret_cast<uintptr_t>(view1) % 16 == 0 &&
                      reinterpret_cast<uintptr_t>(dview0) % 16 == 0 && reinterpret_cast<uintptr_t>(dview1) % 16 == 0;
     if (vec) {
@@ -336,7 +340,8 @@ int ntx_fwd_finalize_launch(const void* q, int dtype, const NtxDims& dm, const N
 
 int ntx_bwd_finalize_launch(const NtxDims& dm, const NtxPlan& plan, const float* partial,
                             const NtxWeights& w, const void* view0, const void* view1, int in_dtype,
-                            const float* inv_norm, void* dview0, void* dview1, cudaStream_t st) {
+                            const float* inv_norm, void* dview0, void* dview1, cudaStream_t st, int in_ld,
+                            int normalised) {
     BwdFinArgs A;
     A.dm = dm;
     A.tile_rows = plan.tile_rows;
@@ -348,6 +353,8 @@ int ntx_bwd_finalize_launch(const NtxDims& dm, const NtxPlan& plan, const float*
     A.partial = partial;
     A.w = w;
     A.inv_norm = inv_norm;
+    A.in_ld = in_ld > 0 ? in_ld : dm.d;
+    A.normalised = normalised;
     if (in_dtype == NTX_F32) return launch_bwd_finalize<float>(A, view0, view1, dview0, dview1, st);
     return launch_bwd_finalize<__nv_bfloat16>(A, view0, view1, dview0, dview1, st);
 }

@@ -139,6 +139,54 @@ class NTXentFunction(torch.autograd.Function):
         return dview0, dview1, None, None, None, None, None, None, None
 
 
+class NTXentHiddenFunction(torch.autograd.Function):
+    """NT-Xent taken one layer earlier: inputs are the activations in front of the head's last
+    ``Linear(h, d, bias=False)`` (model.py:69) and that layer's weight.  The projections z = h @ W.T exist only
+    inside a tcgen05 GEMM whose epilogue normalises them (``ntx_project_l2norm``); backward gets dz from the
+    normalised rows (``ntx_bwd_rows``) and finishes the layer with two library GEMMs."""
+
+    @staticmethod
+    def forward(ctx, h0, h1, weight, temperature, reduction):
+        be = _backend
+        n = h0.shape[0]
+        d = weight.shape[0]
+        dev = h0.device
+        q_rows = 2 * n
+        ld, ws_bytes = _shape_info(be, q_rows, q_rows, d, torch.bfloat16, dev)
+        rows = torch.empty((q_rows, ld), dtype=torch.bfloat16, device=dev)
+        stats = torch.empty((4, q_rows), dtype=torch.float32, device=dev)   # inv_norm, rowsum, pos, row loss
+        loss_sum = torch.empty(2, dtype=torch.float32, device=dev)
+        be.project_l2norm(h0, h1, weight, rows, stats[0])
+        be.fwd(rows, rows, d, (n, 1, 0), temperature, stats[1], stats[2], stats[3], loss_sum,
+               _workspace(dev, ws_bytes))
+        ctx.save_for_backward(h0, h1, weight, rows, stats)
+        ctx.meta = (temperature, reduction, d, ws_bytes)
+        if reduction == "none":
+            out = stats[3].view(2, n).clone()
+        elif reduction == "sum":
+            out = loss_sum[0]
+        else:
+            out = loss_sum[1]
+        return out.to(h0.dtype)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        be = _backend
+        h0, h1, weight, rows, stats = ctx.saved_tensors
+        temperature, reduction, d, ws_bytes = ctx.meta
+        n = h0.shape[0]
+        q_rows = 2 * n
+        g = grad_out.detach().to(torch.float32).contiguous().view(-1)
+        w_stride = 1 if reduction == "none" else 0
+        w_scale = 1.0 / q_rows if reduction == "mean" else 1.0
+        dz = torch.empty((q_rows, d), dtype=torch.bfloat16, device=h0.device)
+        be.bwd_rows(rows, rows, d, (n, 1, 0), temperature, stats[1], stats[1], g, g, w_stride, w_scale, stats[0],
+                    dz, _workspace(h0.device, ws_bytes))
+        dh = dz @ weight                                                     # (2n, d) . (d, h)
+        dw = torch.addmm(dz[n:].t() @ h1, dz[:n].t(), h0)                    # dz^T . [h0 ; h1]
+        return dh[:n], dh[n:], dw, None, None
+
+
 class NT_Xent(torch.nn.Module):
     """
     Normalised temperature-scaled cross entropy loss (B200 implementation).
@@ -217,6 +265,27 @@ class NT_Xent(torch.nn.Module):
         return NTXentFunction.apply(view0.contiguous(), view1.contiguous(), float(self.temperature),
                                     self.reduction, rows_dtype, group, world, rank,
                                     world > 1 and self.gather_backend == "peer")
+
+    def forward_hidden(self, h0: torch.Tensor, h1: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
+        """
+        The loss of ``z0 = h0 @ weight.T``, ``z1 = h1 @ weight.T`` without materialising ``z0``, ``z1``: the last
+        layer of the projection head (``Linear(h, d, bias=False)``, model.py:69) runs fused with the normalisation.
+        bfloat16 only, single rank, hidden size a multiple of 64, d <= 256.
+
+        :param h0: activations in front of the head's last layer for the first view, shape (N, H).
+        :param h1: the same for the other view.
+        :param weight: that layer's ``weight``, shape (D, H).
+        :return: same as ``forward``.
+        """
+        if h0.dim() != 2 or h1.shape != h0.shape or weight.dim() != 2 or weight.shape[1] != h0.shape[1]:
+            raise RuntimeError(f"forward_hidden expects (N, H), (N, H), (D, H); got {tuple(h0.shape)}, "
+                               f"{tuple(h1.shape)}, {tuple(weight.shape)}")
+        if not (h0.dtype == h1.dtype == weight.dtype == torch.bfloat16):
+            raise TypeError("forward_hidden runs on the bf16 tensor-core path: h0, h1 and weight must be bfloat16")
+        if h0.device.type != "cuda":
+            raise RuntimeError("NT_Xent (B200) has no CPU path: inputs must be CUDA tensors")
+        return NTXentHiddenFunction.apply(h0.contiguous(), h1.contiguous(), weight.contiguous(),
+                                          float(self.temperature), self.reduction)
 
     def extra_repr(self) -> str:
         return (f"temperature={self.temperature}, reduction={self.reduction!r}, gather={self.gather}, "

@@ -358,3 +358,28 @@ def test_project_l2norm_matches_linear_then_normalize(n, hdim, d, dev):
     if ld > d:
         assert rows[:, d:].float().abs().max().item() == 0.0
     assert torch.allclose(inv, 1.0 / z.norm(dim=1).clamp_min(1e-12), rtol=2e-3)
+
+
+@pytest.mark.parametrize("n,hdim,d,tau,reduction", [(300, 512, 128, 0.5, "mean"), (1024, 512, 128, 0.2, "sum"),
+                                                    (96, 256, 64, 0.5, "none")])
+def test_forward_hidden_matches_linear_plus_loss(n, hdim, d, tau, reduction, dev):
+    """NT_Xent.forward_hidden(h0, h1, W) against the oracle applied to z = h @ W.T (fp64 on the same bf16 inputs):
+    loss, d/dh0, d/dh1 and d/dW (chain rule through the oracle's dz) within the bf16 tolerance."""
+    from simclr_b200 import NT_Xent
+    g = torch.Generator().manual_seed(3 * n + d)
+    h0 = torch.randn(n, hdim, generator=g).bfloat16()
+    h1 = (torch.randn(n, hdim, generator=g) + 0.5 * h0.float()).bfloat16()
+    w = (torch.randn(d, hdim, generator=g) / hdim ** 0.5).bfloat16()
+    gout = (torch.rand(2, n, generator=g) + 0.25) if reduction == "none" else None
+    H0, H1, W = (t.double().numpy() for t in (h0, h1, w))
+    wts = orc.weights_for(reduction, n, None if gout is None else gout.numpy())
+    ref = orc.ntxent_rows_fp64(H0 @ W.T, H1 @ W.T, tau, weights=wts)
+    dz0, dz1 = ref["dview0"], ref["dview1"]
+    want = {"h0": dz0 @ W, "h1": dz1 @ W, "w": dz0.T @ H0 + dz1.T @ H1}
+    t0, t1, tw = (t.to(dev).requires_grad_(True) for t in (h0, h1, w))
+    loss = NT_Xent(tau, reduction).forward_hidden(t0, t1, tw)
+    loss.backward(None if gout is None else gout.to(dev).to(loss.dtype))
+    assert rel_err(loss.detach().float().cpu().numpy(), orc.reduce_rows(ref["loss"], reduction)) < BF16_TOL
+    for name, t in (("h0", t0), ("h1", t1), ("w", tw)):
+        scale = np.abs(want[name]).max()
+        assert np.abs(t.grad.float().cpu().numpy() - want[name]).max() / scale < 2 * BF16_TOL, name
