@@ -4,7 +4,7 @@
 // the (2n x d) projections z are never written to memory, only their normalised rows and 1/||z||.
 //
 // One CTA per 128-row tile of one view: TMA streams 64-feature blocks of the h tile and of W through a
-// 4-stage ring (128B swizzle), tcgen05.mma (M128 x N = d_pad x K16, bf16 -> fp32) accumulates z in TMEM
+// 4- to 6-stage ring (128B swizzle), tcgen05.mma (M128 x N = d_pad x K16, bf16 -> fp32) accumulates z in TMEM
 // over hdim / 16 steps, and the four epilogue warps (one thread per row) read the accumulator twice:
 // sum of squares, then z / max(||z||, 1e-12) packed to bf16 and stored.  HBM-bound: the h tile (128 x hdim
 // bf16) is read once, W (d x hdim) comes from L2.
@@ -15,12 +15,14 @@ namespace {
 
 using namespace umma;
 
-constexpr int kStages = 4;
+// ring depth: 6 x (16 KB of h + 16 KB of W) = 192 KB at d_pad <= 128, 4 x 48 KB at d_pad = 256
+template <int NP> struct ProjStages { static constexpr int N = NP == 256 ? 4 : 6; };
+constexpr int kMaxStages = 6;
 constexpr int kThreads = 192;                 // 4 epilogue warps + TMA warp + MMA warp
 constexpr uint32_t kABytes = 128 * 128;       // [128 rows x 64 bf16]
 
 struct ProjCtl {
-    uint64_t full[kStages], empty[kStages], acc_full;
+    uint64_t full[kMaxStages], empty[kMaxStages], acc_full;
     uint32_t tmem_base;
 };
 
@@ -31,6 +33,7 @@ project_l2norm_kernel(const __grid_constant__ CUtensorMap tmap_h0, const __grid_
                       __nv_bfloat16* __restrict__ rows, int ld, float* __restrict__ inv_norm) {
     constexpr uint32_t kBBytes = NP * 128;    // [NP rows x 64 bf16]
     constexpr uint32_t kStageBytes = kABytes + kBBytes;
+    constexpr int kStages = ProjStages<NP>::N;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     ntx_dep_trigger();
     uint8_t* smem = smem_raw;
@@ -142,7 +145,7 @@ project_l2norm_kernel(const __grid_constant__ CUtensorMap tmap_h0, const __grid_
 template <int NP>
 int launch(const CUtensorMap& m0, const CUtensorMap& m1, const CUtensorMap& mw, int n, int hdim, int d, void* rows,
            int ld, float* inv_norm, cudaStream_t st) {
-    const size_t smem = (size_t)kStages * (kABytes + NP * 128) + sizeof(ProjCtl);
+    const size_t smem = (size_t)ProjStages<NP>::N * (kABytes + NP * 128) + sizeof(ProjCtl);
     NTX_CUDA(cudaFuncSetAttribute(project_l2norm_kernel<NP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int tiles_per_view = (n + 127) / 128;
     NTX_CUDA(ntx_launch_dep(project_l2norm_kernel<NP>, 2 * tiles_per_view, kThreads, smem, st, m0, m1, mw, n, hdim, d,
