@@ -92,3 +92,37 @@ def test_argument_errors_are_reported_without_a_device():
     assert lib.ntx_plan(16, 16, 512, 1, 148, ctypes.byref(p)) == -4     # bf16 rows wider than a tile
     with pytest.raises(_cabi.NtxError):
         _cabi.Backend().plan(16, 8, 8, torch.float32, 148)               # fewer keys than rows
+
+
+def test_newer_entry_points_validate_before_touching_the_device():
+    """Peer scatter / projection / rows-backward: argument errors come back as NTX_E_ARG with a message and no
+    CUDA call is made (fake, aligned, non-NULL addresses)."""
+    lib = _cabi.load()
+    vp = ctypes.c_void_p
+    two = (vp * 2)(4096, 8192)
+    nine = (vp * 9)(*[4096 * (i + 1) for i in range(9)])
+    holed = (vp * 2)(4096, None)
+    # peer tables: at most 8 ranks (one node), no NULL entries, rank inside the world
+    assert lib.ntx_scatter_peers(4096, 64, nine, 9, 0, None) == -1 and b"world=9" in lib.ntx_last_error()
+    assert lib.ntx_scatter_peers(4096, 64, holed, 2, 0, None) == -1 and b"NULL" in lib.ntx_last_error()
+    assert lib.ntx_scatter_peers(4100, 64, two, 2, 0, None) == -1 and b"aligned" in lib.ntx_last_error()
+    assert lib.ntx_scatter_peers(4096, 64, two, 2, 8, None) == -1 and b"aligned" in lib.ntx_last_error()
+    assert lib.ntx_l2norm_peers(4096, 4096, 4, 8, 0, two, 2, 2, 8, 0, 4096, None) == -1
+    assert b"rank 2" in lib.ntx_last_error()
+    assert lib.ntx_l2norm_peers(4096, 4096, 4, 8, 0, nine, 9, 0, 8, 0, 4096, None) == -1
+    # projection: hidden size in whole TMA blocks, row pitch of bf16 rows, d <= 256
+    assert lib.ntx_project_l2norm(4096, 4096, 4096, 4, 100, 64, 4096, 64, 4096, None) == -1
+    assert b"multiple of 64" in lib.ntx_last_error()
+    assert lib.ntx_project_l2norm(4096, 4096, 4096, 4, 128, 96, 4096, 96, 4096, None) == -1
+    assert b"ntx_row_pitch" in lib.ntx_last_error()
+    assert lib.ntx_project_l2norm(4096, 4096, 4096, 4, 128, 300, 4096, 320, 4096, None) == -1
+    assert lib.ntx_project_l2norm(4096, None, 4096, 4, 128, 64, 4096, 64, 4096, None) == -1
+    # rows-backward: output required, byte count of one view's gradient block 16-byte aligned
+    lay = _cabi.NtxLayout(4, 1, 0)
+    rc = lib.ntx_bwd_rows(4096, 4096, 8, 8, 8, 64, 1, ctypes.byref(lay), 0.5, 4096, 4096, 4096, 4096, 0, 1.0, 4096,
+                          None, 4096, 64, None)
+    assert rc == -1 and b"NULL" in lib.ntx_last_error()
+    lay3 = _cabi.NtxLayout(3, 1, 0)
+    rc = lib.ntx_bwd_rows(4096, 4096, 6, 6, 1, 64, 1, ctypes.byref(lay3), 0.5, 4096, 4096, 4096, 4096, 0, 1.0, 4096,
+                          4096, 4096, 64, None)
+    assert rc == -1 and b"multiple of 16" in lib.ntx_last_error()
