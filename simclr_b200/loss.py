@@ -39,7 +39,7 @@ def _shape_info(be, q_rows: int, k_rows: int, d: int, rows_dtype: torch.dtype, d
 
 def _workspace(device: torch.device, nbytes: int) -> torch.Tensor:
     """Scratch for the partial row sums / dZ slabs, cached per (device, stream)."""
-    key = (device, torch.cuda.current_stream(device).cuda_stream if device.type == "cuda" else 0)
+    key = (device, _cabi.current_stream_handle(device) if device.type == "cuda" else 0)
     buf = _workspaces.get(key)
     if buf is None or buf.numel() < nbytes:
         buf = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
