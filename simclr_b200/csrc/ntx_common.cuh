@@ -82,6 +82,19 @@ NTX_HD int ntx_tri_num_slots(long long T, int G, int key_tiles, int rb) {
     return ntx_tile_owner(T, G, f + (key_tiles - rb) - 1) - ntx_tile_owner(T, G, f) + 1;
 }
 
+// Opt a kernel in to more than 48 KB of dynamic shared memory once per device instead of on every launch
+// (the attribute call costs a few microseconds of host time; a repeated set from two threads is harmless).
+#define NTX_SMEM_OPT_IN(kernel, bytes)                                                                     \
+    do {                                                                                                   \
+        static unsigned done_mask__ = 0;                                                                   \
+        int dev__ = 0;                                                                                     \
+        NTX_CUDA(cudaGetDevice(&dev__));                                                                   \
+        if (!((done_mask__ >> (dev__ & 31)) & 1u)) {                                                       \
+            NTX_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes))); \
+            done_mask__ |= 1u << (dev__ & 31);                                                             \
+        }                                                                                                  \
+    } while (0)
+
 // Programmatic dependent launch: a kernel launched through ntx_launch_dep may start while the previous kernel
 // on the stream is still running; it does its set-up (barriers, TMEM, descriptor prefetch), then ntx_dep_wait()
 // returns once that previous kernel has completed and its writes are visible.  Every kernel launched this way

@@ -146,7 +146,7 @@ template <int NP>
 int launch(const CUtensorMap& m0, const CUtensorMap& m1, const CUtensorMap& mw, int n, int hdim, int d, void* rows,
            int ld, float* inv_norm, cudaStream_t st) {
     const size_t smem = (size_t)ProjStages<NP>::N * (kABytes + NP * 128) + sizeof(ProjCtl);
-    NTX_CUDA(cudaFuncSetAttribute(project_l2norm_kernel<NP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    NTX_SMEM_OPT_IN(project_l2norm_kernel<NP>, smem);
     const int tiles_per_view = (n + 127) / 128;
     NTX_CUDA(ntx_launch_dep(project_l2norm_kernel<NP>, 2 * tiles_per_view, kThreads, smem, st, m0, m1, mw, n, hdim, d,
                             tiles_per_view, (__nv_bfloat16*)rows, ld, inv_norm));

@@ -1074,7 +1074,7 @@ template <int NDB>
 int launch_fwd(const CUtensorMap& mq, const CUtensorMap& mk, const NtxDims& dm, const NtxPlan& plan,
                float* partial, unsigned int* counter, cudaStream_t st) {
     const size_t smem = fwd_smem_bytes<NDB>();
-    NTX_CUDA(cudaFuncSetAttribute(tc_fwd_kernel<NDB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    NTX_SMEM_OPT_IN(tc_fwd_kernel<NDB>, smem);
     const long long T = (long long)plan.row_blocks * plan.key_tiles;
     NTX_CUDA(ntx_launch_dep(tc_fwd_kernel<NDB>, plan.grid, kFwdThreads, smem, st, mq, mk, dm, plan.key_tiles, T,
                             plan.row_blocks * plan.tile_rows, partial, counter));
@@ -1085,7 +1085,7 @@ template <int NDB>
 int launch_bwd(const CUtensorMap& mq, const CUtensorMap& mk, const NtxDims& dm, const NtxPlan& plan,
                const BwdWeights& wt, float* partial, cudaStream_t st) {
     const size_t smem = bwd_smem_bytes<NDB>();
-    NTX_CUDA(cudaFuncSetAttribute(tc_bwd_kernel<NDB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    NTX_SMEM_OPT_IN(tc_bwd_kernel<NDB>, smem);
     const long long T = (long long)plan.row_blocks * plan.key_tiles;
     NTX_CUDA(ntx_launch_dep(tc_bwd_kernel<NDB>, plan.grid, BwdCfg<NDB>::kThreads, smem, st, mq, mk, dm,
                             plan.key_tiles, T, plan.row_blocks * plan.tile_rows, wt, partial));
@@ -1129,12 +1129,12 @@ int ntx_tc_fwd_sym_launch(const __nv_bfloat16* rows, const NtxDims& dm, const Nt
     const int rows_pad = plan.row_blocks * plan.tile_rows;
     if (plan.d_pad == 64) {
         const size_t smem = (size_t)(1 + kSymNS) * 1 * kBlkBytes + kSymWG * 2 * kBlkBytes + 2048 + sizeof(SymCtl);
-        NTX_CUDA(cudaFuncSetAttribute(tc_fwd_sym_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        NTX_SMEM_OPT_IN(tc_fwd_sym_kernel<1>, smem);
         NTX_CUDA(ntx_launch_dep(tc_fwd_sym_kernel<1>, plan.fwd_grid, kSymThreads, smem, st, m, dm, plan.row_blocks, T,
                                 rows_pad, partial, colpart, counter));
     } else if (plan.d_pad == 128) {
         const size_t smem = (size_t)(1 + kSymNS) * 2 * kBlkBytes + kSymWG * 2 * kBlkBytes + 2048 + sizeof(SymCtl);
-        NTX_CUDA(cudaFuncSetAttribute(tc_fwd_sym_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        NTX_SMEM_OPT_IN(tc_fwd_sym_kernel<2>, smem);
         NTX_CUDA(ntx_launch_dep(tc_fwd_sym_kernel<2>, plan.fwd_grid, kSymThreads, smem, st, m, dm, plan.row_blocks, T,
                                 rows_pad, partial, colpart, counter));
     } else {
