@@ -81,6 +81,9 @@ typedef struct NtxPlan {
 
 int ntx_version(void);
 const char* ntx_last_error(void);
+/* Kernels this library has launched (or recorded into a CUDA graph under capture) in this process so far.
+ * bench.py counts the launches of one step with it.  No counterpart in the reference. */
+long long ntx_launch_count(void);
 
 /* Leading dimension (elements per row) the library wants for normalised rows of
  * feature size d in dtype NTX_F32 / NTX_BF16: d rounded up to 4 (fp32) or 64 (bf16). */

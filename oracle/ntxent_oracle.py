@@ -12,12 +12,14 @@ reference itself: ``tests/golden/make_golden.py`` imports
 and commits the input/output vectors under ``tests/golden/``;
 ``tests/test_oracle.py`` checks every function here against those vectors.
 
-Three restatements of the same algorithm live here:
+Restatements of the same algorithm that live here:
 
 * :func:`ntxent_rows_fp64` -- numpy float64, row-chunked closed form (never
   materialises more than ``chunk x 2N`` logits), with the closed-form
   gradient.  It is the checker at sizes where the reference's O(N^2)
   temporaries do not fit.
+* :func:`ntxent_sampled_fp64` -- the same closed form with every row's ``lse`` but the gradient
+  of a chosen subset of rows only (large-size checks: full loss, sampled gradients).
 * :func:`ntxent_reference_form` -- torch, dtype-following, autograd backward;
   it walks the reference's own operator sequence (three N x N similarity
   blocks, diagonal removal, concatenation, softmax cross-entropy,
@@ -130,6 +132,67 @@ def ntxent_rows_fp64(view0, view1, temperature: float, weights=None, chunk: int 
     proj = (zh * dzh).sum(axis=1, keepdims=True)
     dz = np.where((norm > EPS)[:, None], (dzh - zh * proj) / denom[:, None], dzh / EPS)
     out["dview0"], out["dview1"] = dz[:n], dz[n:]
+    return out
+
+
+def ntxent_sampled_fp64(view0, view1, temperature: float, weights, rows, chunk: int = 2048):
+    """All-row ``lse`` / ``pos`` / row loss plus the closed-form gradient of ONLY the rows in ``rows``.
+
+    The checker at sizes where the full gradient pass of :func:`ntxent_rows_fp64` is too slow
+    (BASELINE configs[3] inside ``bench.py``, configs[4] in the GPU tests; SURVEY.md section 8c:
+    "full loss + gradients on a fixed random subset of rows and all-row lse").  Same mathematics,
+    following loss.py:33-65: with ``P_rc = exp(s_rc - lse_r)`` (zero on the self column) and
+    ``p(r)`` the positive of row ``r``,
+
+        d/dzhat_r sum_q w_q loss_q = (1/tau) [ sum_c (w_r P_rc + w_c P_cr) zhat_c - (w_r + w_p(r)) zhat_p(r) ]
+
+    and ``s`` is symmetric, so row ``r`` of ``S`` gives both ``P_rc`` and ``P_cr = exp(s_rc - lse_c)``
+    once every row's ``lse`` is known.  ``rows`` index the concatenation [view0 ; view1].
+    The matrix products run in torch float64 (threaded BLAS); everything else is numpy float64.
+    ``weights`` is one (2, N) array or a list of them (several weightings share the all-row pass).
+    Returns dict: ``loss`` (2, N), ``lse``, ``pos``, ``rows``, ``dz`` (len(rows), D) -- a list of such
+    arrays when a list of weights was given.
+    """
+    import torch
+    v0 = np.asarray(view0, dtype=np.float64)
+    v1 = np.asarray(view1, dtype=np.float64)
+    n = v0.shape[0]
+    m = 2 * n
+    z = np.concatenate([v0, v1], axis=0)
+    zh, denom = l2_normalise(z)
+    inv_t = 1.0 / float(temperature)
+    zt = torch.from_numpy(zh)
+    lse_t = torch.empty(m, dtype=torch.float64)
+    pos_t = torch.empty(m, dtype=torch.float64)
+    for lo in range(0, m, chunk):
+        hi = min(m, lo + chunk)
+        s = (zt[lo:hi] @ zt.T) * inv_t
+        rr = torch.arange(lo, hi)
+        pos_t[lo:hi] = s[rr - lo, (rr + n) % m]
+        s[rr - lo, rr] = -float("inf")                          # self column (mask of loss.py:38,46-47)
+        lse_t[lo:hi] = torch.logsumexp(s, dim=1)
+    lse, pos = lse_t.numpy(), pos_t.numpy()
+    out = {"loss": (lse - pos).reshape(2, n), "lse": lse, "pos": pos}
+    rows = np.asarray(rows, dtype=np.int64)
+    many = isinstance(weights, (list, tuple))
+    ws = [np.asarray(w, dtype=np.float64).reshape(m) for w in (weights if many else [weights])]
+    dzs = [np.empty((len(rows), zh.shape[1])) for _ in ws]
+    for lo in range(0, len(rows), chunk):
+        r = rows[lo:lo + chunk]
+        s = (zt[r] @ zt.T).numpy() * inv_t                      # rows r of S == columns r of S
+        i = np.arange(len(r))
+        p_row, p_col = np.exp(s - lse[r, None]), np.exp(s - lse[None, :])     # P_rc and P_cr
+        p = (r + n) % m
+        zr = zh[r]
+        norm = np.sqrt((z[r] * z[r]).sum(axis=1))
+        for w, dz in zip(ws, dzs):
+            coef = w[r, None] * p_row + w[None, :] * p_col
+            coef[i, r] = 0.0                                    # self column (mask of loss.py:38,46-47)
+            coef[i, p] -= w[r] + w[p]                           # the two one-hot terms of the positive pair
+            dzh = (torch.from_numpy(coef) @ zt).numpy() * inv_t
+            proj = (zr * dzh).sum(axis=1, keepdims=True)
+            dz[lo:lo + len(r)] = np.where((norm > EPS)[:, None], (dzh - zr * proj) / denom[r, None], dzh / EPS)
+    out["rows"], out["dz"] = rows, (dzs if many else dzs[0])
     return out
 
 

@@ -20,7 +20,7 @@ DTYPES = {torch.float32: NTX_F32, torch.bfloat16: NTX_BF16}
 EXPORTS = (
     "ntx_version", "ntx_last_error", "ntx_row_pitch", "ntx_plan", "ntx_l2norm", "ntx_fwd",
     "ntx_bwd", "ntx_debug_indices", "ntx_profile_next", "ntx_fwd_static", "ntx_l2norm_peers",
-    "ntx_scatter_peers", "ntx_project_l2norm", "ntx_bwd_rows",
+    "ntx_scatter_peers", "ntx_project_l2norm", "ntx_bwd_rows", "ntx_launch_count",
 )
 
 
@@ -70,6 +70,7 @@ def _declare(lib):
     for name in EXPORTS:
         if name != "ntx_last_error":
             getattr(lib, name).restype = i
+    lib.ntx_launch_count.restype = ctypes.c_longlong
 
 
 def load():
@@ -113,6 +114,10 @@ class Backend:
     tensors' device and returns immediately."""
 
     name = "libntxent_b200"
+
+    def launch_count(self) -> int:
+        """Kernels the library has launched (or recorded under stream capture) so far in this process."""
+        return int(load().ntx_launch_count())
 
     def row_pitch(self, d: int, dtype: torch.dtype) -> int:
         return load().ntx_row_pitch(d, DTYPES[dtype])

@@ -5,6 +5,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <atomic>
 #include <mutex>
 
 #include "ntx_common.cuh"
@@ -18,6 +19,9 @@ bool ntx_pdl_enabled() {
     }();
     return on;
 }
+
+static std::atomic<long long> g_launches{0};
+void ntx_note_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
 void ntx_set_error(const char* fmt, ...) {
     va_list ap;
@@ -103,6 +107,7 @@ int aligned16(const void* p, const char* what) {
 extern "C" {
 
 int ntx_version(void) { return NTX_VERSION; }
+long long ntx_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 const char* ntx_last_error(void) { return g_err; }
 
 int ntx_row_pitch(int d, int dtype) {
@@ -346,7 +351,6 @@ int ntx_bwd_rows(const void* q, const void* k, int q_rows, int k_rows, int d, in
     NTX_CHECK_ARG(dtype == NTX_F32 || dtype == NTX_BF16, "rows dtype %d not supported", dtype);
     const size_t esz = dtype == NTX_BF16 ? 2 : 4;
     const int n = layout->n_local;
-    NTX_CHECK_ARG((size_t)n * d * esz % 16 == 0, "n_local * d * sizeof(element) must be a multiple of 16");
     // the normalised rows of this rank stand in for the views: rows [0, n) and [n, 2n), pitch ld
     const char* qb = static_cast<const char*>(q);
     char* out = static_cast<char*>(dz);

@@ -104,6 +104,7 @@ NTX_HD int ntx_tri_num_slots(long long T, int G, int key_tiles, int rb) {
 __device__ __forceinline__ void ntx_dep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void ntx_dep_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 bool ntx_pdl_enabled();
+void ntx_note_launch();          // every kernel launch of the library is counted (ntx_launch_count)
 template <typename... KArgs, typename... Args>
 inline cudaError_t ntx_launch_dep(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
                                   Args&&... args) {
@@ -117,6 +118,7 @@ inline cudaError_t ntx_launch_dep(void (*kernel)(KArgs...), dim3 grid, dim3 bloc
     attr[0].val.programmaticStreamSerializationAllowed = ntx_pdl_enabled() ? 1 : 0;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
+    ntx_note_launch();
     return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 #endif

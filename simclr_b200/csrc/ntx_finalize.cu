@@ -296,6 +296,7 @@ int launch_bwd_finalize(const BwdFinArgs& A, const void* view0, const void* view
 #undef NTX_BWD_FIN
     } else {
         const int grid = (A.dm.q_rows + kThreads / 32 - 1) / (kThreads / 32);
+        ntx_note_launch();
         bwd_finalize_kernel<TIn><<<grid, kThreads, 0, st>>>(A, (const TIn*)view0, (const TIn*)view1, (TIn*)dview0,
                                                             (TIn*)dview1);
     }
@@ -307,6 +308,7 @@ int launch_bwd_finalize(const BwdFinArgs& A, const void* view0, const void* view
 
 int ntx_debug_indices_launch(int n_local, int rank, int32_t* self_col, int32_t* pos_col,
                              cudaStream_t st) {
+    ntx_note_launch();
     debug_indices_kernel<<<(2 * n_local + 255) / 256, 256, 0, st>>>(n_local, rank, self_col, pos_col);
     NTX_CUDA(cudaGetLastError());
     return NTX_OK;

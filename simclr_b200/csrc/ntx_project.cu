@@ -35,7 +35,6 @@ project_l2norm_kernel(const __grid_constant__ CUtensorMap tmap_h0, const __grid_
     constexpr uint32_t kStageBytes = kABytes + kBBytes;
     constexpr int kStages = ProjStages<NP>::N;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
-    ntx_dep_trigger();
     uint8_t* smem = smem_raw;
     if (smem_u32(smem) & 1023u) __trap();
     ProjCtl* ctl = reinterpret_cast<ProjCtl*>(smem + kStages * kStageBytes);
@@ -58,6 +57,8 @@ project_l2norm_kernel(const __grid_constant__ CUtensorMap tmap_h0, const __grid_
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = ctl->tmem_base;
+    // our TMEM is allocated: only now may the next kernel on the stream be staged (its CTAs allocate TMEM too)
+    ntx_dep_trigger();
     ntx_dep_wait();
 
     if (warp == 4) {

@@ -230,6 +230,7 @@ int ntx_simt_fwd_launch(const float* q, const float* k, const NtxDims& dm, const
                         float* partial, unsigned int* counter, cudaStream_t st) {
     const long long T = (long long)plan.row_blocks * plan.key_tiles;
     const int rows_pad = plan.row_blocks * plan.tile_rows;
+    ntx_note_launch();
     simt_fwd_kernel<<<plan.grid, NT, 0, st>>>(q, k, dm, plan.key_tiles, T, rows_pad, partial, counter);
     NTX_CUDA(cudaGetLastError());
     return NTX_OK;
@@ -240,6 +241,7 @@ int ntx_simt_bwd_launch(const float* q, const float* k, const NtxDims& dm, const
     const long long T = (long long)plan.row_blocks * plan.key_tiles;
     const int rows_pad = plan.row_blocks * plan.tile_rows;
     dim3 grid(plan.grid, (plan.d_pad + BD - 1) / BD);
+    ntx_note_launch();
     simt_bwd_kernel<<<grid, NT, 0, st>>>(q, k, dm, plan.key_tiles, T, rows_pad, plan.d_pad, wt, partial);
     NTX_CUDA(cudaGetLastError());
     return NTX_OK;

@@ -212,7 +212,6 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     constexpr int NS = FwdCfg<NDB>::NS;
     constexpr uint32_t kTileBytes = NDB * kBlkBytes;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
-    ntx_dep_trigger();
     uint8_t* smem = checked_1024(smem_raw);
     uint8_t* q_smem = smem;
     uint8_t* k_smem = smem + kTileBytes;
@@ -236,6 +235,8 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    // our TMEM is allocated: only now may the next kernel on the stream be staged (its CTAs allocate TMEM too)
+    ntx_dep_trigger();
     // the whole TMEM (512 columns) is ours, so the allocation starts at column 0, lane 0;
     // using the literal keeps every TMEM address a compile-time constant
     if (ctl->tmem_base != 0) {
@@ -432,7 +433,6 @@ tc_fwd_sym_kernel(const __grid_constant__ CUtensorMap tmap, NtxDims dm, int key_
     constexpr uint32_t kTileBytes = NDB * kBlkBytes;
     constexpr uint32_t kEBytes = 2 * kBlkBytes;             // [128 rows x 128 keys] bf16
     extern __shared__ __align__(1024) uint8_t smem_raw[];
-    ntx_dep_trigger();
     uint8_t* smem = checked_1024(smem_raw);
     uint8_t* q_smem = smem;
     uint8_t* k_smem = smem + kTileBytes;
@@ -467,6 +467,8 @@ tc_fwd_sym_kernel(const __grid_constant__ CUtensorMap tmap, NtxDims dm, int key_
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    // our TMEM is allocated: only now may the next kernel on the stream be staged (its CTAs allocate TMEM too)
+    ntx_dep_trigger();
     if (ctl->tmem_base != 0) {
         if (threadIdx.x == 0) printf("ntxent: unexpected TMEM base %u\n", ctl->tmem_base);
         __trap();
@@ -792,7 +794,6 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     constexpr uint32_t kSCol = Cfg::kSCol;
     constexpr uint32_t kTileBytes = NDB * kBlkBytes;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
-    ntx_dep_trigger();
     uint8_t* smem = checked_1024(smem_raw);
     uint8_t* q_smem = smem;
     uint8_t* k_smem = smem + kTileBytes;
@@ -822,6 +823,8 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    // our TMEM is allocated: only now may the next kernel on the stream be staged (its CTAs allocate TMEM too)
+    ntx_dep_trigger();
     // the whole TMEM (512 columns) is ours, so the allocation starts at column 0, lane 0;
     // using the literal keeps every TMEM address a compile-time constant
     if (ctl->tmem_base != 0) {

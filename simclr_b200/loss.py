@@ -14,6 +14,7 @@ reference computes the loss on each rank's local batch only (SURVEY.md section 0
 """
 from __future__ import annotations
 
+import contextlib
 import os
 
 import torch
@@ -45,6 +46,17 @@ def _workspace(device: torch.device, nbytes: int) -> torch.Tensor:
         buf = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
         _workspaces[key] = buf
     return buf
+
+
+def _require_cuda(t: torch.Tensor) -> None:
+    if t.device.type != "cuda":
+        raise RuntimeError(f"NT_Xent (B200) has no CPU path: inputs must be CUDA tensors (got {t.device})")
+
+
+def _device_of(t: torch.Tensor):
+    """Context that makes the tensor's GPU current: the library plans, opts kernels in and launches on the
+    current device, while the stream is taken from the tensor's device."""
+    return torch.cuda.device(t.device) if t.device.type == "cuda" else contextlib.nullcontext()
 
 
 def _env_flag(name: str) -> bool:
@@ -251,9 +263,7 @@ class NT_Xent(torch.nn.Module):
             raise RuntimeError("view0 and view1 must share dtype and device")
         if view0.dtype not in (torch.float32, torch.bfloat16):
             raise TypeError(f"NT_Xent (B200) supports float32 and bfloat16 inputs, got {view0.dtype}")
-        if view0.device.type != "cuda" and not getattr(_backend, "allows_cpu", False):
-            raise RuntimeError("NT_Xent (B200) has no CPU path: inputs must be CUDA tensors "
-                               f"(got {view0.device})")
+        _require_cuda(view0)
         if view0.shape[0] < 1 or view0.shape[1] < 1:
             raise RuntimeError("empty batch or feature dimension")
 
@@ -262,9 +272,10 @@ class NT_Xent(torch.nn.Module):
             group = self.process_group
             world, rank = dist.get_world_size(group), dist.get_rank(group)
         rows_dtype = self.compute_dtype or view0.dtype
-        return NTXentFunction.apply(view0.contiguous(), view1.contiguous(), float(self.temperature),
-                                    self.reduction, rows_dtype, group, world, rank,
-                                    world > 1 and self.gather_backend == "peer")
+        with _device_of(view0):
+            return NTXentFunction.apply(view0.contiguous(), view1.contiguous(), float(self.temperature),
+                                        self.reduction, rows_dtype, group, world, rank,
+                                        world > 1 and self.gather_backend == "peer")
 
     def forward_hidden(self, h0: torch.Tensor, h1: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
         """
@@ -282,10 +293,10 @@ class NT_Xent(torch.nn.Module):
                                f"{tuple(h1.shape)}, {tuple(weight.shape)}")
         if not (h0.dtype == h1.dtype == weight.dtype == torch.bfloat16):
             raise TypeError("forward_hidden runs on the bf16 tensor-core path: h0, h1 and weight must be bfloat16")
-        if h0.device.type != "cuda":
-            raise RuntimeError("NT_Xent (B200) has no CPU path: inputs must be CUDA tensors")
-        return NTXentHiddenFunction.apply(h0.contiguous(), h1.contiguous(), weight.contiguous(),
-                                          float(self.temperature), self.reduction)
+        _require_cuda(h0)
+        with _device_of(h0):
+            return NTXentHiddenFunction.apply(h0.contiguous(), h1.contiguous(), weight.contiguous(),
+                                              float(self.temperature), self.reduction)
 
     def extra_repr(self) -> str:
         return (f"temperature={self.temperature}, reduction={self.reduction!r}, gather={self.gather}, "

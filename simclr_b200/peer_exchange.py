@@ -98,3 +98,9 @@ def exchange_for(group, q_rows: int, ld: int, rows_dtype: torch.dtype, device: t
     if ex is None:
         ex = _exchanges[key] = PeerExchange(group, q_rows, ld, rows_dtype, device)
     return ex
+
+
+def close_all() -> None:
+    """Drop every PeerExchange (symmetric buffers and their rendezvous handles).  Call it on all ranks, after the
+    CUDA graphs that captured the buffers have been destroyed and before ``destroy_process_group``."""
+    _exchanges.clear()

@@ -12,7 +12,6 @@ import torch
 
 class StandInBackend:
     name = "standin"
-    allows_cpu = True
 
     def row_pitch(self, d, dtype):
         g = 64 if dtype == torch.bfloat16 else 4

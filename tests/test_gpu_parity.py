@@ -232,6 +232,105 @@ def test_full_size_config4_properties(dev):
     assert torch.equal(loss, loss2) and torch.equal(ta.grad, ta2.grad) and torch.equal(tb.grad, tb2.grad)
 
 
+def _nonuniform_weights(n):
+    """Deterministic per-row upstream gradient of reduction='none', bf16-exact (the module's output is bf16)."""
+    i = torch.arange(2 * n, dtype=torch.float64).reshape(2, n)
+    return ((1.0 + 0.5 * torch.sin(0.37 * i)) / (2.0 * n)).to(torch.bfloat16)
+
+
+def test_config5_size_against_sampled_oracle(dev):
+    """BASELINE configs[4] at full size on one GPU (N = 32768 pairs, D = 256, bf16 rows): every row's row sum,
+    positive logit and loss, and the gradient of 4096 sampled rows under non-uniform row weights, against the
+    fp64 oracle (the reference's own temporaries do not fit at this size)."""
+    from simclr_b200 import NT_Xent, _cabi
+    n, d, tau = 32768, 256, 0.5
+    g = torch.Generator().manual_seed(7)
+    a = torch.randn(n, d, generator=g).bfloat16()
+    b = torch.randn(n, d, generator=g).bfloat16()
+    w = _nonuniform_weights(n)
+    rng = np.random.default_rng(11)
+    pairs = np.sort(rng.choice(n, size=2048, replace=False))
+    rows = np.concatenate([pairs, n + pairs])                                 # 4096 rows of [view0 ; view1]
+    ref = orc.ntxent_sampled_fp64(a.float().numpy(), b.float().numpy(), tau, w.double().numpy(), rows)
+
+    ta, tb = a.to(dev).requires_grad_(True), b.to(dev).requires_grad_(True)
+    out = NT_Xent(tau, "none")(ta, tb)
+    out.backward(w.to(dev))
+    assert rel_err(out.detach().float().cpu().numpy(), ref["loss"]) < BF16_TOL
+    want = ref["dz"]
+    scale = np.abs(want).max()
+    got = np.concatenate([ta.grad[pairs].float().cpu().numpy(), tb.grad[pairs].float().cpu().numpy()])
+    assert np.abs(got - want).max() / scale < BF16_TOL
+
+    # all-row lse and positive logit through the C ABI
+    be = _cabi.Backend()
+    ld = be.row_pitch(d, torch.bfloat16)
+    rws = torch.empty(2 * n, ld, dtype=torch.bfloat16, device=dev)
+    st = torch.empty(4, 2 * n, device=dev)
+    ls = torch.empty(2, device=dev)
+    be.l2norm(ta.detach(), tb.detach(), rws, st[0])
+    plan = be.plan(2 * n, 2 * n, d, torch.bfloat16)
+    ws = torch.empty(max(plan.fwd_ws_bytes, 16), dtype=torch.uint8, device=dev)
+    be.fwd(rws, rws, d, (n, 1, 0), tau, st[1], st[2], st[3], ls, ws)
+    lse = (torch.log(st[1].double()) + 1.0 / tau).cpu().numpy()
+    assert np.abs(lse - ref["lse"]).max() < BF16_TOL * np.abs(ref["lse"]).max()
+    assert np.abs(st[2].double().cpu().numpy() - ref["pos"]).max() < BF16_TOL * max(np.abs(ref["pos"]).max(), 1.0)
+    assert abs(float(ls[1]) - ref["loss"].mean()) < BF16_TOL * ref["loss"].mean()
+
+
+def test_rank7_of_8_at_config4_shard_size(dev):
+    """The 8-rank split of BASELINE configs[3] (N = 8192, D = 128, bf16) emulated on one GPU at the real shard
+    size: rank 7's 2048 query rows against all 16384 rank-major keys.  Every rank's forward supplies the row sums
+    the backward needs; rank 7's losses and ALL its gradient rows are checked against the oracle on the
+    concatenated batch, under non-uniform row weights."""
+    from simclr_b200 import _cabi
+    be = _cabi.Backend()
+    n, d, tau, world, rank = 8192, 128, 0.5, 8, 7
+    nl = n // world
+    q_rows = 2 * nl
+    g = torch.Generator().manual_seed(7)
+    a = torch.randn(n, d, generator=g).bfloat16()
+    b = torch.randn(n, d, generator=g).bfloat16()
+    w = _nonuniform_weights(n)                                                 # (2, n) on the GLOBAL batch
+    gl = rank * nl + np.arange(nl)
+    rows = np.concatenate([gl, n + gl])
+    ref = orc.ntxent_sampled_fp64(a.float().numpy(), b.float().numpy(), tau, w.double().numpy(), rows)
+
+    ld = be.row_pitch(d, torch.bfloat16)
+    keys = torch.empty(world * q_rows, ld, dtype=torch.bfloat16, device=dev)
+    inv = torch.empty(world, q_rows, device=dev)
+    views = []
+    for k in range(world):
+        sl = slice(k * nl, (k + 1) * nl)
+        va, vb = a[sl].to(dev), b[sl].to(dev)
+        views.append((va, vb))
+        be.l2norm(va, vb, keys[k * q_rows:(k + 1) * q_rows], inv[k])
+    plan = be.plan(q_rows, keys.shape[0], d, torch.bfloat16)
+    ws = torch.empty(max(plan.fwd_ws_bytes, plan.bwd_ws_bytes), dtype=torch.uint8, device=dev)
+    st = torch.empty(world, 3, q_rows, device=dev)
+    ls = torch.empty(world, 2, device=dev)
+    for k in range(world):
+        be.fwd(keys[k * q_rows:(k + 1) * q_rows], keys, d, (nl, world, k), tau, st[k, 0], st[k, 1], st[k, 2], ls[k], ws)
+    # rank-major vectors, as the gather builds them: chunk k = [view0 rows of rank k ; view1 rows of rank k]
+    rowsum_k = st[:, 0, :].reshape(-1).contiguous()
+    w_k = torch.stack([torch.cat([w[0, k * nl:(k + 1) * nl], w[1, k * nl:(k + 1) * nl]]) for k in range(world)])
+    w_k = w_k.float().to(dev).reshape(-1).contiguous()
+    lse_all = ref["lse"].reshape(2, n)
+    want_rowsum = np.concatenate([np.exp(np.concatenate([lse_all[0, k * nl:(k + 1) * nl], lse_all[1, k * nl:(k + 1) * nl]])
+                                         - 1.0 / tau) for k in range(world)])
+    assert rel_err(rowsum_k.cpu().numpy(), want_rowsum) < BF16_TOL
+    got_loss = st[rank, 2].cpu().numpy().reshape(2, nl)
+    assert rel_err(got_loss, ref["loss"][:, rank * nl:(rank + 1) * nl]) < BF16_TOL
+
+    va, vb = views[rank]
+    d0, d1 = torch.empty_like(va), torch.empty_like(vb)
+    w_q = w_k[rank * q_rows:(rank + 1) * q_rows]
+    be.bwd(keys[rank * q_rows:(rank + 1) * q_rows], keys, d, (nl, world, rank), tau, st[rank, 0], rowsum_k, w_q, w_k,
+           1, 1.0, va, vb, inv[rank], d0, d1, ws)
+    got = np.concatenate([d0.float().cpu().numpy(), d1.float().cpu().numpy()])
+    assert np.abs(got - ref["dz"]).max() / np.abs(ref["dz"]).max() < BF16_TOL
+
+
 def test_training_step_call_pattern(dev):
     """main.py:104-122 call pattern: model(view0), model(view1), loss, backward, SGD step.  Every step
     the reference-form oracle runs on the same projections z0, z1 as the checker: the loss value and

@@ -104,3 +104,20 @@ def test_closed_form_gradient_matches_autograd_fp64():
     assert _rel(out["loss"], loss.detach().numpy()) < 1e-12
     assert _rel(out["dview0"], ta.grad.numpy()) < 1e-11
     assert _rel(out["dview1"], tb.grad.numpy()) < 1e-11
+
+
+def test_sampled_gradient_equals_full_closed_form():
+    # the large-size checker (all-row lse, gradients of a subset of rows) against the full fp64 closed form,
+    # with a clamped (all-zero) row and non-uniform row weights
+    rng = np.random.default_rng(1)
+    n, d = 300, 40
+    a, b = rng.standard_normal((n, d)), rng.standard_normal((n, d))
+    a[3] = 0.0
+    w = rng.uniform(0.5, 1.5, (2, n))
+    full = orc.ntxent_rows_fp64(a, b, 0.3, weights=w)
+    rows = np.array([0, 3, 5, 299, 300, 303, 599, 17])
+    part = orc.ntxent_sampled_fp64(a, b, 0.3, w, rows, chunk=128)
+    want = np.concatenate([full["dview0"], full["dview1"]])[rows]
+    assert np.abs(part["loss"] - full["loss"]).max() < 1e-12
+    assert _rel(part["dz"][rows != 3], want[rows != 3]) < 1e-12
+    assert _rel(part["dz"][rows == 3], want[rows == 3]) < 1e-12        # the eps-clamped row (huge gradient)
