@@ -109,21 +109,49 @@ int ntx_l2norm(const void* view0, const void* view1, int n, int d, int in_dtype,
 int ntx_project_l2norm(const void* h0, const void* h1, const void* weight, int n, int hdim, int d, void* rows,
                        int ld, float* inv_norm, void* stream);
 
-/* Multi-rank gather without a collective library call (one node, NVLink / NVSwitch peer memory).
- * ntx_l2norm_peers is ntx_l2norm whose output goes straight into every rank's key buffer: peer_keys[p] is the
- * address, mapped into this process, of rank p's [world*2n x ld] key buffer (peer_keys[rank] is this rank's own);
- * the 2n normalised rows land in rows [rank*2n, (rank+1)*2n) of each.  Replaces F.normalize (loss.py:33-34)
- * followed by the cross-rank embedding gather of BASELINE.json's north_star (the reference itself has no gather:
- * distributed_utils.py:8-24 is only init_ddp / cleanup).  world <= 8.
- * ntx_scatter_peers copies `bytes` bytes from src to peer_dst[p] + dst_offset for every p (the row sums and row
- * weights the backward needs from every rank).  Both only enqueue stores; the caller orders them against the
- * readers with a cross-rank barrier on the stream (simclr_b200/peer_exchange.py uses torch's symmetric-memory
- * barrier) and owns the peer mappings. */
+/* Multi-rank exchange without a collective library call (one node, NVLink / NVSwitch peer memory).
+ * Every rank owns one EXCHANGE BLOCK of ntx_peer_block_bytes() bytes that is mapped into every process
+ * (e.g. torch.distributed._symmetric_memory): control words, the row sums and row weights of every key, and two
+ * key buffers [world * 2n x ld] used by alternate steps.  NtxPeerBlocks.base[p] is rank p's block as THIS
+ * process sees it (base[rank] = its own).  Blocks must start zeroed (on every rank, before the first call of any
+ * rank), be 1024-byte aligned, and every rank must make the same sequence of calls.
+ * The kernels themselves move the data and order it: a producer stores into every rank's block, fences at system
+ * scope and writes the step number into a flag word of every block; a consumer polls the flag words of its own
+ * block before it first touches the data of a rank.  No barrier kernel, no host synchronisation.
+ *   ntx_peer_l2norm : ntx_l2norm whose rows land in rows [rank*2n, (rank+1)*2n) of the step's key buffer of every
+ *                     block.  Replaces F.normalize (loss.py:33-34) followed by the cross-rank embedding gather of
+ *                     BASELINE.json's north_star (the reference itself has no gather: distributed_utils.py:8-24
+ *                     is only init_ddp / cleanup).  Counts this rank's steps (a word in its block; the count picks
+ *                     the key buffer, so replaying a captured CUDA graph alternates buffers) and writes the
+ *                     step number to *step (device memory), which the later calls of the same step take.
+ *   ntx_peer_fwd    : ntx_fwd of this rank's rows against all keys of the step (loss.py:36-61 on the gathered
+ *                     batch); its finalize also stores the row sums into every block.
+ *   ntx_peer_post_weights : stores this rank's row weights (w: the upstream gradient, one value or one per row
+ *                     as in ntx_bwd, unscaled) into every block: the first call of a backward.
+ *   ntx_peer_bwd    : ntx_bwd that reads every key's row sum and weight from this rank's own block (w_stride as
+ *                     posted, on every rank alike; w_scale as in ntx_bwd); call it after ntx_peer_post_weights
+ *                     of the same step.
+ * A rank may run ahead of another by less than one step: its forward waits for every rank's rows of the same
+ * step, which a rank sends only after its previous backward.  At most two forwards may be outstanding without
+ * their backward (two key buffers). */
 #define NTX_MAX_PEERS 8
-int ntx_l2norm_peers(const void* view0, const void* view1, int n, int d, int in_dtype, void* const* peer_keys,
-                     int world, int rank, int ld, int rows_dtype, float* inv_norm, void* stream);
-int ntx_scatter_peers(const void* src, size_t bytes, void* const* peer_dst, int world, size_t dst_offset,
-                      void* stream);
+typedef struct NtxPeerBlocks {
+    void* base[NTX_MAX_PEERS];
+    int32_t world;
+    int32_t rank;
+} NtxPeerBlocks;
+size_t ntx_peer_block_bytes(int q_rows, int ld, int rows_dtype, int world);
+int ntx_peer_l2norm(const void* view0, const void* view1, int n, int d, int in_dtype, const NtxPeerBlocks* blocks,
+                    int ld, int rows_dtype, float* inv_norm, uint32_t* step, void* stream);
+int ntx_peer_fwd(const NtxPeerBlocks* blocks, int n_local, int d, int ld, int dtype, float temperature,
+                 const uint32_t* step, float* rowsum, float* pos_logit, float* row_loss, float* loss_sum,
+                 void* workspace, size_t workspace_bytes, void* stream);
+int ntx_peer_post_weights(const NtxPeerBlocks* blocks, int n_local, int ld, int dtype, const uint32_t* step,
+                          const void* w, int w_stride, int w_dtype, void* stream);
+int ntx_peer_bwd(const NtxPeerBlocks* blocks, int n_local, int d, int ld, int dtype, float temperature,
+                 const uint32_t* step, const float* rowsum_q, int w_stride, float w_scale, const void* view0,
+                 const void* view1, int in_dtype, const float* inv_norm, void* dview0, void* dview1, void* workspace,
+                 size_t workspace_bytes, void* stream);
 
 /* Forward.  For each of this rank's q_rows = 2*n_local rows:
  *   rowsum[r]   = sum over keys c != self of exp(s_rc - 1/tau),  s = <row r, key c> / tau
@@ -151,6 +179,7 @@ int ntx_fwd(const void* q_rows_ptr, const void* k_rows_ptr, int q_rows, int k_ro
  *     reduction mean / sum: w_stride = 0, w_q = w_k = the upstream gradient (one device float),
  *                           w_scale = 1 / q_rows (mean, loss.py:65) or 1 (sum);
  *     reduction none      : w_stride = 1, w_q = upstream gradient laid out (2, n_local), w_scale = 1.
+ *   w_dtype: NTX_F32 or NTX_BF16 -- the upstream gradient is read in the dtype the loss was returned in.
  *   rowsum_q / rowsum_k: the forward's rowsum of this rank's rows / of every key (with world > 1 the
  *   caller all-gathers rowsum and, for w_stride = 1, the weights).
  * Replaces the autograd graph of loss.py:33-65 (softmax - onehot, un-concatenate, index_put through
@@ -158,7 +187,7 @@ int ntx_fwd(const void* q_rows_ptr, const void* k_rows_ptr, int q_rows, int k_ro
  * dview0/dview1 are (n_local x d) in `in_dtype`, like view0/view1. */
 int ntx_bwd(const void* q_rows_ptr, const void* k_rows_ptr, int q_rows, int k_rows, int d, int ld,
             int dtype, const NtxLayout* layout, float temperature, const float* rowsum_q,
-            const float* rowsum_k, const float* w_q, const float* w_k, int w_stride, float w_scale,
+            const float* rowsum_k, const void* w_q, const void* w_k, int w_stride, int w_dtype, float w_scale,
             const void* view0, const void* view1, int in_dtype, const float* inv_norm, void* dview0,
             void* dview1, void* workspace, size_t workspace_bytes, void* stream);
 
@@ -169,8 +198,8 @@ int ntx_bwd(const void* q_rows_ptr, const void* k_rows_ptr, int q_rows, int k_ro
  * The caller finishes the layer with two library GEMMs: dh = dz . W, dW = dz^T . [h0 ; h1]. */
 int ntx_bwd_rows(const void* q_rows_ptr, const void* k_rows_ptr, int q_rows, int k_rows, int d, int ld, int dtype,
                  const NtxLayout* layout, float temperature, const float* rowsum_q, const float* rowsum_k,
-                 const float* w_q, const float* w_k, int w_stride, float w_scale, const float* inv_norm, void* dz,
-                 void* workspace, size_t workspace_bytes, void* stream);
+                 const void* w_q, const void* w_k, int w_stride, int w_dtype, float w_scale, const float* inv_norm,
+                 void* dz, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ntx_fwd without a caller-supplied scratch buffer.  This entry point has no counterpart in the
  * reference.  It is for hosts that hold nothing but their input and output buffers and cannot

@@ -19,13 +19,19 @@ DTYPES = {torch.float32: NTX_F32, torch.bfloat16: NTX_BF16}
 
 EXPORTS = (
     "ntx_version", "ntx_last_error", "ntx_row_pitch", "ntx_plan", "ntx_l2norm", "ntx_fwd",
-    "ntx_bwd", "ntx_debug_indices", "ntx_profile_next", "ntx_fwd_static", "ntx_l2norm_peers",
-    "ntx_scatter_peers", "ntx_project_l2norm", "ntx_bwd_rows", "ntx_launch_count",
+    "ntx_bwd", "ntx_debug_indices", "ntx_profile_next", "ntx_fwd_static", "ntx_peer_block_bytes",
+    "ntx_peer_l2norm", "ntx_peer_fwd", "ntx_peer_post_weights", "ntx_peer_bwd", "ntx_project_l2norm", "ntx_bwd_rows", "ntx_launch_count",
 )
+
+MAX_PEERS = 8
 
 
 class NtxLayout(ctypes.Structure):
     _fields_ = [("n_local", ctypes.c_int32), ("world", ctypes.c_int32), ("rank", ctypes.c_int32)]
+
+
+class NtxPeerBlocks(ctypes.Structure):
+    _fields_ = [("base", ctypes.c_void_p * MAX_PEERS), ("world", ctypes.c_int32), ("rank", ctypes.c_int32)]
 
 
 class NtxPlan(ctypes.Structure):
@@ -57,13 +63,17 @@ def _declare(lib):
     lib.ntx_plan.argtypes = [i, i, i, i, i, ctypes.POINTER(NtxPlan)]
     lib.ntx_l2norm.argtypes = [vp, vp, i, i, i, vp, i, i, vp, vp]
     lib.ntx_fwd.argtypes = [vp, vp, i, i, i, i, i, ctypes.POINTER(NtxLayout), f, vp, vp, vp, vp, vp, sz, vp]
-    lib.ntx_bwd.argtypes = [vp, vp, i, i, i, i, i, ctypes.POINTER(NtxLayout), f, vp, vp, vp, vp, i, f,
+    lib.ntx_bwd.argtypes = [vp, vp, i, i, i, i, i, ctypes.POINTER(NtxLayout), f, vp, vp, vp, vp, i, i, f,
                             vp, vp, i, vp, vp, vp, vp, sz, vp]
     lib.ntx_fwd_static.argtypes = [vp, vp, i, i, i, i, i, ctypes.POINTER(NtxLayout), f, vp, vp, vp, vp, vp]
-    lib.ntx_l2norm_peers.argtypes = [vp, vp, i, i, i, ctypes.POINTER(vp), i, i, i, i, vp, vp]
-    lib.ntx_scatter_peers.argtypes = [vp, sz, ctypes.POINTER(vp), i, sz, vp]
+    pb = ctypes.POINTER(NtxPeerBlocks)
+    lib.ntx_peer_block_bytes.argtypes = [i, i, i, i]
+    lib.ntx_peer_l2norm.argtypes = [vp, vp, i, i, i, pb, i, i, vp, vp, vp]
+    lib.ntx_peer_fwd.argtypes = [pb, i, i, i, i, f, vp, vp, vp, vp, vp, vp, sz, vp]
+    lib.ntx_peer_post_weights.argtypes = [pb, i, i, i, vp, vp, i, i, vp]
+    lib.ntx_peer_bwd.argtypes = [pb, i, i, i, i, f, vp, vp, i, f, vp, vp, i, vp, vp, vp, vp, sz, vp]
     lib.ntx_project_l2norm.argtypes = [vp, vp, vp, i, i, i, vp, i, vp, vp]
-    lib.ntx_bwd_rows.argtypes = [vp, vp, i, i, i, i, i, ctypes.POINTER(NtxLayout), f, vp, vp, vp, vp, i, f, vp, vp,
+    lib.ntx_bwd_rows.argtypes = [vp, vp, i, i, i, i, i, ctypes.POINTER(NtxLayout), f, vp, vp, vp, vp, i, i, f, vp, vp,
                                  vp, sz, vp]
     lib.ntx_debug_indices.argtypes = [ctypes.POINTER(NtxLayout), vp, vp, vp]
     lib.ntx_profile_next.argtypes = [i, vp, vp]
@@ -71,6 +81,7 @@ def _declare(lib):
         if name != "ntx_last_error":
             getattr(lib, name).restype = i
     lib.ntx_launch_count.restype = ctypes.c_longlong
+    lib.ntx_peer_block_bytes.restype = ctypes.c_size_t
 
 
 def load():
@@ -139,20 +150,47 @@ class Backend:
         _check(load().ntx_project_l2norm(h0.data_ptr(), h1.data_ptr(), weight.data_ptr(), n, hdim, weight.shape[0],
                                          rows.data_ptr(), rows.shape[1], inv_norm.data_ptr(), _stream(rows)))
 
-    def l2norm_peers(self, view0, view1, peer_ptrs, rank, ld, rows_dtype, inv_norm):
-        """ntx_l2norm_peers: normalised rows written into rows [rank*2n, (rank+1)*2n) of every rank's
-        key buffer; ``peer_ptrs`` are the buffers' addresses in this process (peer memory)."""
-        n, d = view0.shape
-        table = (ctypes.c_void_p * len(peer_ptrs))(*peer_ptrs)
-        _check(load().ntx_l2norm_peers(view0.data_ptr(), view1.data_ptr(), n, d, DTYPES[view0.dtype], table,
-                                       len(peer_ptrs), rank, ld, DTYPES[rows_dtype], inv_norm.data_ptr(),
-                                       _stream(view0)))
+    # ---- peer exchange (include/ntxent_b200.h, "Multi-rank exchange"): `blocks` is an NtxPeerBlocks
+    def peer_block_bytes(self, q_rows: int, ld: int, rows_dtype: torch.dtype, world: int) -> int:
+        return int(load().ntx_peer_block_bytes(q_rows, ld, DTYPES[rows_dtype], world))
 
-    def scatter_peers(self, src, peer_ptrs, dst_offset_bytes):
-        """ntx_scatter_peers: the bytes of ``src`` to the same offset of every rank's buffer."""
-        table = (ctypes.c_void_p * len(peer_ptrs))(*peer_ptrs)
-        _check(load().ntx_scatter_peers(src.data_ptr(), src.numel() * src.element_size(), table,
-                                        len(peer_ptrs), dst_offset_bytes, _stream(src)))
+    @staticmethod
+    def peer_blocks(ptrs, rank: int) -> NtxPeerBlocks:
+        pb = NtxPeerBlocks()
+        if not 1 <= len(ptrs) <= MAX_PEERS:
+            raise ValueError(f"peer exchange: world {len(ptrs)} outside [1, {MAX_PEERS}] (one node)")
+        for p, addr in enumerate(ptrs):
+            pb.base[p] = addr
+        pb.world, pb.rank = len(ptrs), rank
+        return pb
+
+    def peer_l2norm(self, view0, view1, blocks, ld, rows_dtype, inv_norm, step):
+        """ntx_peer_l2norm: normalised rows into the step's key buffer of every rank's block; ``step`` (one int32
+        on the device) receives the step number the later calls of this step take."""
+        n, d = view0.shape
+        _check(load().ntx_peer_l2norm(view0.data_ptr(), view1.data_ptr(), n, d, DTYPES[view0.dtype],
+                                      ctypes.byref(blocks), ld, DTYPES[rows_dtype], inv_norm.data_ptr(),
+                                      step.data_ptr(), _stream(view0)))
+
+    def peer_fwd(self, blocks, n_local, d, ld, rows_dtype, temperature, step, rowsum, pos_logit, row_loss, loss_sum,
+                 workspace):
+        _check(load().ntx_peer_fwd(ctypes.byref(blocks), n_local, d, ld, DTYPES[rows_dtype], float(temperature),
+                                   step.data_ptr(), rowsum.data_ptr(), pos_logit.data_ptr(), row_loss.data_ptr(),
+                                   loss_sum.data_ptr(), workspace.data_ptr(),
+                                   workspace.numel() * workspace.element_size(), _stream(rowsum)))
+
+    def peer_post_weights(self, blocks, n_local, ld, rows_dtype, step, w, w_stride):
+        """ntx_peer_post_weights: this rank's row weights (upstream gradient) into every rank's block."""
+        _check(load().ntx_peer_post_weights(ctypes.byref(blocks), n_local, ld, DTYPES[rows_dtype], step.data_ptr(),
+                                            w.data_ptr(), int(w_stride), DTYPES[w.dtype], _stream(w)))
+
+    def peer_bwd(self, blocks, n_local, d, ld, rows_dtype, temperature, step, rowsum_q, w_stride, w_scale, view0,
+                 view1, inv_norm, dview0, dview1, workspace):
+        _check(load().ntx_peer_bwd(ctypes.byref(blocks), n_local, d, ld, DTYPES[rows_dtype], float(temperature),
+                                   step.data_ptr(), rowsum_q.data_ptr(), int(w_stride), float(w_scale),
+                                   view0.data_ptr(), view1.data_ptr(), DTYPES[view0.dtype], inv_norm.data_ptr(),
+                                   dview0.data_ptr(), dview1.data_ptr(), workspace.data_ptr(),
+                                   workspace.numel() * workspace.element_size(), _stream(view0)))
 
     def fwd(self, q, k, d, layout, temperature, rowsum, pos_logit, row_loss, loss_sum, workspace):
         lay = NtxLayout(*layout)
@@ -172,13 +210,20 @@ class Backend:
                                      rowsum.data_ptr(), pos_logit.data_ptr(), row_loss.data_ptr(),
                                      loss_sum.data_ptr(), _stream(q)))
 
+    @staticmethod
+    def _weight_dtype(w_q, w_k) -> int:
+        if w_q.dtype != w_k.dtype:
+            raise TypeError(f"row weights of the rows and of the keys differ in dtype: {w_q.dtype} vs {w_k.dtype}")
+        return DTYPES[w_q.dtype]
+
     def bwd(self, q, k, d, layout, temperature, rowsum_q, rowsum_k, w_q, w_k, w_stride, w_scale, view0,
             view1, inv_norm, dview0, dview1, workspace):
         lay = NtxLayout(*layout)
         _check(load().ntx_bwd(q.data_ptr(), k.data_ptr(), q.shape[0], k.shape[0], d, q.shape[1],
                               DTYPES[q.dtype], ctypes.byref(lay), float(temperature), rowsum_q.data_ptr(),
                               rowsum_k.data_ptr(), w_q.data_ptr(), w_k.data_ptr(), int(w_stride),
-                              float(w_scale), view0.data_ptr(), view1.data_ptr(), DTYPES[view0.dtype],
+                              self._weight_dtype(w_q, w_k), float(w_scale), view0.data_ptr(), view1.data_ptr(),
+                              DTYPES[view0.dtype],
                               inv_norm.data_ptr(), dview0.data_ptr(), dview1.data_ptr(),
                               workspace.data_ptr(), workspace.numel() * workspace.element_size(),
                               _stream(q)))
@@ -190,7 +235,8 @@ class Backend:
         _check(load().ntx_bwd_rows(q.data_ptr(), k.data_ptr(), q.shape[0], k.shape[0], d, q.shape[1],
                                    DTYPES[q.dtype], ctypes.byref(lay), float(temperature), rowsum_q.data_ptr(),
                                    rowsum_k.data_ptr(), w_q.data_ptr(), w_k.data_ptr(), int(w_stride),
-                                   float(w_scale), inv_norm.data_ptr(), dz.data_ptr(), workspace.data_ptr(),
+                                   self._weight_dtype(w_q, w_k), float(w_scale), inv_norm.data_ptr(), dz.data_ptr(),
+                                   workspace.data_ptr(),
                                    workspace.numel() * workspace.element_size(), _stream(q)))
 
     def profile_next(self, which: int, ev_start: "torch.cuda.Event", ev_stop: "torch.cuda.Event"):

@@ -190,10 +190,8 @@ int ntx_l2norm(const void* view0, const void* view1, int n, int d, int in_dtype,
                   rows_dtype);
     NTX_CHECK_ARG(ld >= ntx_row_pitch(d, rows_dtype) && ld % (rows_dtype == NTX_BF16 ? 64 : 4) == 0,
                   "ld=%d too small or misaligned for d=%d", ld, d);
-    NtxPeers dst{};
-    dst.base[0] = rows;
-    dst.count = 1;
-    return ntx_l2norm_launch(view0, view1, n, d, in_dtype, dst, 0, ld, rows_dtype, inv_norm, (cudaStream_t)stream);
+    return ntx_l2norm_launch(view0, view1, n, d, in_dtype, rows, NtxPeerOut{}, 0, 0, nullptr, ld, rows_dtype, inv_norm,
+                             (cudaStream_t)stream);
 }
 
 int ntx_project_l2norm(const void* h0, const void* h1, const void* weight, int n, int hdim, int d, void* rows,
@@ -210,54 +208,22 @@ int ntx_project_l2norm(const void* h0, const void* h1, const void* weight, int n
     return ntx_project_launch(h0, h1, weight, n, hdim, d, rows, ld, inv_norm, (cudaStream_t)stream);
 }
 
-static int fill_peers(NtxPeers* out, void* const* peers, int world, const char* who) {
-    if (world < 1 || world > NTX_MAX_PEERS) {
-        ntx_set_error("%s: world=%d outside [1, %d] (peer memory spans one node)", who, world, NTX_MAX_PEERS);
-        return NTX_E_ARG;
-    }
-    if (!peers) { ntx_set_error("%s: NULL peer table", who); return NTX_E_ARG; }
-    for (int p = 0; p < world; ++p) {
-        if (!peers[p]) { ntx_set_error("%s: peer buffer %d is NULL", who, p); return NTX_E_ARG; }
-        out->base[p] = peers[p];
-    }
-    out->count = world;
-    return NTX_OK;
-}
+}  // extern "C"
 
-int ntx_l2norm_peers(const void* view0, const void* view1, int n, int d, int in_dtype, void* const* peer_keys,
-                     int world, int rank, int ld, int rows_dtype, float* inv_norm, void* stream) {
-    NTX_CHECK_ARG(n >= 1 && d >= 1, "bad sizes n=%d d=%d", n, d);
-    NTX_CHECK_ARG(view0 && view1 && inv_norm, "NULL buffer");
-    NTX_CHECK_ARG(in_dtype == NTX_F32 || in_dtype == NTX_BF16, "view dtype %d not supported", in_dtype);
-    NTX_CHECK_ARG(rows_dtype == NTX_F32 || rows_dtype == NTX_BF16, "rows dtype %d not supported",
-                  rows_dtype);
-    NTX_CHECK_ARG(ld >= ntx_row_pitch(d, rows_dtype) && ld % (rows_dtype == NTX_BF16 ? 64 : 4) == 0,
-                  "ld=%d too small or misaligned for d=%d", ld, d);
-    NTX_CHECK_ARG(rank >= 0 && rank < world, "rank %d outside world %d", rank, world);
-    NtxPeers dst{};
-    int rc = fill_peers(&dst, peer_keys, world, "ntx_l2norm_peers");
-    if (rc) return rc;
-    return ntx_l2norm_launch(view0, view1, n, d, in_dtype, dst, (size_t)rank * 2 * (size_t)n, ld, rows_dtype,
-                             inv_norm, (cudaStream_t)stream);
-}
+namespace {
 
-int ntx_scatter_peers(const void* src, size_t bytes, void* const* peer_dst, int world, size_t dst_offset,
-                      void* stream) {
-    NTX_CHECK_ARG(src != nullptr, "NULL source");
-    NTX_CHECK_ARG(reinterpret_cast<uintptr_t>(src) % 16 == 0 && dst_offset % 16 == 0,
-                  "source and destination offset must be 16-byte aligned");
-    NtxPeers dst{};
-    int rc = fill_peers(&dst, peer_dst, world, "ntx_scatter_peers");
-    if (rc) return rc;
-    for (int p = 0; p < world; ++p)
-        NTX_CHECK_ARG(reinterpret_cast<uintptr_t>(dst.base[p]) % 16 == 0, "peer buffer %d not 16-byte aligned", p);
-    if (bytes == 0) return NTX_OK;
-    return ntx_scatter_launch(src, bytes, dst, dst_offset, (cudaStream_t)stream);
-}
+// the exchange of one call: where its results go on every rank, what it waits for, where key buffer 1 lies
+struct Exchange {
+    NtxPeerOut out{};
+    NtxGate gate{};
+    NtxPeerGeom geom{};
+    size_t key_buf_elems = 0;
+};
 
-int ntx_fwd(const void* q, const void* k, int q_rows, int k_rows, int d, int ld, int dtype,
-            const NtxLayout* layout, float temperature, float* rowsum, float* pos_logit,
-            float* row_loss, float* loss_sum, void* workspace, size_t workspace_bytes, void* stream) {
+int fwd_impl(const void* q, const void* k, int q_rows, int k_rows, int d, int ld, int dtype,
+             const NtxLayout* layout, float temperature, float* rowsum, float* pos_logit,
+             float* row_loss, float* loss_sum, void* workspace, size_t workspace_bytes, const Exchange& ex,
+             void* stream) {
     NtxDims dm;
     int rc = make_dims(q_rows, k_rows, d, ld, dtype, layout, temperature, &dm);
     if (rc) return rc;
@@ -288,20 +254,36 @@ int ntx_fwd(const void* q, const void* k, int q_rows, int k_rows, int d, int ld,
             rc = ntx_tc_fwd_sym_launch((const __nv_bfloat16*)q, dm, plan, partial, colpart, counter, st);
         else if (plan.tensor_cores)
             rc = ntx_tc_fwd_launch((const __nv_bfloat16*)q, (const __nv_bfloat16*)k, dm, plan, partial,
-                                   counter, st);
+                                   counter, ex.gate, ex.key_buf_elems, st);
         else
-            rc = ntx_simt_fwd_launch((const float*)q, (const float*)k, dm, plan, partial, counter, st);
+            rc = ntx_simt_fwd_launch((const float*)q, (const float*)k, dm, plan, partial, counter, ex.gate,
+                                     ex.key_buf_elems, st);
     }
     if (rc) return rc;
     return ntx_fwd_finalize_launch(q, dtype, dm, plan, partial, colpart, counter, block_sums, rowsum,
-                                   pos_logit, row_loss, loss_sum, st);
+                                   pos_logit, row_loss, loss_sum, ex.out, ex.geom.rowsum_off, ex.gate,
+                                   ex.key_buf_elems, st);
 }
+
+}  // namespace
+
+extern "C" {
+
+int ntx_fwd(const void* q, const void* k, int q_rows, int k_rows, int d, int ld, int dtype,
+            const NtxLayout* layout, float temperature, float* rowsum, float* pos_logit,
+            float* row_loss, float* loss_sum, void* workspace, size_t workspace_bytes, void* stream) {
+    return fwd_impl(q, k, q_rows, k_rows, d, ld, dtype, layout, temperature, rowsum, pos_logit, row_loss, loss_sum,
+                    workspace, workspace_bytes, Exchange{}, stream);
+}
+
+}  // extern "C"
 
 static int bwd_impl(const void* q, const void* k, int q_rows, int k_rows, int d, int ld, int dtype,
                     const NtxLayout* layout, float temperature, const float* rowsum_q, const float* rowsum_k,
-                    const float* w_q, const float* w_k, int w_stride, float w_scale, const void* view0,
+                    const void* w_q, const void* w_k, int w_stride, int w_dtype, float w_scale, const void* view0,
                     const void* view1, int in_dtype, int in_ld, int normalised, const float* inv_norm,
-                    void* dview0, void* dview1, void* workspace, size_t workspace_bytes, void* stream) {
+                    void* dview0, void* dview1, void* workspace, size_t workspace_bytes, void* stream,
+                    const Exchange& ex = Exchange{}, int w_chunk = 0) {
     NtxDims dm;
     int rc = make_dims(q_rows, k_rows, d, ld, dtype, layout, temperature, &dm);
     if (rc) return rc;
@@ -309,6 +291,7 @@ static int bwd_impl(const void* q, const void* k, int q_rows, int k_rows, int d,
     NTX_CHECK_ARG(rowsum_q && rowsum_k && w_q && w_k && view0 && view1 && inv_norm && dview0 && dview1,
                   "NULL buffer");
     NTX_CHECK_ARG(w_stride == 0 || w_stride == 1, "w_stride must be 0 (one weight) or 1 (one per row)");
+    NTX_CHECK_ARG(w_dtype == NTX_F32 || w_dtype == NTX_BF16, "weight dtype %d not supported", w_dtype);
     NTX_CHECK_ARG(in_dtype == NTX_F32 || in_dtype == NTX_BF16, "view dtype %d not supported", in_dtype);
     NtxPlan plan;
     if ((rc = ntx_plan(q_rows, k_rows, d, dtype, 0, &plan))) return rc;
@@ -320,33 +303,148 @@ static int bwd_impl(const void* q, const void* k, int q_rows, int k_rows, int d,
     if ((rc = aligned16(workspace, "workspace"))) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     float* partial = (float*)workspace;
-    const NtxWeights wt{rowsum_q, rowsum_k, w_q, w_k, w_stride, w_scale};
+    const NtxWeights wt{rowsum_q, rowsum_k, (const float*)w_q, (const float*)w_k, w_stride, w_scale, w_chunk,
+                        w_dtype == NTX_BF16 ? 1 : 0};
     {
         ProfScope prof(1, st);
         if (plan.tensor_cores)
-            rc = ntx_tc_bwd_launch((const __nv_bfloat16*)q, (const __nv_bfloat16*)k, dm, plan, wt, partial, st);
+            rc = ntx_tc_bwd_launch((const __nv_bfloat16*)q, (const __nv_bfloat16*)k, dm, plan, wt, partial, ex.gate,
+                                   ex.key_buf_elems, st);
         else
-            rc = ntx_simt_bwd_launch((const float*)q, (const float*)k, dm, plan, wt, partial, st);
+            rc = ntx_simt_bwd_launch((const float*)q, (const float*)k, dm, plan, wt, partial, ex.gate,
+                                     ex.key_buf_elems, st);
     }
     if (rc) return rc;
     return ntx_bwd_finalize_launch(dm, plan, partial, wt, view0, view1, in_dtype, inv_norm, dview0,
                                    dview1, st, in_ld, normalised);
 }
 
+namespace {
+
+// NtxPeerBlocks -> what the kernels need; checks the table
+int make_exchange(const NtxPeerBlocks* pb, int q_rows, int ld, int dtype, const uint32_t* step, Exchange* ex,
+                  const char* who) {
+    if (!pb) { ntx_set_error("%s: NULL peer blocks", who); return NTX_E_ARG; }
+    if (pb->world < 1 || pb->world > NTX_MAX_PEERS || pb->rank < 0 || pb->rank >= pb->world) {
+        ntx_set_error("%s: world=%d rank=%d outside [1, %d] (peer memory spans one node)", who, pb->world, pb->rank,
+                      NTX_MAX_PEERS);
+        return NTX_E_ARG;
+    }
+    for (int p = 0; p < pb->world; ++p) {
+        if (!pb->base[p] || reinterpret_cast<uintptr_t>(pb->base[p]) % 1024 != 0) {
+            ntx_set_error("%s: block of rank %d is NULL or not 1024-byte aligned", who, p);
+            return NTX_E_ARG;
+        }
+        ex->out.base[p] = static_cast<uint8_t*>(pb->base[p]);
+    }
+    if (!step) { ntx_set_error("%s: NULL step word", who); return NTX_E_ARG; }
+    const int esz = dtype == NTX_BF16 ? 2 : 4;
+    ex->out.world = pb->world;
+    ex->out.rank = pb->rank;
+    ex->geom = ntx_peer_geom(q_rows, ld, esz, pb->world);
+    ex->key_buf_elems = ex->geom.key_buf_bytes / esz;
+    ex->gate.step = step;
+    ex->gate.ctl = reinterpret_cast<const uint32_t*>(pb->base[pb->rank]);
+    ex->gate.chunk_rows = q_rows;
+    ex->gate.world = pb->world;
+    return NTX_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t ntx_peer_block_bytes(int q_rows, int ld, int rows_dtype, int world) {
+    if (q_rows < 1 || ld < 1 || world < 1 || world > NTX_MAX_PEERS) return 0;
+    return ntx_peer_geom(q_rows, ld, rows_dtype == NTX_BF16 ? 2 : 4, world).total;
+}
+
+int ntx_peer_l2norm(const void* view0, const void* view1, int n, int d, int in_dtype, const NtxPeerBlocks* blocks,
+                    int ld, int rows_dtype, float* inv_norm, uint32_t* step, void* stream) {
+    NTX_CHECK_ARG(n >= 1 && d >= 1, "bad sizes n=%d d=%d", n, d);
+    NTX_CHECK_ARG(view0 && view1 && inv_norm, "NULL buffer");
+    NTX_CHECK_ARG(in_dtype == NTX_F32 || in_dtype == NTX_BF16, "view dtype %d not supported", in_dtype);
+    NTX_CHECK_ARG(rows_dtype == NTX_F32 || rows_dtype == NTX_BF16, "rows dtype %d not supported", rows_dtype);
+    NTX_CHECK_ARG(ld == ntx_row_pitch(d, rows_dtype), "ld=%d must be ntx_row_pitch(d=%d)=%d", ld, d,
+                  ntx_row_pitch(d, rows_dtype));
+    Exchange ex;
+    int rc = make_exchange(blocks, 2 * n, ld, rows_dtype, step, &ex, "ntx_peer_l2norm");
+    if (rc) return rc;
+    return ntx_l2norm_launch(view0, view1, n, d, in_dtype, nullptr, ex.out, ex.geom.keys_off, ex.geom.key_buf_bytes,
+                             step, ld, rows_dtype, inv_norm, (cudaStream_t)stream);
+}
+
+int ntx_peer_fwd(const NtxPeerBlocks* blocks, int n_local, int d, int ld, int dtype, float temperature,
+                 const uint32_t* step, float* rowsum, float* pos_logit, float* row_loss, float* loss_sum,
+                 void* workspace, size_t workspace_bytes, void* stream) {
+    NTX_CHECK_ARG(n_local >= 1 && d >= 1, "bad sizes n_local=%d d=%d", n_local, d);
+    NTX_CHECK_ARG(dtype == NTX_F32 || dtype == NTX_BF16, "rows dtype %d not supported", dtype);
+    const int q_rows = 2 * n_local;
+    Exchange ex;
+    int rc = make_exchange(blocks, q_rows, ld, dtype, step, &ex, "ntx_peer_fwd");
+    if (rc) return rc;
+    const NtxLayout lay{n_local, blocks->world, blocks->rank};
+    const size_t esz = dtype == NTX_BF16 ? 2 : 4;
+    const uint8_t* keys = ex.out.base[blocks->rank] + ex.geom.keys_off;            // key buffer 0 of this rank's block
+    const uint8_t* q = keys + (size_t)blocks->rank * q_rows * ld * esz;
+    return fwd_impl(q, keys, q_rows, q_rows * blocks->world, d, ld, dtype, &lay, temperature, rowsum, pos_logit, row_loss,
+                    loss_sum, workspace, workspace_bytes, ex, stream);
+}
+
+int ntx_peer_post_weights(const NtxPeerBlocks* blocks, int n_local, int ld, int dtype, const uint32_t* step,
+                          const void* w, int w_stride, int w_dtype, void* stream) {
+    NTX_CHECK_ARG(n_local >= 1, "bad size n_local=%d", n_local);
+    NTX_CHECK_ARG(dtype == NTX_F32 || dtype == NTX_BF16, "rows dtype %d not supported", dtype);
+    NTX_CHECK_ARG(w != nullptr, "NULL row weights");
+    NTX_CHECK_ARG(w_stride == 0 || w_stride == 1, "w_stride must be 0 (one weight) or 1 (one per row)");
+    NTX_CHECK_ARG(w_dtype == NTX_F32 || w_dtype == NTX_BF16, "weight dtype %d not supported", w_dtype);
+    Exchange ex;
+    int rc = make_exchange(blocks, 2 * n_local, ld, dtype, step, &ex, "ntx_peer_post_weights");
+    if (rc) return rc;
+    return ntx_post_weights_launch(w, w_stride, w_dtype == NTX_BF16 ? 1 : 0, 2 * n_local, ex.out, ex.geom.weight_off,
+                                   step, (cudaStream_t)stream);
+}
+
+int ntx_peer_bwd(const NtxPeerBlocks* blocks, int n_local, int d, int ld, int dtype, float temperature,
+                 const uint32_t* step, const float* rowsum_q, int w_stride, float w_scale, const void* view0,
+                 const void* view1, int in_dtype, const float* inv_norm, void* dview0, void* dview1, void* workspace,
+                 size_t workspace_bytes, void* stream) {
+    NTX_CHECK_ARG(n_local >= 1 && d >= 1, "bad sizes n_local=%d d=%d", n_local, d);
+    NTX_CHECK_ARG(w_stride == 0 || w_stride == 1, "w_stride must be 0 (one weight) or 1 (one per row)");
+    NTX_CHECK_ARG(dtype == NTX_F32 || dtype == NTX_BF16, "rows dtype %d not supported", dtype);
+    const int q_rows = 2 * n_local;
+    Exchange ex;
+    int rc = make_exchange(blocks, q_rows, ld, dtype, step, &ex, "ntx_peer_bwd");
+    if (rc) return rc;
+    const NtxLayout lay{n_local, blocks->world, blocks->rank};
+    const size_t esz = dtype == NTX_BF16 ? 2 : 4;
+    const uint8_t* own = ex.out.base[blocks->rank];
+    const uint8_t* keys = own + ex.geom.keys_off;
+    const uint8_t* q = keys + (size_t)blocks->rank * q_rows * ld * esz;
+    const float* rowsum_k = reinterpret_cast<const float*>(own + ex.geom.rowsum_off);
+    const float* w_k = reinterpret_cast<const float*>(own + ex.geom.weight_off);
+    // one weight per rank (posted with w_stride 0): this rank's is w_k[rank], key c's is w_k[c / q_rows];
+    // one per row: this rank's rows start at w_k[rank * q_rows], key c's is w_k[c]
+    const float* w_q = w_stride == 0 ? w_k + blocks->rank : w_k + (size_t)blocks->rank * q_rows;
+    return bwd_impl(q, keys, q_rows, q_rows * blocks->world, d, ld, dtype, &lay, temperature, rowsum_q, rowsum_k, w_q,
+                    w_k, w_stride, NTX_F32, w_scale, view0, view1, in_dtype, 0, 0, inv_norm, dview0, dview1, workspace,
+                    workspace_bytes, stream, ex, w_stride == 0 ? q_rows : 0);
+}
+
 int ntx_bwd(const void* q, const void* k, int q_rows, int k_rows, int d, int ld, int dtype,
             const NtxLayout* layout, float temperature, const float* rowsum_q, const float* rowsum_k,
-            const float* w_q, const float* w_k, int w_stride, float w_scale, const void* view0,
+            const void* w_q, const void* w_k, int w_stride, int w_dtype, float w_scale, const void* view0,
             const void* view1, int in_dtype, const float* inv_norm, void* dview0, void* dview1,
             void* workspace, size_t workspace_bytes, void* stream) {
     return bwd_impl(q, k, q_rows, k_rows, d, ld, dtype, layout, temperature, rowsum_q, rowsum_k, w_q, w_k, w_stride,
-                    w_scale, view0, view1, in_dtype, 0, 0, inv_norm, dview0, dview1, workspace, workspace_bytes,
+                    w_dtype, w_scale, view0, view1, in_dtype, 0, 0, inv_norm, dview0, dview1, workspace, workspace_bytes,
                     stream);
 }
 
 int ntx_bwd_rows(const void* q, const void* k, int q_rows, int k_rows, int d, int ld, int dtype,
                  const NtxLayout* layout, float temperature, const float* rowsum_q, const float* rowsum_k,
-                 const float* w_q, const float* w_k, int w_stride, float w_scale, const float* inv_norm, void* dz,
-                 void* workspace, size_t workspace_bytes, void* stream) {
+                 const void* w_q, const void* w_k, int w_stride, int w_dtype, float w_scale, const float* inv_norm,
+                 void* dz, void* workspace, size_t workspace_bytes, void* stream) {
     NTX_CHECK_ARG(q != nullptr && dz != nullptr && layout != nullptr, "NULL buffer");
     NTX_CHECK_ARG(dtype == NTX_F32 || dtype == NTX_BF16, "rows dtype %d not supported", dtype);
     const size_t esz = dtype == NTX_BF16 ? 2 : 4;
@@ -355,7 +453,7 @@ int ntx_bwd_rows(const void* q, const void* k, int q_rows, int k_rows, int d, in
     const char* qb = static_cast<const char*>(q);
     char* out = static_cast<char*>(dz);
     return bwd_impl(q, k, q_rows, k_rows, d, ld, dtype, layout, temperature, rowsum_q, rowsum_k, w_q, w_k, w_stride,
-                    w_scale, qb, qb + (size_t)n * ld * esz, dtype, ld, 1, inv_norm, out, out + (size_t)n * d * esz,
+                    w_dtype, w_scale, qb, qb + (size_t)n * ld * esz, dtype, ld, 1, inv_norm, out, out + (size_t)n * d * esz,
                     workspace, workspace_bytes, stream);
 }
 

@@ -144,38 +144,145 @@ struct NtxWeights {
     const float* w_k;
     int w_stride;      // 0: one upstream gradient for every row (mean / sum), 1: one per row (none)
     float w_scale;     // 1 / q_rows for mean, 1 otherwise
+    int w_chunk;       // > 0 (peer exchange, one weight per RANK): the weight of key c is w_k[c / w_chunk]
+    int w_bf16;        // 1: w_q / w_k point at bf16 values (the upstream gradient of a bf16 loss), 0: fp32
+};
+#ifdef __CUDACC__
+// one weight, fp32 or bf16 (read-only for the kernel's lifetime unless `l2`, which skips L1: data written by a peer)
+__device__ __forceinline__ float ntx_ld_weight(const float* base, size_t i, int bf16, bool l2 = false) {
+    if (bf16) {
+        const unsigned short* p = reinterpret_cast<const unsigned short*>(base) + i;
+        unsigned short v;
+        if (l2) asm volatile("ld.relaxed.gpu.global.u16 %0, [%1];" : "=h"(v) : "l"(p) : "memory");
+        else v = __ldg(p);
+        return __uint_as_float((unsigned)v << 16);
+    }
+    if (l2) {
+        float v;
+        asm volatile("ld.relaxed.gpu.global.f32 %0, [%1];" : "=f"(v) : "l"(base + i) : "memory");
+        return v;
+    }
+    return __ldg(base + i);
+}
+#endif
+NTX_HD size_t ntx_key_weight_index(int c, int w_stride, int w_chunk) {
+    return w_chunk > 0 ? (size_t)(c / w_chunk) : (size_t)c * w_stride;
+}
+
+// ---------------------------------------------------------------------------
+// peer exchange (one node, NVLink peer memory; include/ntxent_b200.h "Multi-rank exchange")
+// ---------------------------------------------------------------------------
+// Every rank owns one exchange block, mapped into every process:
+//   [0, 256)            control words (uint32): [0] steps taken, [1] / [2] tickets of the normalise / weight-post kernel,
+//                       [8 + p] kflag, [16 + p] rflag, [24 + p] wflag: rank p's keys / row sums / row weights
+//                       of step >= the stored value have landed in THIS block
+//   [256, ...)          float rowsum[world * q_rows], float weight[world * q_rows]  (rank-major, like the keys; with one
+//                       upstream gradient per rank only weight[0 .. world) is used: one value per rank)
+//   [keys_off, ...)     two key buffers [world * q_rows x ld], used by alternate steps
+#define NTX_CTL_BYTES 256
+#define NTX_CTL_STEP 0
+#define NTX_CTL_TICKET 1
+#define NTX_CTL_POST_TICKET 2
+#define NTX_CTL_KFLAG 8
+#define NTX_CTL_RFLAG 16
+#define NTX_CTL_WFLAG 24
+
+struct NtxPeerGeom {           // byte offsets inside an exchange block
+    size_t rowsum_off, weight_off, keys_off, key_buf_bytes, total;
+};
+NTX_HD NtxPeerGeom ntx_peer_geom(int q_rows, int ld, int esz, int world) {
+    NtxPeerGeom g;
+    const size_t vec = (size_t)world * q_rows * sizeof(float);
+    g.rowsum_off = NTX_CTL_BYTES;
+    g.weight_off = g.rowsum_off + vec;
+    g.keys_off = (g.weight_off + vec + 1023) & ~(size_t)1023;
+    g.key_buf_bytes = (((size_t)world * q_rows * ld * esz) + 1023) & ~(size_t)1023;
+    g.total = g.keys_off + 2 * g.key_buf_bytes;
+    return g;
+}
+
+// What a kernel needs to store into every rank's block and to raise the flags there.
+struct NtxPeerOut {
+    uint8_t* base[NTX_MAX_PEERS];   // block of rank p as mapped into this process; base[rank] is this rank's own
+    int world, rank;                // world == 0: no exchange
+};
+// What a kernel needs to wait for data other ranks store into this rank's block.
+struct NtxGate {
+    const uint32_t* step;           // number of the step being computed (device memory; NULL = no exchange)
+    const uint32_t* ctl;            // this rank's control words
+    int chunk_rows;                 // keys per rank
+    int world;
 };
 
+#ifdef __CUDACC__
+__device__ __forceinline__ uint32_t ntx_ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+// Raising the flags of a step.  A system-scope fence after stores to peer memory waits for their round trip over
+// NVLink (~2 us measured), and st.release.sys carries one each: a fence per thread, per CTA or per flag multiplies
+// that.  So: every CTA orders its stores with a GPU-scope fence and takes a ticket; the last CTA alone issues ONE
+// system-scope fence -- cumulative over everything the tickets made visible to it -- and then writes the flag
+// word of every rank with relaxed stores, back to back.
+__device__ __forceinline__ void ntx_fence_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
+__device__ __forceinline__ void ntx_st_relaxed_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void ntx_raise_flags(const NtxPeerOut& peers, int word, uint32_t step) {
+    ntx_fence_sys();
+    for (int p = 0; p < peers.world; ++p)
+        ntx_st_relaxed_sys(reinterpret_cast<uint32_t*>(peers.base[p]) + word + peers.rank, step);
+}
+__device__ __forceinline__ uint32_t ntx_ld_relaxed(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ float ntx_ld_l2(const float* p) {            // skips L1: the line may have been written by a peer
+    float v;
+    asm volatile("ld.relaxed.gpu.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+    return v;
+}
+// spin until flag word `which + p` of this rank's block has reached `step` (wrap-safe)
+__device__ __forceinline__ void ntx_gate_wait(const uint32_t* ctl, int word, uint32_t step) {
+    while ((int)(ntx_ld_acquire_sys(ctl + word) - step) < 0) __nanosleep(32);
+}
+#endif
+
 // launch helpers implemented per translation unit
-// Destinations of a kernel that writes the same rows into the buffers of several ranks (peer memory mapped
-// into this process; one node, at most NTX_MAX_PEERS ranks).  count == 1 is the ordinary local case.
-#define NTX_MAX_PEERS 8
-struct NtxPeers {
-    void* base[NTX_MAX_PEERS];
-    int count;
-};
-int ntx_l2norm_launch(const void* v0, const void* v1, int n, int d, int in_dtype, const NtxPeers& rows,
-                      size_t row_offset, int ld, int rows_dtype, float* inv_norm, cudaStream_t st);
-int ntx_scatter_launch(const void* src, size_t bytes, const NtxPeers& dst, size_t dst_offset, cudaStream_t st);
+int ntx_l2norm_launch(const void* v0, const void* v1, int n, int d, int in_dtype, void* rows, const NtxPeerOut& peers,
+                      size_t keys_off, size_t key_buf_bytes, uint32_t* step_out, int ld, int rows_dtype,
+                      float* inv_norm, cudaStream_t st);
+int ntx_post_weights_launch(const void* w, int w_stride, int w_bf16, int q_rows, const NtxPeerOut& peers, size_t weight_off,
+                            const uint32_t* step, cudaStream_t st);
 int ntx_make_rows_tmap(void* map, const void* base, int rows, int ld, int box_rows);      // map = CUtensorMap*
 int ntx_project_launch(const void* h0, const void* h1, const void* weight, int n, int hdim, int d, void* rows, int ld,
                        float* inv_norm, cudaStream_t st);
+// q / k: the rows; with an exchange (gate.step != NULL) they point at key buffer 0 and buffer 1 lies key_buf_elems
+// elements further on -- the kernels pick the buffer of the step
 int ntx_simt_fwd_launch(const float* q, const float* k, const NtxDims& dm, const NtxPlan& plan,
-                        float* partial, unsigned int* counter, cudaStream_t st);
+                        float* partial, unsigned int* counter, const NtxGate& gate, size_t key_buf_elems,
+                        cudaStream_t st);
 int ntx_simt_bwd_launch(const float* q, const float* k, const NtxDims& dm, const NtxPlan& plan,
-                        const NtxWeights& w, float* partial, cudaStream_t st);
+                        const NtxWeights& w, float* partial, const NtxGate& gate, size_t key_buf_elems,
+                        cudaStream_t st);
 int ntx_tc_fwd_launch(const __nv_bfloat16* q, const __nv_bfloat16* k, const NtxDims& dm,
-                      const NtxPlan& plan, float* partial, unsigned int* counter, cudaStream_t st);
+                      const NtxPlan& plan, float* partial, unsigned int* counter, const NtxGate& gate,
+                      size_t key_buf_elems, cudaStream_t st);
 int ntx_tc_fwd_sym_launch(const __nv_bfloat16* rows, const NtxDims& dm, const NtxPlan& plan, float* partial,
                           float* colpart, unsigned int* counter, cudaStream_t st);
 int ntx_tc_bwd_launch(const __nv_bfloat16* q, const __nv_bfloat16* k, const NtxDims& dm,
-                      const NtxPlan& plan, const NtxWeights& w, float* partial, cudaStream_t st);
+                      const NtxPlan& plan, const NtxWeights& w, float* partial, const NtxGate& gate,
+                      size_t key_buf_elems, cudaStream_t st);
 int ntx_fwd_finalize_blocks(int q_rows, int ld);   // grid of the forward finalize (one fp64 block sum each)
 // colpart != NULL: symmetric forward (upper-triangle partition, column partials added per row)
+// peers.world > 0: the row sums also go to every rank's block (rowsum_off) and the last block raises rflag
 int ntx_fwd_finalize_launch(const void* q, int dtype, const NtxDims& dm, const NtxPlan& plan,
                             const float* partial, const float* colpart, unsigned int* counter,
                             double* block_sums, float* rowsum, float* pos_logit, float* row_loss,
-                            float* loss_sum, cudaStream_t st);
+                            float* loss_sum, const NtxPeerOut& peers, size_t rowsum_off, const NtxGate& gate,
+                            size_t key_buf_elems, cudaStream_t st);
 int ntx_debug_indices_launch(int n_local, int rank, int32_t* self_col, int32_t* pos_col,
                              cudaStream_t st);
 int ntx_bwd_finalize_launch(const NtxDims& dm, const NtxPlan& plan, const float* partial,

@@ -54,9 +54,13 @@ fwd_finalize_kernel(const T* __restrict__ q, NtxDims dm, int lanes, int tile_row
                     const float* __restrict__ colpart, unsigned int* __restrict__ counter,
                     double* __restrict__ block_sums, float* __restrict__ rowsum,
                     float* __restrict__ pos_logit, float* __restrict__ row_loss,
-                    float* __restrict__ loss_sum) {
+                    float* __restrict__ loss_sum, NtxPeerOut peers, size_t rowsum_off, NtxGate gate,
+                    size_t key_buf_elems) {
     ntx_dep_trigger();
     ntx_dep_wait();
+    // peer exchange: the rows sit in the key buffer of this step; the row sums also go to every rank's block
+    const uint32_t step = gate.step ? *gate.step : 0u;      // written by the normalise kernel, earlier on the stream
+    if (step & 1u) q += key_buf_elems;
     // rows of one block share a row block (tile_rows is a multiple of rows_per_block): one slot count.
     // colpart != NULL: the symmetric forward's upper-triangle partition (Tt, G describe that one).
     __shared__ int ns_sh;
@@ -106,6 +110,8 @@ fwd_finalize_kernel(const T* __restrict__ q, NtxDims dm, int lanes, int tile_row
             pos_logit[r] = pos;
             row_loss[r] = l;
             my_loss = (double)l;
+            for (int p = 0; p < peers.world; ++p)
+                reinterpret_cast<float*>(peers.base[p] + rowsum_off)[(size_t)peers.rank * dm.q_rows + r] = R;
         }
     }
     // Block sums in a fixed order, then the last block standing adds the block sums in block
@@ -121,7 +127,7 @@ fwd_finalize_kernel(const T* __restrict__ q, NtxDims dm, int lanes, int tile_row
         double v = 0.0;
         for (int w = 0; w < kFwdThreads / 32; ++w) v += part[w];
         block_sums[blockIdx.x] = v;
-        __threadfence();
+        __threadfence();                                     // also orders the block's peer stores (barrier above)
         is_last = atomicAdd(counter, 1u) == gridDim.x - 1;
     }
     __syncthreads();
@@ -139,6 +145,7 @@ fwd_finalize_kernel(const T* __restrict__ q, NtxDims dm, int lanes, int tile_row
         loss_sum[0] = (float)v;                              // reduction="sum"
         loss_sum[1] = (float)(v / (double)dm.q_rows);        // reduction="mean": sum / N * 0.5, rows = 2N
         *counter = 0;
+        if (peers.world > 0) ntx_raise_flags(peers, NTX_CTL_RFLAG, step);   // every block's row sums are out
     }
 }
 
@@ -156,7 +163,8 @@ struct BwdFinArgs {
 
 __device__ __forceinline__ float pair_weight(const NtxWeights& w, int r, int p) {
     // (P - Y) and its transpose both hit the positive pair: weight w_r + w_p
-    return (__ldg(w.w_q + (size_t)r * w.w_stride) + __ldg(w.w_q + (size_t)p * w.w_stride)) * w.w_scale;
+    return (ntx_ld_weight(w.w_q, (size_t)r * w.w_stride, w.w_bf16) + ntx_ld_weight(w.w_q, (size_t)p * w.w_stride, w.w_bf16)) *
+           w.w_scale;
 }
 
 // fast path: d % 4 == 0, one group of `lanes` threads per row, up to kMaxV float4 per thread
@@ -322,7 +330,8 @@ int ntx_fwd_finalize_blocks(int q_rows, int ld) {
 int ntx_fwd_finalize_launch(const void* q, int dtype, const NtxDims& dm, const NtxPlan& plan,
                             const float* partial, const float* colpart, unsigned int* counter,
                             double* block_sums, float* rowsum, float* pos_logit, float* row_loss,
-                            float* loss_sum, cudaStream_t st) {
+                            float* loss_sum, const NtxPeerOut& peers, size_t rowsum_off, const NtxGate& gate,
+                            size_t key_buf_elems, cudaStream_t st) {
     const long long T = colpart ? (long long)plan.row_blocks * (plan.row_blocks + 1) / 2
                                 : (long long)plan.row_blocks * plan.key_tiles;
     const int G = colpart ? plan.fwd_grid : plan.grid;
@@ -332,11 +341,13 @@ int ntx_fwd_finalize_launch(const void* q, int dtype, const NtxDims& dm, const N
     if (dtype == NTX_F32)
         NTX_CUDA(ntx_launch_dep(fwd_finalize_kernel<float>, grid, kFwdThreads, 0, st, (const float*)q, dm, lanes,
                                 plan.tile_rows, plan.key_tiles, T, G, rows_pad, partial, colpart, counter,
-                                block_sums, rowsum, pos_logit, row_loss, loss_sum));
+                                block_sums, rowsum, pos_logit, row_loss, loss_sum, peers, rowsum_off, gate,
+                                key_buf_elems));
     else
         NTX_CUDA(ntx_launch_dep(fwd_finalize_kernel<__nv_bfloat16>, grid, kFwdThreads, 0, st,
                                 (const __nv_bfloat16*)q, dm, lanes, plan.tile_rows, plan.key_tiles, T, G, rows_pad,
-                                partial, colpart, counter, block_sums, rowsum, pos_logit, row_loss, loss_sum));
+                                partial, colpart, counter, block_sums, rowsum, pos_logit, row_loss, loss_sum, peers,
+                                rowsum_off, gate, key_buf_elems));
     return NTX_OK;
 }
 

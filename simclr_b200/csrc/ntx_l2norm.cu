@@ -58,10 +58,17 @@ __device__ __forceinline__ void storev(__nv_bfloat16* p, const float (&v)[N]) {
 
 // `lanes` consecutive threads (power of two <= 32) share one row, so short rows
 // (d = 128 bf16 is only 16 sixteen-byte loads) still keep every lane busy.
+//
+// Peer mode (peers.world > 0): the rows go into the key buffer of the step in EVERY rank's exchange block
+// (rows [rank*2n, (rank+1)*2n) there), over NVLink for the other ranks.  The step number is this rank's own
+// count of normalise calls (control word 0 of its block): it picks the key buffer (step & 1), is handed to the
+// later kernels of the step through *step_out, and is what the last CTA to finish stores -- after a system-scope
+// fence -- into kflag[rank] of every block, which is what the readers on the other ranks wait for.
 template <typename TIn, typename TOut, bool kVector>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 l2norm_kernel(const TIn* __restrict__ view0, const TIn* __restrict__ view1, int n, int d,
-              NtxPeers rows, size_t row_offset, int ld, float* __restrict__ inv_norm, int lanes) {
+              TOut* __restrict__ rows_local, NtxPeerOut peers, size_t keys_off, size_t key_buf_bytes,
+              uint32_t* __restrict__ step_out, int ld, float* __restrict__ inv_norm, int lanes) {
     ntx_dep_trigger();
     ntx_dep_wait();
     const int sub = threadIdx.x % lanes;
@@ -70,8 +77,22 @@ l2norm_kernel(const TIn* __restrict__ view0, const TIn* __restrict__ view1, int 
     const bool live = r_raw < 2 * n;
     const int r = live ? r_raw : 2 * n - 1;                   // keep every lane in the shuffles
     const TIn* src = (r < n) ? view0 + (size_t)r * d : view1 + (size_t)(r - n) * d;
-    const size_t dst_off = (row_offset + (size_t)r) * ld;     // same place in every destination buffer
     constexpr int V = Vec<TIn>::N;
+    const int ndst = peers.world > 0 ? peers.world : 1;
+    uint32_t* ctl = nullptr;
+    uint32_t step = 0;
+    size_t dst_off = (size_t)r * ld;                          // elements, same place in every destination
+    size_t dst_bytes = 0;
+    if (peers.world > 0) {
+        ctl = reinterpret_cast<uint32_t*>(peers.base[peers.rank]);
+        step = ctl[NTX_CTL_STEP] + 1;     // plain cached load (one word for the whole grid: an L2-only load from every
+                                          // thread serialises on it); only the last CTA, once all have read it, bumps it
+        dst_off += (size_t)peers.rank * 2 * n * ld;
+        dst_bytes = keys_off + (step & 1u) * key_buf_bytes;
+    }
+    auto dst_rows = [&](int p) -> TOut* {
+        return peers.world > 0 ? reinterpret_cast<TOut*>(peers.base[p] + dst_bytes) : rows_local;
+    };
 
     float ss = 0.f;
     if constexpr (kVector) {
@@ -89,40 +110,54 @@ l2norm_kernel(const TIn* __restrict__ view0, const TIn* __restrict__ view1, int 
     }
     for (int o = lanes >> 1; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
     const float denom = fmaxf(sqrtf(ss), 1e-12f);   // clamp_min(eps) of F.normalize
-    if (!live) return;
-    if (sub == 0) inv_norm[r] = 1.0f / denom;
-
-    if constexpr (kVector) {
-        for (int c = sub * V; c < ld; c += lanes * V) {   // ld is a multiple of V on this path
-            float v[V];
-            if (c < d) {
-                Vec<TIn>::load(src + c, v);
+    if (live) {
+        if (sub == 0) inv_norm[r] = 1.0f / denom;
+        if constexpr (kVector) {
+            for (int c = sub * V; c < ld; c += lanes * V) {   // ld is a multiple of V on this path
+                float v[V];
+                if (c < d) {
+                    Vec<TIn>::load(src + c, v);
 #pragma unroll
-                for (int i = 0; i < V; ++i) v[i] = v[i] / denom;
-            } else {
+                    for (int i = 0; i < V; ++i) v[i] = v[i] / denom;
+                } else {
 #pragma unroll
-                for (int i = 0; i < V; ++i) v[i] = 0.f;
+                    for (int i = 0; i < V; ++i) v[i] = 0.f;
+                }
+                for (int p = 0; p < ndst; ++p) storev<V>(dst_rows(p) + dst_off + c, v);
             }
-            for (int p = 0; p < rows.count; ++p) storev<V>(static_cast<TOut*>(rows.base[p]) + dst_off + c, v);
+        } else {
+            for (int c = sub; c < ld; c += lanes) {
+                const float x = c < d ? to_f32(src[c]) / denom : 0.f;
+                for (int p = 0; p < ndst; ++p) store1(dst_rows(p) + dst_off + c, x);
+            }
         }
-    } else {
-        for (int c = sub; c < ld; c += lanes) {
-            const float x = c < d ? to_f32(src[c]) / denom : 0.f;
-            for (int p = 0; p < rows.count; ++p) store1(static_cast<TOut*>(rows.base[p]) + dst_off + c, x);
+    }
+    if (peers.world > 0) {
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();                                  // the CTA's stores (barrier above) before its ticket
+            if (atomicAdd(ctl + NTX_CTL_TICKET, 1u) == gridDim.x - 1) {
+                __threadfence();
+                ctl[NTX_CTL_TICKET] = 0;
+                ctl[NTX_CTL_STEP] = step;
+                *step_out = step;
+                ntx_raise_flags(peers, NTX_CTL_KFLAG, step);
+            }
         }
     }
 }
 
 template <typename TIn, typename TOut>
-int launch(const void* v0, const void* v1, int n, int d, const NtxPeers& rows, size_t row_offset, int ld,
-           float* inv_norm, cudaStream_t st) {
+int launch(const void* v0, const void* v1, int n, int d, void* rows, const NtxPeerOut& peers, size_t keys_off,
+           size_t key_buf_bytes, uint32_t* step_out, int ld, float* inv_norm, cudaStream_t st) {
     constexpr int V = Vec<TIn>::N;
     const bool vec = (d % V == 0) && (ld % V == 0) &&
                      (reinterpret_cast<uintptr_t>(v0) % 16 == 0) &&
                      (reinterpret_cast<uintptr_t>(v1) % 16 == 0) &&
                      [&] {
-                         for (int p = 0; p < rows.count; ++p)
-                             if (reinterpret_cast<uintptr_t>(rows.base[p]) % 16 != 0) return false;
+                         if (peers.world <= 0) return reinterpret_cast<uintptr_t>(rows) % 16 == 0;
+                         for (int p = 0; p < peers.world; ++p)
+                             if (reinterpret_cast<uintptr_t>(peers.base[p]) % 16 != 0) return false;
                          return true;
                      }();
     const int work = vec ? (ld + V - 1) / V : ld;
@@ -132,48 +167,68 @@ int launch(const void* v0, const void* v1, int n, int d, const NtxPeers& rows, s
     const int grid = (2 * n + rows_per_block - 1) / rows_per_block;
     if (vec)
         NTX_CUDA(ntx_launch_dep(l2norm_kernel<TIn, TOut, true>, grid, kWarpsPerBlock * 32, 0, st, (const TIn*)v0,
-                                (const TIn*)v1, n, d, rows, row_offset, ld, inv_norm, lanes));
+                                (const TIn*)v1, n, d, (TOut*)rows, peers, keys_off, key_buf_bytes, step_out, ld,
+                                inv_norm, lanes));
     else
         NTX_CUDA(ntx_launch_dep(l2norm_kernel<TIn, TOut, false>, grid, kWarpsPerBlock * 32, 0, st, (const TIn*)v0,
-                                (const TIn*)v1, n, d, rows, row_offset, ld, inv_norm, lanes));
+                                (const TIn*)v1, n, d, (TOut*)rows, peers, keys_off, key_buf_bytes, step_out, ld,
+                                inv_norm, lanes));
     return NTX_OK;
+}
+
+// Row weights of the backward (the upstream gradient of this rank's rows) into the weight area of every rank's
+// block, then wflag[rank] = step there.  w_stride == 0 (one upstream gradient for the whole rank): ONE value, at
+// weight[rank]; w_stride == 1: q_rows values at weight[rank * q_rows ..].  The last CTA raises the flags.
+__global__ void __launch_bounds__(1024)
+post_weights_kernel(const float* __restrict__ w, int w_stride, int w_bf16, int q_rows, NtxPeerOut peers,
+                    size_t weight_off, const uint32_t* __restrict__ step_ptr) {
+    ntx_dep_trigger();
+    ntx_dep_wait();
+    if (w_stride == 0) {
+        if (threadIdx.x < peers.world)
+            reinterpret_cast<float*>(peers.base[threadIdx.x] + weight_off)[peers.rank] = ntx_ld_weight(w, 0, w_bf16);
+    } else {
+        const int r = blockIdx.x * blockDim.x + threadIdx.x;
+        if (r < q_rows) {
+            const float v = ntx_ld_weight(w, r, w_bf16);
+            for (int p = 0; p < peers.world; ++p)
+                reinterpret_cast<float*>(peers.base[p] + weight_off)[(size_t)peers.rank * q_rows + r] = v;
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t* ctl = reinterpret_cast<uint32_t*>(peers.base[peers.rank]);
+        __threadfence();
+        if (gridDim.x == 1 || atomicAdd(ctl + NTX_CTL_POST_TICKET, 1u) == gridDim.x - 1) {
+            __threadfence();
+            ctl[NTX_CTL_POST_TICKET] = 0;
+            ntx_raise_flags(peers, NTX_CTL_WFLAG, *step_ptr);
+        }
+    }
 }
 
 }  // namespace
 
-// the same bytes to the same offset of every destination buffer (16-byte units; the tail in bytes)
-__global__ void __launch_bounds__(256) ntx_scatter_kernel(const uint8_t* __restrict__ src, size_t bytes, NtxPeers dst,
-                                                      size_t dst_offset) {
-    ntx_dep_trigger();
-    ntx_dep_wait();
-    const size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 16;
-    if (i + 16 <= bytes) {
-        const uint4 v = *reinterpret_cast<const uint4*>(src + i);
-        for (int p = 0; p < dst.count; ++p)
-            *reinterpret_cast<uint4*>(static_cast<uint8_t*>(dst.base[p]) + dst_offset + i) = v;
-    } else {
-        for (size_t b = i; b < bytes; ++b)
-            for (int p = 0; p < dst.count; ++p) static_cast<uint8_t*>(dst.base[p])[dst_offset + b] = src[b];
-    }
-}
-
-int ntx_scatter_launch(const void* src, size_t bytes, const NtxPeers& dst, size_t dst_offset, cudaStream_t st) {
-    const size_t units = (bytes + 15) / 16;
-    NTX_CUDA(ntx_launch_dep(ntx_scatter_kernel, (unsigned)((units + 255) / 256), 256, 0, st, (const uint8_t*)src, bytes,
-                            dst, dst_offset));
+int ntx_post_weights_launch(const void* w, int w_stride, int w_bf16, int q_rows, const NtxPeerOut& peers,
+                            size_t weight_off, const uint32_t* step, cudaStream_t st) {
+    const int threads = w_stride == 0 ? 32 : 256;
+    const int grid = w_stride == 0 ? 1 : (q_rows + threads - 1) / threads;
+    NTX_CUDA(ntx_launch_dep(post_weights_kernel, grid, threads, 0, st, (const float*)w, w_stride, w_bf16, q_rows, peers,
+                            weight_off, step));
     return NTX_OK;
 }
 
-int ntx_l2norm_launch(const void* v0, const void* v1, int n, int d, int in_dtype, const NtxPeers& rows,
-                      size_t row_offset, int ld, int rows_dtype, float* inv_norm, cudaStream_t st) {
+int ntx_l2norm_launch(const void* v0, const void* v1, int n, int d, int in_dtype, void* rows, const NtxPeerOut& peers,
+                      size_t keys_off, size_t key_buf_bytes, uint32_t* step_out, int ld, int rows_dtype,
+                      float* inv_norm, cudaStream_t st) {
     if (in_dtype == NTX_F32 && rows_dtype == NTX_F32)
-        return launch<float, float>(v0, v1, n, d, rows, row_offset, ld, inv_norm, st);
+        return launch<float, float>(v0, v1, n, d, rows, peers, keys_off, key_buf_bytes, step_out, ld, inv_norm, st);
     if (in_dtype == NTX_F32 && rows_dtype == NTX_BF16)
-        return launch<float, __nv_bfloat16>(v0, v1, n, d, rows, row_offset, ld, inv_norm, st);
+        return launch<float, __nv_bfloat16>(v0, v1, n, d, rows, peers, keys_off, key_buf_bytes, step_out, ld, inv_norm, st);
     if (in_dtype == NTX_BF16 && rows_dtype == NTX_BF16)
-        return launch<__nv_bfloat16, __nv_bfloat16>(v0, v1, n, d, rows, row_offset, ld, inv_norm, st);
+        return launch<__nv_bfloat16, __nv_bfloat16>(v0, v1, n, d, rows, peers, keys_off, key_buf_bytes, step_out, ld, inv_norm, st);
     if (in_dtype == NTX_BF16 && rows_dtype == NTX_F32)
-        return launch<__nv_bfloat16, float>(v0, v1, n, d, rows, row_offset, ld, inv_norm, st);
+        return launch<__nv_bfloat16, float>(v0, v1, n, d, rows, peers, keys_off, key_buf_bytes, step_out, ld, inv_norm, st);
     ntx_set_error("ntx_l2norm: unsupported dtype pair (%d -> %d)", in_dtype, rows_dtype);
     return NTX_E_ARG;
 }

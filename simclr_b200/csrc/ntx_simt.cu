@@ -68,12 +68,37 @@ __device__ __forceinline__ void similarity_tile(float (&acc)[4][4], float (*As)[
     }
 }
 
+// Peer exchange: one thread waits until every rank's data of this step has landed in this rank's block (the fp32
+// path is not the fast one: no overlap is attempted), then all threads pick the key buffer of the step.
+__device__ __forceinline__ size_t simt_gate(const NtxGate& gate, bool backward, size_t key_buf_elems) {
+    if (!gate.step) return 0;
+    __shared__ uint32_t step_sh;
+    if (threadIdx.x == 0) {
+        const uint32_t step = *gate.step;
+        for (int p = 0; p < gate.world; ++p) {
+            ntx_gate_wait(gate.ctl, NTX_CTL_KFLAG + p, step);
+            if (backward) {
+                ntx_gate_wait(gate.ctl, NTX_CTL_RFLAG + p, step);
+                ntx_gate_wait(gate.ctl, NTX_CTL_WFLAG + p, step);
+            }
+        }
+        step_sh = step;
+    }
+    __syncthreads();
+    return (step_sh & 1u) ? key_buf_elems : 0;
+}
+
 __global__ void __launch_bounds__(NT)
 simt_fwd_kernel(const float* __restrict__ q, const float* __restrict__ k, NtxDims dm, int key_tiles,
                 long long T, int rows_pad, float* __restrict__ partial,
-                unsigned int* __restrict__ done_counter) {
+                unsigned int* __restrict__ done_counter, NtxGate gate, size_t key_buf_elems) {
     __shared__ __align__(16) float As[BK][PITCH];
     __shared__ __align__(16) float Bs[BK][PITCH];
+    {
+        const size_t off = simt_gate(gate, false, key_buf_elems);
+        q += off;
+        k += off;
+    }
     const int G = gridDim.x, cta = blockIdx.x;
     const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
     const long long t_begin = ntx_chunk_begin(T, G, cta), t_end = ntx_chunk_begin(T, G, cta + 1);
@@ -120,9 +145,15 @@ simt_fwd_kernel(const float* __restrict__ q, const float* __restrict__ k, NtxDim
 
 __global__ void __launch_bounds__(NT)
 simt_bwd_kernel(const float* __restrict__ q, const float* __restrict__ k, NtxDims dm, int key_tiles,
-                long long T, int rows_pad, int d_pad, NtxWeights wt, float* __restrict__ partial) {
+                long long T, int rows_pad, int d_pad, NtxWeights wt, float* __restrict__ partial, NtxGate gate,
+                size_t key_buf_elems) {
     __shared__ __align__(16) float As[BK][PITCH];
     __shared__ __align__(16) float Bs[BK][PITCH];
+    {
+        const size_t off = simt_gate(gate, true, key_buf_elems);
+        q += off;
+        k += off;
+    }
     __shared__ __align__(16) float Ct[BN][PITCH];     // coefficient tile, [key][row]
     __shared__ __align__(16) float Ks[KC][BD];        // keys x features of this CTA's dZ slab
     const int G = gridDim.x, cta = blockIdx.x;
@@ -167,16 +198,17 @@ simt_bwd_kernel(const float* __restrict__ q, const float* __restrict__ k, NtxDim
         for (int i = 0; i < 4; ++i) {
             const int r = rb * BM + ty * 4 + i;
             alpha[i] = r < dm.q_rows
-                           ? __ldg(wt.w_q + (size_t)r * wt.w_stride) * wt.w_scale / __ldg(wt.rowsum_q + r)
+                           ? ntx_ld_weight(wt.w_q, (size_t)r * wt.w_stride, wt.w_bf16) * wt.w_scale / __ldg(wt.rowsum_q + r)
                            : 0.f;
             self[i] = ntx_self_col(r, dm.n_local, dm.rank);
         }
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const int c = kt * BN + tx * 4 + j;
-            beta[j] = c < dm.k_rows
-                          ? __ldg(wt.w_k + (size_t)c * wt.w_stride) * wt.w_scale / __ldg(wt.rowsum_k + c)
-                          : 0.f;
+            const size_t wi = ntx_key_weight_index(c, wt.w_stride, wt.w_chunk);
+            if (c >= dm.k_rows) beta[j] = 0.f;
+            else if (gate.step) beta[j] = ntx_ld_weight(wt.w_k, wi, wt.w_bf16, true) * wt.w_scale / ntx_ld_l2(wt.rowsum_k + c);   // written by peers
+            else beta[j] = ntx_ld_weight(wt.w_k, wi, wt.w_bf16) * wt.w_scale / __ldg(wt.rowsum_k + c);
         }
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -227,22 +259,26 @@ simt_bwd_kernel(const float* __restrict__ q, const float* __restrict__ k, NtxDim
 }  // namespace
 
 int ntx_simt_fwd_launch(const float* q, const float* k, const NtxDims& dm, const NtxPlan& plan,
-                        float* partial, unsigned int* counter, cudaStream_t st) {
+                        float* partial, unsigned int* counter, const NtxGate& gate, size_t key_buf_elems,
+                        cudaStream_t st) {
     const long long T = (long long)plan.row_blocks * plan.key_tiles;
     const int rows_pad = plan.row_blocks * plan.tile_rows;
     ntx_note_launch();
-    simt_fwd_kernel<<<plan.grid, NT, 0, st>>>(q, k, dm, plan.key_tiles, T, rows_pad, partial, counter);
+    simt_fwd_kernel<<<plan.grid, NT, 0, st>>>(q, k, dm, plan.key_tiles, T, rows_pad, partial, counter, gate,
+                                              key_buf_elems);
     NTX_CUDA(cudaGetLastError());
     return NTX_OK;
 }
 
 int ntx_simt_bwd_launch(const float* q, const float* k, const NtxDims& dm, const NtxPlan& plan,
-                        const NtxWeights& wt, float* partial, cudaStream_t st) {
+                        const NtxWeights& wt, float* partial, const NtxGate& gate, size_t key_buf_elems,
+                        cudaStream_t st) {
     const long long T = (long long)plan.row_blocks * plan.key_tiles;
     const int rows_pad = plan.row_blocks * plan.tile_rows;
     dim3 grid(plan.grid, (plan.d_pad + BD - 1) / BD);
     ntx_note_launch();
-    simt_bwd_kernel<<<grid, NT, 0, st>>>(q, k, dm, plan.key_tiles, T, rows_pad, plan.d_pad, wt, partial);
+    simt_bwd_kernel<<<grid, NT, 0, st>>>(q, k, dm, plan.key_tiles, T, rows_pad, plan.d_pad, wt, partial, gate,
+                                         key_buf_elems);
     NTX_CUDA(cudaGetLastError());
     return NTX_OK;
 }

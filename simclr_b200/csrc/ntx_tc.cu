@@ -165,11 +165,40 @@ __device__ __forceinline__ void issue_gemm1(uint32_t d_tmem, const uint8_t* q_sm
         }
 }
 
+__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+
+// Cross-rank gate of the TMA producer: before the first key tile that touches rank c's chunk of the key buffer
+// is loaded, wait until that rank's rows of this step have landed (kflag[c] >= step, written by its normalise
+// kernel after a system-scope fence), then order the async proxy (TMA) behind the acquire.
+struct KeyGate {
+    NtxGate g;
+    uint32_t step, ready;
+    int k_rows;
+    __device__ __forceinline__ void init(const NtxGate& gate, int k_rows_) {
+        g = gate;
+        k_rows = k_rows_;
+        ready = 0;
+        step = gate.step ? *gate.step : 0u;                  // written by the normalise kernel, earlier on the stream
+    }
+    __device__ __forceinline__ void wait_tile(int kt) {
+        if (!g.step) return;
+        const int c_lo = kt * 128 / g.chunk_rows, c_hi = min(kt * 128 + 127, k_rows - 1) / g.chunk_rows;
+        bool fresh = false;
+        for (int c = c_lo; c <= c_hi; ++c)
+            if (!((ready >> c) & 1u)) {
+                ntx_gate_wait(g.ctl, NTX_CTL_KFLAG + c, step);
+                ready |= 1u << c;
+                fresh = true;
+            }
+        if (fresh) fence_proxy_async_all();
+    }
+};
+
 // TMA producer shared by both kernels: the Q tile of each row block, then its key tiles
 template <int NDB, int NS, class Ctl>
 __device__ __forceinline__ void producer_loop(Ctl* ctl, uint8_t* q_smem, uint8_t* k_smem,
                                               const CUtensorMap* tmap_q, const CUtensorMap* tmap_k,
-                                              long long t_begin, int n_tiles, int key_tiles) {
+                                              long long t_begin, int n_tiles, int key_tiles, KeyGate& gate) {
     constexpr uint32_t kTileBytes = NDB * kBlkBytes;
     int cur_rb = -1, seg = 0;
     for (int i = 0; i < n_tiles; ++i) {
@@ -185,6 +214,7 @@ __device__ __forceinline__ void producer_loop(Ctl* ctl, uint8_t* q_smem, uint8_t
             ++seg;
         }
         const int s = i % NS;
+        gate.wait_tile(kt);
         mbar_wait(&ctl->k_empty[s], ((i / NS) & 1) ^ 1);
         mbar_expect_tx(&ctl->k_full[s], kTileBytes);
 #pragma unroll
@@ -207,8 +237,9 @@ template <int NS> struct FwdCtl {
 template <int NDB>
 __global__ void __launch_bounds__(kFwdThreads, 1)
 tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
+              const __grid_constant__ CUtensorMap tmap_q1, const __grid_constant__ CUtensorMap tmap_k1,
               NtxDims dm, int key_tiles, long long T, int rows_pad, float* __restrict__ partial,
-              unsigned int* __restrict__ done_counter) {
+              unsigned int* __restrict__ done_counter, NtxGate gate) {
     constexpr int NS = FwdCfg<NDB>::NS;
     constexpr uint32_t kTileBytes = NDB * kBlkBytes;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -231,7 +262,10 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         fence_barrier_init();
     }
     if (warp == kMmaWarp) tmem_alloc(&ctl->tmem_base, kTmemCols);
-    if (warp == kProducerWarp && lane == 0) { tma_prefetch_desc(&tmap_q); tma_prefetch_desc(&tmap_k); }
+    if (warp == kProducerWarp && lane == 0) {
+        tma_prefetch_desc(&tmap_q); tma_prefetch_desc(&tmap_k);
+        tma_prefetch_desc(&tmap_q1); tma_prefetch_desc(&tmap_k1);
+    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -249,8 +283,13 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     if (threadIdx.x == 0 && cta == 0) *done_counter = 0;    // ticket of the finalize kernel
 
     if (warp == kProducerWarp) {
-        if (elect_one())
-            producer_loop<NDB, NS>(ctl, q_smem, k_smem, &tmap_q, &tmap_k, t_begin, n_tiles, key_tiles);
+        if (elect_one()) {
+            KeyGate kg;
+            kg.init(gate, dm.k_rows);
+            const bool alt = kg.step & 1u;                   // key buffer of this step (peer exchange)
+            producer_loop<NDB, NS>(ctl, q_smem, k_smem, alt ? &tmap_q1 : &tmap_q, alt ? &tmap_k1 : &tmap_k, t_begin,
+                                   n_tiles, key_tiles, kg);
+        }
     } else if (warp >= kMmaWarp) {
         // Two issuing warps take alternate tiles: tcgen05.mma issue blocks while the tensor pipe's
         // short queue is full, so one warp's barrier waits (~150-200 cycles each, even when the
@@ -750,6 +789,8 @@ struct BwdWeights {
     const float* w_k;
     int w_stride;       // 0: one weight for every row, 1: one per row
     float w_scale;
+    int w_chunk;        // > 0: one weight per rank, key c takes w_k[c / w_chunk]
+    int w_bf16;         // weights are bf16 values
 };
 
 // 32 similarity values of one row -> 32 coefficients, packed bf16x2
@@ -784,8 +825,9 @@ __device__ __forceinline__ void coef_chunk(const uint32_t (&v)[32], uint32_t (&p
 template <int NDB>
 __global__ void __launch_bounds__(BwdCfg<NDB>::kThreads, 1)
 tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
+              const __grid_constant__ CUtensorMap tmap_q1, const __grid_constant__ CUtensorMap tmap_k1,
               NtxDims dm, int key_tiles, long long T, int rows_pad, BwdWeights wt,
-              float* __restrict__ partial) {
+              float* __restrict__ partial, NtxGate gate) {
     using Cfg = BwdCfg<NDB>;
 #ifdef NTX_TIMELINE
     const long long t_entry = clock64();
@@ -819,7 +861,10 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         fence_barrier_init();
     }
     if (warp == kMmaWarp) tmem_alloc(&ctl->tmem_base, kTmemCols);
-    if (warp == kProducerWarp && lane == 0) { tma_prefetch_desc(&tmap_q); tma_prefetch_desc(&tmap_k); }
+    if (warp == kProducerWarp && lane == 0) {
+        tma_prefetch_desc(&tmap_q); tma_prefetch_desc(&tmap_k);
+        tma_prefetch_desc(&tmap_q1); tma_prefetch_desc(&tmap_k1);
+    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -836,8 +881,13 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     ntx_dep_wait();
 
     if (warp == kProducerWarp) {
-        if (elect_one())
-            producer_loop<NDB, NS>(ctl, q_smem, k_smem, &tmap_q, &tmap_k, t_begin, n_tiles, key_tiles);
+        if (elect_one()) {
+            KeyGate kg;
+            kg.init(gate, dm.k_rows);
+            const bool alt = kg.step & 1u;                   // key buffer the forward of this step used
+            producer_loop<NDB, NS>(ctl, q_smem, k_smem, alt ? &tmap_q1 : &tmap_q, alt ? &tmap_k1 : &tmap_k, t_begin,
+                                   n_tiles, key_tiles, kg);
+        }
     } else if (warp == kMmaWarp) {
         // GEMM1 issuer: S(i) = Q . K(i)^T as soon as the key tile has landed and S/C buffer i % NWG
         // is free again.  Unrolled by NS (a multiple of NWG): stage / buffer indices are compile-time
@@ -947,12 +997,36 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
 
         // w_c and R_c of one key are fetched a whole tile ahead (raw: the division waits until the
         // values are consumed, so the load latency stays off the critical path)
+        // With a peer exchange the values of rank c's keys are stored into this rank's block by rank c: its forward
+        // finalize (row sums, rflag) and the start of its backward (weights, wflag) -- wait for both flags once.
         float w_next = 0.f, r_next = 1.f;
+        const uint32_t gate_step = gate.step ? *gate.step : 0u;
+        uint32_t gate_ready = 0;
         auto fetch_beta = [&](int key_tile) {
             const int c = key_tile * 128 + tid_g;
             const bool ok = c < dm.k_rows;
-            w_next = ok ? __ldg(wt.w_k + (size_t)c * wt.w_stride) : 0.f;
-            r_next = ok ? __ldg(wt.rowsum_k + c) : 1.f;
+            if (gate.step) {
+                // one poller per warp (every thread polling the same word serialises on its L2 slice); the warp
+                // barrier passes the acquire on to the other lanes
+                const int c0 = key_tile * 128 + (warp & 3) * 32;
+                if (c0 < dm.k_rows) {
+                    const int ch_lo = c0 / gate.chunk_rows, ch_hi = min(c0 + 31, dm.k_rows - 1) / gate.chunk_rows;
+                    for (int ch = ch_lo; ch <= ch_hi; ++ch)
+                        if (!((gate_ready >> ch) & 1u)) {
+                            if (lane == 0) {
+                                ntx_gate_wait(gate.ctl, NTX_CTL_RFLAG + ch, gate_step);
+                                ntx_gate_wait(gate.ctl, NTX_CTL_WFLAG + ch, gate_step);
+                            }
+                            gate_ready |= 1u << ch;
+                            __syncwarp();
+                        }
+                }
+                w_next = ok ? ntx_ld_weight(wt.w_k, ntx_key_weight_index(c, wt.w_stride, wt.w_chunk), wt.w_bf16, true) : 0.f;
+                r_next = ok ? ntx_ld_l2(wt.rowsum_k + c) : 1.f;
+            } else {
+                w_next = ok ? ntx_ld_weight(wt.w_k, ntx_key_weight_index(c, wt.w_stride, wt.w_chunk), wt.w_bf16) : 0.f;
+                r_next = ok ? __ldg(wt.rowsum_k + c) : 1.f;
+            }
         };
         int rb = (int)(t_begin / key_tiles), kt = (int)(t_begin % key_tiles);
         int seg = 0, own = 0, turn = 0;
@@ -963,7 +1037,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
             if (new_seg) {
                 const int row = rb * 128 + row_in_tile;
                 row_ok = row < dm.q_rows;
-                alpha = row_ok ? __ldg(wt.w_q + (size_t)row * wt.w_stride) * wt.w_scale / __ldg(wt.rowsum_q + row)
+                alpha = row_ok ? ntx_ld_weight(wt.w_q, (size_t)row * wt.w_stride, wt.w_bf16) * wt.w_scale / __ldg(wt.rowsum_q + row)
                                : 0.f;
                 new_seg = false;
             }
@@ -1048,10 +1122,25 @@ int get_encode_fn(EncodeTiledFn* out) {
 }
 
 // [rows x ld] bf16 row buffer -> tiles of 128 rows x 64 features, 128B swizzle, zero OOB fill
+// cuTensorMapEncodeTiled is a DRIVER call: it needs a context bound to the calling thread.  Runtime calls bind the
+// primary context lazily, but a thread whose first CUDA work is this library (PyTorch's autograd thread, when the
+// backward is its first CUDA call) has none yet: bind it once per (thread, device).
+int bind_context() {
+    thread_local int bound_dev = -1;
+    int dev = 0;
+    NTX_CUDA(cudaGetDevice(&dev));
+    if (dev != bound_dev) {
+        NTX_CUDA(cudaFree(nullptr));
+        bound_dev = dev;
+    }
+    return NTX_OK;
+}
+
 int make_rows_tmap(CUtensorMap* m, const __nv_bfloat16* base, int rows, int ld, int box_rows = 128) {
     EncodeTiledFn enc;
     int rc = get_encode_fn(&enc);
     if (rc) return rc;
+    if ((rc = bind_context())) return rc;
     const cuuint64_t dims[2] = {(cuuint64_t)ld, (cuuint64_t)rows};
     const cuuint64_t strides[1] = {(cuuint64_t)ld * sizeof(__nv_bfloat16)};
     const cuuint32_t box[2] = {64, (cuuint32_t)box_rows};
@@ -1073,25 +1162,45 @@ template <int NDB> size_t bwd_smem_bytes() {
     return (size_t)(1 + BwdCfg<NDB>::NS) * NDB * kBlkBytes + sizeof(BwdCtl<BwdCfg<NDB>::NS, BwdCfg<NDB>::NWG>);
 }
 
-template <int NDB>
-int launch_fwd(const CUtensorMap& mq, const CUtensorMap& mk, const NtxDims& dm, const NtxPlan& plan,
-               float* partial, unsigned int* counter, cudaStream_t st) {
-    const size_t smem = fwd_smem_bytes<NDB>();
-    NTX_SMEM_OPT_IN(tc_fwd_kernel<NDB>, smem);
-    const long long T = (long long)plan.row_blocks * plan.key_tiles;
-    NTX_CUDA(ntx_launch_dep(tc_fwd_kernel<NDB>, plan.grid, kFwdThreads, smem, st, mq, mk, dm, plan.key_tiles, T,
-                            plan.row_blocks * plan.tile_rows, partial, counter));
+// the maps of a launch: rows and keys in key buffer 0 and, with a peer exchange, in key buffer 1
+struct RowMaps {
+    CUtensorMap q[2], k[2];
+};
+int make_row_maps(RowMaps* m, const __nv_bfloat16* q, const __nv_bfloat16* k, const NtxDims& dm, const NtxGate& gate,
+                  size_t key_buf_elems) {
+    int rc;
+    if ((rc = make_rows_tmap(&m->q[0], q, dm.q_rows, dm.ld)) || (rc = make_rows_tmap(&m->k[0], k, dm.k_rows, dm.ld)))
+        return rc;
+    if (gate.step) {
+        if ((rc = make_rows_tmap(&m->q[1], q + key_buf_elems, dm.q_rows, dm.ld)) ||
+            (rc = make_rows_tmap(&m->k[1], k + key_buf_elems, dm.k_rows, dm.ld)))
+            return rc;
+    } else {
+        m->q[1] = m->q[0];
+        m->k[1] = m->k[0];
+    }
     return NTX_OK;
 }
 
 template <int NDB>
-int launch_bwd(const CUtensorMap& mq, const CUtensorMap& mk, const NtxDims& dm, const NtxPlan& plan,
-               const BwdWeights& wt, float* partial, cudaStream_t st) {
+int launch_fwd(const RowMaps& m, const NtxDims& dm, const NtxPlan& plan, float* partial, unsigned int* counter,
+               const NtxGate& gate, cudaStream_t st) {
+    const size_t smem = fwd_smem_bytes<NDB>();
+    NTX_SMEM_OPT_IN(tc_fwd_kernel<NDB>, smem);
+    const long long T = (long long)plan.row_blocks * plan.key_tiles;
+    NTX_CUDA(ntx_launch_dep(tc_fwd_kernel<NDB>, plan.grid, kFwdThreads, smem, st, m.q[0], m.k[0], m.q[1], m.k[1], dm,
+                            plan.key_tiles, T, plan.row_blocks * plan.tile_rows, partial, counter, gate));
+    return NTX_OK;
+}
+
+template <int NDB>
+int launch_bwd(const RowMaps& m, const NtxDims& dm, const NtxPlan& plan, const BwdWeights& wt, float* partial,
+               const NtxGate& gate, cudaStream_t st) {
     const size_t smem = bwd_smem_bytes<NDB>();
     NTX_SMEM_OPT_IN(tc_bwd_kernel<NDB>, smem);
     const long long T = (long long)plan.row_blocks * plan.key_tiles;
-    NTX_CUDA(ntx_launch_dep(tc_bwd_kernel<NDB>, plan.grid, BwdCfg<NDB>::kThreads, smem, st, mq, mk, dm,
-                            plan.key_tiles, T, plan.row_blocks * plan.tile_rows, wt, partial));
+    NTX_CUDA(ntx_launch_dep(tc_bwd_kernel<NDB>, plan.grid, BwdCfg<NDB>::kThreads, smem, st, m.q[0], m.k[0], m.q[1],
+                            m.k[1], dm, plan.key_tiles, T, plan.row_blocks * plan.tile_rows, wt, partial, gate));
     return NTX_OK;
 }
 
@@ -1109,15 +1218,15 @@ extern "C" int ntx_debug_timers(long long* host_out) {   // 148 x 16 cycle count
 #endif
 
 int ntx_tc_fwd_launch(const __nv_bfloat16* q, const __nv_bfloat16* k, const NtxDims& dm,
-                      const NtxPlan& plan, float* partial, unsigned int* counter, cudaStream_t st) {
-    CUtensorMap mq, mk;
-    int rc;
-    if ((rc = make_rows_tmap(&mq, q, dm.q_rows, dm.ld)) || (rc = make_rows_tmap(&mk, k, dm.k_rows, dm.ld)))
-        return rc;
+                      const NtxPlan& plan, float* partial, unsigned int* counter, const NtxGate& gate,
+                      size_t key_buf_elems, cudaStream_t st) {
+    RowMaps m;
+    int rc = make_row_maps(&m, q, k, dm, gate, key_buf_elems);
+    if (rc) return rc;
     switch (plan.d_pad) {
-        case 64: return launch_fwd<1>(mq, mk, dm, plan, partial, counter, st);
-        case 128: return launch_fwd<2>(mq, mk, dm, plan, partial, counter, st);
-        case 256: return launch_fwd<4>(mq, mk, dm, plan, partial, counter, st);
+        case 64: return launch_fwd<1>(m, dm, plan, partial, counter, gate, st);
+        case 128: return launch_fwd<2>(m, dm, plan, partial, counter, gate, st);
+        case 256: return launch_fwd<4>(m, dm, plan, partial, counter, gate, st);
     }
     ntx_set_error("tensor-core forward: padded feature dim %d not built", plan.d_pad);
     return NTX_E_UNSUPPORTED;
@@ -1149,16 +1258,16 @@ int ntx_tc_fwd_sym_launch(const __nv_bfloat16* rows, const NtxDims& dm, const Nt
 }
 
 int ntx_tc_bwd_launch(const __nv_bfloat16* q, const __nv_bfloat16* k, const NtxDims& dm,
-                      const NtxPlan& plan, const NtxWeights& w, float* partial, cudaStream_t st) {
-    CUtensorMap mq, mk;
-    int rc;
-    if ((rc = make_rows_tmap(&mq, q, dm.q_rows, dm.ld)) || (rc = make_rows_tmap(&mk, k, dm.k_rows, dm.ld)))
-        return rc;
-    BwdWeights wt{w.rowsum_q, w.rowsum_k, w.w_q, w.w_k, w.w_stride, w.w_scale};
+                      const NtxPlan& plan, const NtxWeights& w, float* partial, const NtxGate& gate,
+                      size_t key_buf_elems, cudaStream_t st) {
+    RowMaps m;
+    int rc = make_row_maps(&m, q, k, dm, gate, key_buf_elems);
+    if (rc) return rc;
+    BwdWeights wt{w.rowsum_q, w.rowsum_k, w.w_q, w.w_k, w.w_stride, w.w_scale, w.w_chunk, w.w_bf16};
     switch (plan.d_pad) {
-        case 64: return launch_bwd<1>(mq, mk, dm, plan, wt, partial, st);
-        case 128: return launch_bwd<2>(mq, mk, dm, plan, wt, partial, st);
-        case 256: return launch_bwd<4>(mq, mk, dm, plan, wt, partial, st);
+        case 64: return launch_bwd<1>(m, dm, plan, wt, partial, gate, st);
+        case 128: return launch_bwd<2>(m, dm, plan, wt, partial, gate, st);
+        case 256: return launch_bwd<4>(m, dm, plan, wt, partial, gate, st);
     }
     ntx_set_error("tensor-core backward: padded feature dim %d not built", plan.d_pad);
     return NTX_E_UNSUPPORTED;

@@ -80,29 +80,30 @@ class NTXentFunction(torch.autograd.Function):
         stats = torch.empty((4, q_rows), dtype=torch.float32, device=dev)   # inv_norm, rowsum, pos, row loss
         loss_sum = torch.empty(2, dtype=torch.float32, device=dev)
         inv_norm, rowsum, pos_logit, row_loss = stats[0], stats[1], stats[2], stats[3]
-        exchange, key_slot = None, 0
+        exchange = None
+        ws = _workspace(dev, ws_bytes)
         if world > 1 and peer:
-            # the normalise kernel stores straight into every rank's key buffer (NVLink peer memory)
-            exchange = peer_exchange.exchange_for(group, q_rows, ld, rows_dtype, dev)
-            needs_grad = any(ctx.needs_input_grad[:2])
-            keys, key_slot = exchange.gather_rows(be, view0, view1, inv_norm, hold=needs_grad)
-            q = keys[rank * q_rows:(rank + 1) * q_rows]
-        elif world > 1:
-            rows = torch.empty((q_rows, ld), dtype=rows_dtype, device=dev)
-            be.l2norm(view0, view1, rows, inv_norm)
-            keys = torch.empty((world * q_rows, ld), dtype=rows_dtype, device=dev)
-            dist.all_gather_into_tensor(keys, rows, group=group)          # rank-major key buffer
-            q = keys[rank * q_rows:(rank + 1) * q_rows]
+            # kernels store rows, row sums and weights straight into every rank's exchange block (NVLink peer
+            # memory) and order them with flag words: no collective call, no barrier kernel
+            exchange = peer_exchange.exchange_for(be, group, q_rows, ld, rows_dtype, dev)
+            exchange.begin_forward(any(ctx.needs_input_grad[:2]))
+            keys = torch.empty(1, dtype=torch.int32, device=dev)           # the step number, set on the device
+            be.peer_l2norm(view0, view1, exchange.blocks, ld, rows_dtype, inv_norm, keys)
+            be.peer_fwd(exchange.blocks, n, d, ld, rows_dtype, temperature, keys, rowsum, pos_logit, row_loss,
+                        loss_sum, ws)
         else:
             rows = torch.empty((q_rows, ld), dtype=rows_dtype, device=dev)
             be.l2norm(view0, view1, rows, inv_norm)
-            keys = q = rows
-        layout = (n, world, rank)
-        ws = _workspace(dev, ws_bytes)
-        be.fwd(q, keys, d, layout, temperature, rowsum, pos_logit, row_loss, loss_sum, ws)
+            if world > 1:
+                keys = torch.empty((world * q_rows, ld), dtype=rows_dtype, device=dev)
+                dist.all_gather_into_tensor(keys, rows, group=group)      # rank-major key buffer
+                q = keys[rank * q_rows:(rank + 1) * q_rows]
+            else:
+                keys = q = rows
+            be.fwd(q, keys, d, (n, world, rank), temperature, rowsum, pos_logit, row_loss, loss_sum, ws)
 
         ctx.save_for_backward(view0, view1, keys, stats)
-        ctx.meta = (temperature, reduction, group, world, rank, d, exchange, key_slot)
+        ctx.meta = (temperature, reduction, group, world, rank, d, exchange, rows_dtype)
         if reduction == "none":
             out = row_loss.view(2, n).clone()                              # loss.py:55-58
         elif reduction == "sum":
@@ -115,39 +116,44 @@ class NTXentFunction(torch.autograd.Function):
     def backward(ctx, grad_out):
         be = _backend
         view0, view1, keys, stats = ctx.saved_tensors
-        temperature, reduction, group, world, rank, d, exchange, key_slot = ctx.meta
+        temperature, reduction, group, world, rank, d, exchange, rows_dtype = ctx.meta
         n = view0.shape[0]
         q_rows = 2 * n
         dev = view0.device
         inv_norm, rowsum = stats[0], stats[1]
-        g = grad_out.detach().to(torch.float32).contiguous()
+        g = grad_out.detach().contiguous()            # read by the kernels in its own dtype (fp32 or bf16)
+        if g.dtype not in (torch.float32, torch.bfloat16):
+            g = g.to(torch.float32)
         # row weights w_r of  sum_r w_r * row_loss_r : one upstream gradient (mean / sum) or one per row (none)
         w_stride = 1 if reduction == "none" else 0
         w_scale = 1.0 / q_rows if reduction == "mean" else 1.0
         w_q = g.view(-1)
+        dview0 = torch.empty_like(view0)
+        dview1 = torch.empty_like(view1)
+        ld, ws_bytes = _shape_info(be, q_rows, world * q_rows, d, rows_dtype, dev)
+        ws = _workspace(dev, ws_bytes)
+        if exchange is not None:
+            # `keys` is the step number here: the library sends this rank's row weights to every rank and reads
+            # every key's row sum and weight from its own exchange block
+            be.peer_post_weights(exchange.blocks, n, ld, rows_dtype, keys, w_q, w_stride)
+            be.peer_bwd(exchange.blocks, n, d, ld, rows_dtype, temperature, keys, rowsum, w_stride, w_scale, view0,
+                        view1, inv_norm, dview0, dview1, ws)
+            exchange.end_backward()
+            return dview0, dview1, None, None, None, None, None, None, None
         if world > 1:
             # one collective for both per-key vectors: every rank contributes [rowsum ; row weights]
-            mine = torch.stack((rowsum, w_q.expand(q_rows)))                       # (2, q_rows)
-            if exchange is not None:
-                both = exchange.gather_vectors(be, mine)                           # peer stores + barrier
-            else:
-                both = torch.empty((world * 2, q_rows), dtype=torch.float32, device=dev)
-                dist.all_gather_into_tensor(both, mine, group=group)
-                both = both.view(world, 2, q_rows)
+            mine = torch.stack((rowsum, w_q.to(torch.float32).expand(q_rows)))     # (2, q_rows)
+            both = torch.empty((world * 2, q_rows), dtype=torch.float32, device=dev)
+            dist.all_gather_into_tensor(both, mine, group=group)
+            both = both.view(world, 2, q_rows)
             rowsum_k = both[:, 0, :].reshape(-1)                                   # rank-major, like the keys
             w_k = both[:, 1, :].reshape(-1)
             w_q, w_stride = w_k[rank * q_rows:(rank + 1) * q_rows], 1              # ranks may hold different upstream gradients
             q = keys[rank * q_rows:(rank + 1) * q_rows]
         else:
             rowsum_k, w_k, q = rowsum, w_q, keys
-        dview0 = torch.empty_like(view0)
-        dview1 = torch.empty_like(view1)
-        _, ws_bytes = _shape_info(be, q_rows, keys.shape[0], d, keys.dtype, dev)
-        ws = _workspace(dev, ws_bytes)
         be.bwd(q, keys, d, (n, world, rank), temperature, rowsum, rowsum_k, w_q, w_k, w_stride, w_scale,
                view0, view1, inv_norm, dview0, dview1, ws)
-        if exchange is not None:
-            exchange.release(key_slot)          # the key buffer may be written again two forward calls from now
         return dview0, dview1, None, None, None, None, None, None, None
 
 
@@ -188,7 +194,9 @@ class NTXentHiddenFunction(torch.autograd.Function):
         temperature, reduction, d, ws_bytes = ctx.meta
         n = h0.shape[0]
         q_rows = 2 * n
-        g = grad_out.detach().to(torch.float32).contiguous().view(-1)
+        g = grad_out.detach().contiguous().view(-1)
+        if g.dtype not in (torch.float32, torch.bfloat16):
+            g = g.to(torch.float32)
         w_stride = 1 if reduction == "none" else 0
         w_scale = 1.0 / q_rows if reduction == "mean" else 1.0
         dz = torch.empty((q_rows, d), dtype=torch.bfloat16, device=h0.device)

@@ -85,7 +85,7 @@ def test_argument_errors_are_reported_without_a_device():
     # rows must be 2 * n_local
     rc = lib.ntx_fwd(16, 16, 10, 10, 8, 8, 0, ctypes.byref(lay), 0.5, 16, 16, 16, 16, 16, 64, None)
     assert rc == -1 and b"q_rows" in lib.ntx_last_error()
-    rc = lib.ntx_bwd(16, 16, 8, 8, 8, 8, 0, ctypes.byref(lay), 0.5, 16, 16, 16, 16, 3, 1.0, 16, 16, 0, 16, 16,
+    rc = lib.ntx_bwd(16, 16, 8, 8, 8, 8, 0, ctypes.byref(lay), 0.5, 16, 16, 16, 16, 3, 0, 1.0, 16, 16, 0, 16, 16,
                      16, 16, 64, None)
     assert rc == -1 and b"w_stride" in lib.ntx_last_error()
     p = _cabi.NtxPlan()
@@ -95,21 +95,27 @@ def test_argument_errors_are_reported_without_a_device():
 
 
 def test_newer_entry_points_validate_before_touching_the_device():
-    """Peer scatter / projection / rows-backward: argument errors come back as NTX_E_ARG with a message and no
+    """Peer exchange / projection / rows-backward: argument errors come back as NTX_E_ARG with a message and no
     CUDA call is made (fake, aligned, non-NULL addresses)."""
     lib = _cabi.load()
-    vp = ctypes.c_void_p
-    two = (vp * 2)(4096, 8192)
-    nine = (vp * 9)(*[4096 * (i + 1) for i in range(9)])
-    holed = (vp * 2)(4096, None)
-    # peer tables: at most 8 ranks (one node), no NULL entries, rank inside the world
-    assert lib.ntx_scatter_peers(4096, 64, nine, 9, 0, None) == -1 and b"world=9" in lib.ntx_last_error()
-    assert lib.ntx_scatter_peers(4096, 64, holed, 2, 0, None) == -1 and b"NULL" in lib.ntx_last_error()
-    assert lib.ntx_scatter_peers(4100, 64, two, 2, 0, None) == -1 and b"aligned" in lib.ntx_last_error()
-    assert lib.ntx_scatter_peers(4096, 64, two, 2, 8, None) == -1 and b"aligned" in lib.ntx_last_error()
-    assert lib.ntx_l2norm_peers(4096, 4096, 4, 8, 0, two, 2, 2, 8, 0, 4096, None) == -1
-    assert b"rank 2" in lib.ntx_last_error()
-    assert lib.ntx_l2norm_peers(4096, 4096, 4, 8, 0, nine, 9, 0, 8, 0, 4096, None) == -1
+    # peer exchange: at most 8 ranks (one node), no NULL / misaligned block, rank inside the world, a step word
+    be = _cabi.Backend()
+    assert be.peer_block_bytes(2048, 128, torch.bfloat16, 8) >= 256 + 2 * 8 * 2048 * 4 + 2 * 8 * 2048 * 128 * 2
+    assert be.peer_block_bytes(2048, 128, torch.bfloat16, 9) == 0
+    bad_rank = be.peer_blocks([4096, 8192], 2)
+    assert lib.ntx_peer_l2norm(4096, 4096, 4, 8, 0, ctypes.byref(bad_rank), 8, 0, 4096, 4096, None) == -1
+    assert b"rank=2" in lib.ntx_last_error()
+    holed = be.peer_blocks([4096, 0], 0)
+    assert lib.ntx_peer_fwd(ctypes.byref(holed), 4, 8, 8, 0, 0.5, 4096, 4096, 4096, 4096, 4096, 4096, 1 << 20, None) == -1
+    assert b"rank 1" in lib.ntx_last_error()
+    skew = be.peer_blocks([4096, 8192 + 16], 0)
+    assert lib.ntx_peer_fwd(ctypes.byref(skew), 4, 8, 8, 0, 0.5, 4096, 4096, 4096, 4096, 4096, 4096, 1 << 20, None) == -1
+    assert b"aligned" in lib.ntx_last_error()
+    good = be.peer_blocks([4096, 8192], 0)
+    assert lib.ntx_peer_fwd(ctypes.byref(good), 4, 8, 8, 0, 0.5, None, 4096, 4096, 4096, 4096, 4096, 1 << 20, None) == -1
+    assert b"step" in lib.ntx_last_error()
+    assert lib.ntx_peer_post_weights(ctypes.byref(good), 4, 8, 0, 4096, 4096, 2, 0, None) == -1
+    assert b"w_stride" in lib.ntx_last_error()
     # projection: hidden size in whole TMA blocks, row pitch of bf16 rows, d <= 256
     assert lib.ntx_project_l2norm(4096, 4096, 4096, 4, 100, 64, 4096, 64, 4096, None) == -1
     assert b"multiple of 64" in lib.ntx_last_error()
@@ -119,6 +125,6 @@ def test_newer_entry_points_validate_before_touching_the_device():
     assert lib.ntx_project_l2norm(4096, None, 4096, 4, 128, 64, 4096, 64, 4096, None) == -1
     # rows-backward: output required (odd sizes go to the unaligned finalize: no size restriction)
     lay = _cabi.NtxLayout(4, 1, 0)
-    rc = lib.ntx_bwd_rows(4096, 4096, 8, 8, 8, 64, 1, ctypes.byref(lay), 0.5, 4096, 4096, 4096, 4096, 0, 1.0, 4096,
+    rc = lib.ntx_bwd_rows(4096, 4096, 8, 8, 8, 64, 1, ctypes.byref(lay), 0.5, 4096, 4096, 4096, 4096, 0, 0, 1.0, 4096,
                           None, 4096, 64, None)
     assert rc == -1 and b"NULL" in lib.ntx_last_error()

@@ -331,6 +331,45 @@ def test_rank7_of_8_at_config4_shard_size(dev):
     assert np.abs(got - ref["dz"]).max() / np.abs(ref["dz"]).max() < BF16_TOL
 
 
+def test_first_cuda_call_of_a_thread_may_be_the_library(dev):
+    """PyTorch runs backward on its own thread; when the library's call is that thread's first CUDA work no
+    context is bound to it yet, and building a TMA descriptor is a driver call.  A fresh host thread makes
+    forward and backward through the C ABI and must get the main thread's results."""
+    import threading
+    from simclr_b200 import _cabi
+    be = _cabi.Backend()
+    n, d, tau = 300, 128, 0.5
+    g = torch.Generator().manual_seed(3)
+    a, b = torch.randn(n, d, generator=g).to(dev), torch.randn(n, d, generator=g).to(dev)
+    ld = be.row_pitch(d, torch.bfloat16)
+    rows = torch.empty(2 * n, ld, dtype=torch.bfloat16, device=dev)
+    st = torch.empty(4, 2 * n, device=dev)
+    ls = torch.empty(2, device=dev)
+    plan = be.plan(2 * n, 2 * n, d, torch.bfloat16)
+    ws = torch.empty(max(plan.fwd_ws_bytes, plan.bwd_ws_bytes), dtype=torch.uint8, device=dev)
+    one = torch.ones(1, device=dev)
+    outs = [(torch.empty_like(a), torch.empty_like(b)) for _ in range(2)]
+    be.l2norm(a, b, rows, st[0])
+    torch.cuda.synchronize()
+    errors = []
+
+    def work(out):
+        try:
+            be.fwd(rows, rows, d, (n, 1, 0), tau, st[1], st[2], st[3], ls, ws)
+            be.bwd(rows, rows, d, (n, 1, 0), tau, st[1], st[1], one, one, 0, 0.5 / n, a, b, st[0], out[0], out[1], ws)
+        except Exception as e:  # noqa: BLE001
+            errors.append(e)
+
+    t = threading.Thread(target=work, args=(outs[0],))
+    t.start()
+    t.join()
+    assert not errors, errors
+    torch.cuda.synchronize()
+    work(outs[1])
+    torch.cuda.synchronize()
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+
+
 def test_training_step_call_pattern(dev):
     """main.py:104-122 call pattern: model(view0), model(view1), loss, backward, SGD step.  Every step
     the reference-form oracle runs on the same projections z0, z1 as the checker: the loss value and
@@ -400,38 +439,74 @@ def test_symmetric_forward_matches_full_tile_forward_and_oracle(n, d, tau, dev):
     assert abs(sym_sum[1] - ref["loss"].mean()) < BF16_TOL * abs(ref["loss"].mean())
 
 
-@pytest.mark.parametrize("in_dtype,rows_dtype", [(torch.float32, torch.float32), (torch.bfloat16, torch.bfloat16)])
-def test_peer_entry_points_with_local_buffers(in_dtype, rows_dtype, dev):
-    """ntx_l2norm_peers / ntx_scatter_peers through the C ABI, with two buffers of this one GPU standing in
-    for two ranks' key buffers: both receive the rows ntx_l2norm writes, at the rank's row offset, and
-    nothing else is touched; the scatter lands the same bytes at the same offset of both buffers."""
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, FP32_TOL), (torch.bfloat16, BF16_TOL)])
+@pytest.mark.parametrize("world", [2, 4])
+def test_peer_exchange_entry_points_on_one_gpu(world, dtype, tol, dev):
+    """ntx_peer_l2norm / ntx_peer_fwd / ntx_peer_bwd through the C ABI with `world` exchange blocks of this one GPU
+    standing in for the ranks' blocks: every rank's kernels run stage by stage on one stream (so every flag a kernel
+    polls is already up), three steps in a row with fresh inputs each (the key buffers alternate, flags and step
+    counts advance).  Result of every step = the reference on the concatenated batch."""
+    from conftest import GOLDEN
     from simclr_b200 import _cabi
     be = _cabi.Backend()
-    n, d, world, rank = 37, 96, 2, 1
-    g = torch.Generator().manual_seed(5)
-    a = torch.randn(n, d, generator=g).to(in_dtype).to(dev)
-    b = torch.randn(n, d, generator=g).to(in_dtype).to(dev)
-    q_rows = 2 * n
-    ld = be.row_pitch(d, rows_dtype)
-    want = torch.empty(q_rows, ld, dtype=rows_dtype, device=dev)
-    inv_want = torch.empty(q_rows, device=dev)
-    be.l2norm(a, b, want, inv_want)
-    bufs = [torch.full((world * q_rows, ld), 7.0, dtype=rows_dtype, device=dev) for _ in range(world)]
-    inv = torch.empty(q_rows, device=dev)
-    be.l2norm_peers(a, b, [t.data_ptr() for t in bufs], rank, ld, rows_dtype, inv)
-    torch.cuda.synchronize()
-    for t in bufs:
-        assert torch.equal(t[rank * q_rows:(rank + 1) * q_rows], want)
-        assert bool((t[:rank * q_rows] == 7.0).all())
-    assert torch.equal(inv, inv_want)
-    src = torch.arange(2 * q_rows, dtype=torch.float32, device=dev).view(2, q_rows)
-    vecs = [torch.zeros(world, 2, q_rows, device=dev) for _ in range(world)]
-    be.scatter_peers(src, [t.data_ptr() for t in vecs], rank * 2 * q_rows * 4)
-    torch.cuda.synchronize()
-    for t in vecs:
-        assert torch.equal(t[rank], src) and float(t[0].abs().sum()) == 0.0
-    with pytest.raises(_cabi.NtxError, match="world"):
-        be.scatter_peers(src, [vecs[0].data_ptr()] * 9, 0)
+    c = next(g for g in GOLDEN if g.name == f"shard_w{world}")
+    nl, d = c.n // world, c.d
+    q_rows = 2 * nl
+    ld = be.row_pitch(d, dtype)
+    nbytes = be.peer_block_bytes(q_rows, ld, dtype, world)
+    assert nbytes > 0
+    blocks_mem = [torch.zeros(nbytes + 1024, dtype=torch.uint8, device=dev) for _ in range(world)]
+    ptrs = [(t.data_ptr() + 1023) // 1024 * 1024 for t in blocks_mem]
+    plan = be.plan(q_rows, world * q_rows, d, dtype)
+    ws = torch.empty(max(plan.fwd_ws_bytes, plan.bwd_ws_bytes, 16), dtype=torch.uint8, device=dev)
+    w = _nonuniform_weights(c.n).float()                                      # (2, n) on the global batch
+    one = torch.ones(1, device=dev)
+    for it in range(3):
+        if it == 1:       # second step: the views swapped (the loss is symmetric under the swap: rows and gradients swap)
+            v0, v1, wg = c.view1, c.view0, w.flip(0)
+        else:
+            v0, v1, wg = c.view0, c.view1, w
+        scalar = it == 2  # third step: ONE upstream gradient per rank (reduction mean / sum), as w_stride = 0 posts it
+        if scalar:
+            wg = torch.full_like(w, 0.5 / c.n)
+        ref = orc.ntxent_rows_fp64(v0, v1, c.tau, weights=wg.double().numpy())
+        views, invs, steps, stats, grads = [], [], [], [], []
+        for k in range(world):
+            a = torch.tensor(v0[k * nl:(k + 1) * nl], device=dev)
+            b = torch.tensor(v1[k * nl:(k + 1) * nl], device=dev)
+            inv = torch.empty(q_rows, device=dev)
+            step = torch.zeros(1, dtype=torch.int32, device=dev)
+            be.peer_l2norm(a, b, be.peer_blocks(ptrs, k), ld, dtype, inv, step)
+            views.append((a, b)); invs.append(inv); steps.append(step)
+        for k in range(world):
+            st = torch.empty(3, q_rows, device=dev)
+            ls = torch.empty(2, device=dev)
+            be.peer_fwd(be.peer_blocks(ptrs, k), nl, d, ld, dtype, c.tau, steps[k], st[0], st[1], st[2], ls, ws)
+            stats.append((st, ls))
+        for k in range(world):
+            assert int(steps[k]) == it + 1
+            got = stats[k][0][2].cpu().numpy().reshape(2, nl)
+            assert rel_err(got, ref["loss"][:, k * nl:(k + 1) * nl]) < tol
+        for k in range(world):
+            if scalar:
+                be.peer_post_weights(be.peer_blocks(ptrs, k), nl, ld, dtype, steps[k], one, 0)
+            else:
+                wk = torch.cat([wg[0, k * nl:(k + 1) * nl], wg[1, k * nl:(k + 1) * nl]]).to(dev).contiguous()
+                be.peer_post_weights(be.peer_blocks(ptrs, k), nl, ld, dtype, steps[k], wk, 1)
+        for k in range(world):
+            a, b = views[k]
+            d0, d1 = torch.empty_like(a), torch.empty_like(b)
+            be.peer_bwd(be.peer_blocks(ptrs, k), nl, d, ld, dtype, c.tau, steps[k], stats[k][0][0], 0 if scalar else 1,
+                        0.5 / c.n if scalar else 1.0, a, b, invs[k], d0, d1, ws)
+            grads.append((d0, d1))
+        scale = max(np.abs(ref["dview0"]).max(), np.abs(ref["dview1"]).max())
+        for k in range(world):
+            sl = slice(k * nl, (k + 1) * nl)
+            d0, d1 = grads[k]
+            assert np.abs(d0.cpu().numpy() - ref["dview0"][sl]).max() / scale < tol
+            assert np.abs(d1.cpu().numpy() - ref["dview1"][sl]).max() / scale < tol
+    with pytest.raises(ValueError, match="world"):
+        be.peer_blocks(ptrs[:1] * 9, 0)
 
 
 @pytest.mark.parametrize("n,hdim,d", [(8192, 512, 128), (300, 512, 128), (77, 2048, 128), (130, 64, 64),
