@@ -222,6 +222,43 @@ int ntx_fwd_static(const void* q_rows_ptr, const void* k_rows_ptr, int q_rows, i
                    int dtype, const NtxLayout* layout, float temperature, float* rowsum,
                    float* pos_logit, float* row_loss, float* loss_sum, void* stream);
 
+/* Backward of the layer ntx_project_l2norm fuses in front of the loss (Linear(h -> d, bias=False), model.py:69;
+ * SURVEY.md section 8f, rank 1), given dz = d loss / d z from ntx_bwd_rows ((2n x d) bf16, rows [0, n) = first view):
+ *   dh0 = dz[:n] . W,  dh1 = dz[n:] . W      (n x hdim, bf16)
+ *   dweight = dz^T . [h0 ; h1]               (d x hdim, bf16, fp32 accumulation, deterministic)
+ * One tcgen05 kernel (each dz tile feeds both products from shared memory) plus a small reduction of the per-CTA
+ * dweight partials; replaces the two GEMMs autograd derives for that Linear.  d <= 128 and a multiple of 8, hdim a
+ * multiple of 64, n * d a multiple of 8.  Workspace: ntx_project_bwd_workspace_bytes (sm_count <= 0: ask the device). */
+size_t ntx_project_bwd_workspace_bytes(int n, int hdim, int sm_count);
+int ntx_project_bwd(const void* dz, const void* h0, const void* h1, const void* weight, int n, int hdim, int d,
+                    void* dh0, void* dh1, void* dweight, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Fused LARC + SGD-momentum optimizer step for fp32 parameters, all tensors in one launch (SURVEY.md section 8f,
+ * rank 3).  Replaces optimizer.step() of main.py:116 for the optimizer built at main.py:85-94:
+ * apex.parallel.LARC(torch.optim.SGD(momentum, nesterov=False), trust_coefficient=0.001, clip=False) --
+ * per tensor: a = trust * ||p|| / (||g|| + wd * ||p|| + eps) when both norms are non-zero (clip != 0:
+ * a = min(a / lr, 1)), g' = (g + wd * p) * a, else g' = g;  m = momentum * m + g';  p -= lr * m.
+ * `table` (n_tensors entries) and `chunks` (n_chunks pairs {tensor index, chunk index within that tensor}, each
+ * chunk = chunk_elems elements, listed tensor by tensor in order) live in DEVICE memory and are built once by the
+ * caller; a tensor's momentum buffer must start at zero (that reproduces SGD's first step).  The workspace
+ * (ntx_larc_workspace_bytes) must be zeroed once before the first call and is left ready for the next one.
+ * Deterministic: chunk sums are added in chunk order.  One cooperative launch; no host synchronisation (the
+ * reference syncs twice per tensor through `norm != 0`). */
+typedef struct NtxLarcParam {
+    float* param;
+    const float* grad;
+    float* momentum;
+    int64_t numel;
+    float weight_decay;
+    int32_t first_chunk; /* index of this tensor's first entry in `chunks` */
+    int32_t n_chunks;    /* its number of entries: ceil(numel / chunk_elems) */
+    int32_t reserved;
+} NtxLarcParam;
+size_t ntx_larc_workspace_bytes(int n_tensors, int n_chunks);
+int ntx_larc_sgd_step(const NtxLarcParam* table, int n_tensors, const int32_t* chunks, int n_chunks, int chunk_elems,
+                      float lr, float momentum, float trust_coefficient, float eps, int clip, void* workspace,
+                      size_t workspace_bytes, void* stream);
+
 /* Test entry: the self and positive column of every row, computed on the device by
  * the same helper the kernels use (bit-exact contract on loss.py:37-38 indexing). */
 int ntx_debug_indices(const NtxLayout* layout, int32_t* self_col, int32_t* pos_col, void* stream);

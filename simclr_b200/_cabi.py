@@ -21,6 +21,7 @@ EXPORTS = (
     "ntx_version", "ntx_last_error", "ntx_row_pitch", "ntx_plan", "ntx_l2norm", "ntx_fwd",
     "ntx_bwd", "ntx_debug_indices", "ntx_profile_next", "ntx_fwd_static", "ntx_peer_block_bytes",
     "ntx_peer_l2norm", "ntx_peer_fwd", "ntx_peer_post_weights", "ntx_peer_bwd", "ntx_project_l2norm", "ntx_bwd_rows", "ntx_launch_count",
+    "ntx_larc_workspace_bytes", "ntx_larc_sgd_step", "ntx_project_bwd_workspace_bytes", "ntx_project_bwd",
 )
 
 MAX_PEERS = 8
@@ -32,6 +33,12 @@ class NtxLayout(ctypes.Structure):
 
 class NtxPeerBlocks(ctypes.Structure):
     _fields_ = [("base", ctypes.c_void_p * MAX_PEERS), ("world", ctypes.c_int32), ("rank", ctypes.c_int32)]
+
+
+class NtxLarcParam(ctypes.Structure):
+    _fields_ = [("param", ctypes.c_void_p), ("grad", ctypes.c_void_p), ("momentum", ctypes.c_void_p),
+                ("numel", ctypes.c_int64), ("weight_decay", ctypes.c_float), ("first_chunk", ctypes.c_int32),
+                ("n_chunks", ctypes.c_int32), ("reserved", ctypes.c_int32)]
 
 
 class NtxPlan(ctypes.Structure):
@@ -80,7 +87,13 @@ def _declare(lib):
     for name in EXPORTS:
         if name != "ntx_last_error":
             getattr(lib, name).restype = i
+    lib.ntx_project_bwd_workspace_bytes.argtypes = [i, i, i]
+    lib.ntx_project_bwd_workspace_bytes.restype = ctypes.c_size_t
+    lib.ntx_project_bwd.argtypes = [vp, vp, vp, vp, i, i, i, vp, vp, vp, vp, sz, vp]
+    lib.ntx_larc_workspace_bytes.argtypes = [i, i]
+    lib.ntx_larc_sgd_step.argtypes = [vp, i, vp, i, i, f, f, f, f, i, vp, sz, vp]
     lib.ntx_launch_count.restype = ctypes.c_longlong
+    lib.ntx_larc_workspace_bytes.restype = ctypes.c_size_t
     lib.ntx_peer_block_bytes.restype = ctypes.c_size_t
 
 
@@ -238,6 +251,23 @@ class Backend:
                                    self._weight_dtype(w_q, w_k), float(w_scale), inv_norm.data_ptr(), dz.data_ptr(),
                                    workspace.data_ptr(),
                                    workspace.numel() * workspace.element_size(), _stream(q)))
+
+    def project_bwd_workspace_bytes(self, n: int, hdim: int) -> int:
+        return int(load().ntx_project_bwd_workspace_bytes(n, hdim, 0))
+
+    def project_bwd(self, dz, h0, h1, weight, dh0, dh1, dweight, workspace):
+        """ntx_project_bwd: dh = dz @ W and dW = dz.T @ [h0 ; h1] from one tcgen05 kernel (d <= 128)."""
+        n, hdim = h0.shape
+        _check(load().ntx_project_bwd(dz.data_ptr(), h0.data_ptr(), h1.data_ptr(), weight.data_ptr(), n, hdim,
+                                      weight.shape[0], dh0.data_ptr(), dh1.data_ptr(), dweight.data_ptr(),
+                                      workspace.data_ptr(), workspace.numel() * workspace.element_size(), _stream(dz)))
+
+    def larc_sgd_step(self, table_dev, n_tensors, chunks_dev, n_chunks, chunk_elems, lr, momentum, trust, eps, clip,
+                      workspace):
+        """ntx_larc_sgd_step: fused LARC + SGD-momentum update of every tensor in the device table."""
+        _check(load().ntx_larc_sgd_step(table_dev.data_ptr(), n_tensors, chunks_dev.data_ptr(), n_chunks, chunk_elems,
+                                        float(lr), float(momentum), float(trust), float(eps), 1 if clip else 0,
+                                        workspace.data_ptr(), workspace.numel(), _stream(workspace)))
 
     def profile_next(self, which: int, ev_start: "torch.cuda.Event", ev_stop: "torch.cuda.Event"):
         """Arm the measurement hook: the next fwd (0) / bwd (1) call on this thread brackets its

@@ -78,12 +78,25 @@ fwd_finalize_kernel(const T* __restrict__ q, NtxDims dm, int lanes, int tile_row
     {
         const int row_local = threadIdx.x % rows_per_block, part = threadIdx.x / rows_per_block;
         const int r2 = min(blockIdx.x * rows_per_block + row_local, dm.q_rows - 1);
+        // terms part, part + lanes, ... are added in that order; the loads of eight terms are issued together
+        // (these kernels are latency-bound: a load per loop iteration costs an L2 round trip each)
+        auto strided_sum = [&](const float* base, int count) {
+            float acc = 0.f;
+            for (int i0 = part; i0 < count; i0 += 8 * lanes) {
+                float v[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    const int i = i0 + u * lanes;
+                    v[u] = i < count ? __ldg(base + (size_t)i * rows_pad + r2) : 0.f;
+                }
+#pragma unroll
+                for (int u = 0; u < 8; ++u) acc += v[u];
+            }
+            return acc;
+        };
         float c = 0.f;
-        if (colpart) {          // symmetric forward: what the tiles ABOVE this row's block saw in this row's column
-            const int rb = r2 / tile_rows;
-            for (int rbp = part; rbp < rb; rbp += lanes) c += __ldg(colpart + (size_t)rbp * rows_pad + r2);
-        }
-        for (int sl = part; sl < ns_sh; sl += lanes) c += __ldg(partial + (size_t)sl * rows_pad + r2);
+        if (colpart) c = strided_sum(colpart, r2 / tile_rows);   // symmetric forward: what the tiles ABOVE this row's block saw in this row's column
+        c += strided_sum(partial, ns_sh);
         rs_sh[part * rows_per_block + row_local] = c;
     }
     __syncthreads();
@@ -204,9 +217,14 @@ bwd_finalize_vec_kernel(BwdFinArgs A, int lanes, const TIn* __restrict__ view0,
         const int c = (sub + v * lanes) * 4;
         if (c < d) {
             float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-            for (int s = 0; s < ns; ++s) {
-                const float4 t = __ldg(reinterpret_cast<const float4*>(part + s * slot_stride + c));
-                acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+            for (int s0 = 0; s0 < ns; s0 += 4) {           // slot order, four loads in flight
+                float4 t[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    t[u] = s0 + u < ns ? __ldg(reinterpret_cast<const float4*>(part + (s0 + u) * slot_stride + c))
+                                       : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) { acc.x += t[u].x; acc.y += t[u].y; acc.z += t[u].z; acc.w += t[u].w; }
             }
             const float4 zpv = ld4(zp + c), zrv = ld4(zr + c);
             const float k = wpair * sp, it = dm.inv_tau;

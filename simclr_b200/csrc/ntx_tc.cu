@@ -822,7 +822,9 @@ __device__ __forceinline__ void coef_chunk(const uint32_t (&v)[32], uint32_t (&p
     }
 }
 
-template <int NDB>
+// kGate: peer exchange (the row sums and weights of other ranks' keys arrive during the kernel); a separate
+// instantiation so the single-GPU kernel keeps exactly its own instruction stream
+template <int NDB, bool kGate>
 __global__ void __launch_bounds__(BwdCfg<NDB>::kThreads, 1)
 tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
               const __grid_constant__ CUtensorMap tmap_q1, const __grid_constant__ CUtensorMap tmap_k1,
@@ -1000,12 +1002,12 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         // With a peer exchange the values of rank c's keys are stored into this rank's block by rank c: its forward
         // finalize (row sums, rflag) and the start of its backward (weights, wflag) -- wait for both flags once.
         float w_next = 0.f, r_next = 1.f;
-        const uint32_t gate_step = gate.step ? *gate.step : 0u;
+        const uint32_t gate_step = kGate ? *gate.step : 0u;
         uint32_t gate_ready = 0;
         auto fetch_beta = [&](int key_tile) {
             const int c = key_tile * 128 + tid_g;
             const bool ok = c < dm.k_rows;
-            if (gate.step) {
+            if constexpr (kGate) {
                 // one poller per warp (every thread polling the same word serialises on its L2 slice); the warp
                 // barrier passes the acquire on to the other lanes
                 const int c0 = key_tile * 128 + (warp & 3) * 32;
@@ -1193,15 +1195,21 @@ int launch_fwd(const RowMaps& m, const NtxDims& dm, const NtxPlan& plan, float* 
     return NTX_OK;
 }
 
+template <int NDB, bool kGate>
+int launch_bwd_g(const RowMaps& m, const NtxDims& dm, const NtxPlan& plan, const BwdWeights& wt, float* partial,
+                 const NtxGate& gate, cudaStream_t st) {
+    const size_t smem = bwd_smem_bytes<NDB>();
+    NTX_SMEM_OPT_IN((tc_bwd_kernel<NDB, kGate>), smem);
+    const long long T = (long long)plan.row_blocks * plan.key_tiles;
+    NTX_CUDA(ntx_launch_dep(tc_bwd_kernel<NDB, kGate>, plan.grid, BwdCfg<NDB>::kThreads, smem, st, m.q[0], m.k[0],
+                            m.q[1], m.k[1], dm, plan.key_tiles, T, plan.row_blocks * plan.tile_rows, wt, partial, gate));
+    return NTX_OK;
+}
 template <int NDB>
 int launch_bwd(const RowMaps& m, const NtxDims& dm, const NtxPlan& plan, const BwdWeights& wt, float* partial,
                const NtxGate& gate, cudaStream_t st) {
-    const size_t smem = bwd_smem_bytes<NDB>();
-    NTX_SMEM_OPT_IN(tc_bwd_kernel<NDB>, smem);
-    const long long T = (long long)plan.row_blocks * plan.key_tiles;
-    NTX_CUDA(ntx_launch_dep(tc_bwd_kernel<NDB>, plan.grid, BwdCfg<NDB>::kThreads, smem, st, m.q[0], m.k[0], m.q[1],
-                            m.k[1], dm, plan.key_tiles, T, plan.row_blocks * plan.tile_rows, wt, partial, gate));
-    return NTX_OK;
+    return gate.step ? launch_bwd_g<NDB, true>(m, dm, plan, wt, partial, gate, st)
+                     : launch_bwd_g<NDB, false>(m, dm, plan, wt, partial, gate, st);
 }
 
 }  // namespace

@@ -71,8 +71,11 @@ class NTXentFunction(torch.autograd.Function):
     """
 
     @staticmethod
-    def forward(ctx, view0, view1, temperature, reduction, rows_dtype, group, world, rank, peer=False):
+    def forward(ctx, view0, view1, temperature, reduction, rows_dtype, group, world, rank, peer=False, cat=False):
         be = _backend
+        if cat:                      # one (2N, D) tensor [view0 ; view1]: its halves are used in place, no copy
+            half = view0.shape[0] // 2
+            view0, view1 = view0[:half], view0[half:]
         n, d = view0.shape
         dev = view0.device
         q_rows = 2 * n
@@ -103,7 +106,7 @@ class NTXentFunction(torch.autograd.Function):
             be.fwd(q, keys, d, (n, world, rank), temperature, rowsum, pos_logit, row_loss, loss_sum, ws)
 
         ctx.save_for_backward(view0, view1, keys, stats)
-        ctx.meta = (temperature, reduction, group, world, rank, d, exchange, rows_dtype)
+        ctx.meta = (temperature, reduction, group, world, rank, d, exchange, rows_dtype, cat)
         if reduction == "none":
             out = row_loss.view(2, n).clone()                              # loss.py:55-58
         elif reduction == "sum":
@@ -116,7 +119,7 @@ class NTXentFunction(torch.autograd.Function):
     def backward(ctx, grad_out):
         be = _backend
         view0, view1, keys, stats = ctx.saved_tensors
-        temperature, reduction, group, world, rank, d, exchange, rows_dtype = ctx.meta
+        temperature, reduction, group, world, rank, d, exchange, rows_dtype, cat = ctx.meta
         n = view0.shape[0]
         q_rows = 2 * n
         dev = view0.device
@@ -128,8 +131,13 @@ class NTXentFunction(torch.autograd.Function):
         w_stride = 1 if reduction == "none" else 0
         w_scale = 1.0 / q_rows if reduction == "mean" else 1.0
         w_q = g.view(-1)
-        dview0 = torch.empty_like(view0)
-        dview1 = torch.empty_like(view1)
+        if cat:                      # one gradient tensor for the one input; the kernels write its halves
+            dcat = torch.empty((q_rows, d), dtype=view0.dtype, device=dev)
+            dview0, dview1 = dcat[:n], dcat[n:]
+        else:
+            dview0 = torch.empty_like(view0)
+            dview1 = torch.empty_like(view1)
+        grads = (dcat, None) if cat else (dview0, dview1)
         ld, ws_bytes = _shape_info(be, q_rows, world * q_rows, d, rows_dtype, dev)
         ws = _workspace(dev, ws_bytes)
         if exchange is not None:
@@ -139,7 +147,7 @@ class NTXentFunction(torch.autograd.Function):
             be.peer_bwd(exchange.blocks, n, d, ld, rows_dtype, temperature, keys, rowsum, w_stride, w_scale, view0,
                         view1, inv_norm, dview0, dview1, ws)
             exchange.end_backward()
-            return dview0, dview1, None, None, None, None, None, None, None
+            return grads + (None,) * 8
         if world > 1:
             # one collective for both per-key vectors: every rank contributes [rowsum ; row weights]
             mine = torch.stack((rowsum, w_q.to(torch.float32).expand(q_rows)))     # (2, q_rows)
@@ -154,7 +162,7 @@ class NTXentFunction(torch.autograd.Function):
             rowsum_k, w_k, q = rowsum, w_q, keys
         be.bwd(q, keys, d, (n, world, rank), temperature, rowsum, rowsum_k, w_q, w_k, w_stride, w_scale,
                view0, view1, inv_norm, dview0, dview1, ws)
-        return dview0, dview1, None, None, None, None, None, None, None
+        return grads + (None,) * 8
 
 
 class NTXentHiddenFunction(torch.autograd.Function):
@@ -164,8 +172,11 @@ class NTXentHiddenFunction(torch.autograd.Function):
     normalised rows (``ntx_bwd_rows``) and finishes the layer with two library GEMMs."""
 
     @staticmethod
-    def forward(ctx, h0, h1, weight, temperature, reduction):
+    def forward(ctx, h0, h1, weight, temperature, reduction, cat=False):
         be = _backend
+        if cat:                      # one (2N, H) tensor [h0 ; h1]: its halves are used in place
+            half = h0.shape[0] // 2
+            h0, h1 = h0[:half], h0[half:]
         n = h0.shape[0]
         d = weight.shape[0]
         dev = h0.device
@@ -178,7 +189,7 @@ class NTXentHiddenFunction(torch.autograd.Function):
         be.fwd(rows, rows, d, (n, 1, 0), temperature, stats[1], stats[2], stats[3], loss_sum,
                _workspace(dev, ws_bytes))
         ctx.save_for_backward(h0, h1, weight, rows, stats)
-        ctx.meta = (temperature, reduction, d, ws_bytes)
+        ctx.meta = (temperature, reduction, d, ws_bytes, cat)
         if reduction == "none":
             out = stats[3].view(2, n).clone()
         elif reduction == "sum":
@@ -191,7 +202,7 @@ class NTXentHiddenFunction(torch.autograd.Function):
     def backward(ctx, grad_out):
         be = _backend
         h0, h1, weight, rows, stats = ctx.saved_tensors
-        temperature, reduction, d, ws_bytes = ctx.meta
+        temperature, reduction, d, ws_bytes, cat = ctx.meta
         n = h0.shape[0]
         q_rows = 2 * n
         g = grad_out.detach().contiguous().view(-1)
@@ -202,9 +213,20 @@ class NTXentHiddenFunction(torch.autograd.Function):
         dz = torch.empty((q_rows, d), dtype=torch.bfloat16, device=h0.device)
         be.bwd_rows(rows, rows, d, (n, 1, 0), temperature, stats[1], stats[1], g, g, w_stride, w_scale, stats[0],
                     dz, _workspace(h0.device, ws_bytes))
-        dh = dz @ weight                                                     # (2n, d) . (d, h)
-        dw = torch.addmm(dz[n:].t() @ h1, dz[:n].t(), h0)                    # dz^T . [h0 ; h1]
-        return dh[:n], dh[n:], dw, None, None
+        hdim = h0.shape[1]
+        dh = torch.empty((q_rows, hdim), dtype=torch.bfloat16, device=h0.device)
+        if d <= 128 and d % 8 == 0 and (n * d) % 8 == 0:
+            # both GEMMs of the layer from one tcgen05 kernel: each dz tile feeds dh = dz . W and dW += dz^T . h
+            dw = torch.empty_like(weight)
+            ws2 = _workspace(h0.device, max(ws_bytes, be.project_bwd_workspace_bytes(n, hdim)))
+            be.project_bwd(dz, h0, h1, weight, dh[:n], dh[n:], dw, ws2)
+        else:
+            # shapes the kernel is not built for (d > 128, odd d): library GEMMs
+            torch.matmul(dz, weight, out=dh)                                 # (2n, d) . (d, h)
+            dw = torch.addmm(dz[n:].t() @ h1, dz[:n].t(), h0)                # dz^T . [h0 ; h1]
+        if cat:
+            return dh, None, dw, None, None, None
+        return dh[:n], dh[n:], dw, None, None, None
 
 
 class NT_Xent(torch.nn.Module):
@@ -285,6 +307,32 @@ class NT_Xent(torch.nn.Module):
                                         self.reduction, rows_dtype, group, world, rank,
                                         world > 1 and self.gather_backend == "peer")
 
+    def forward_cat(self, z: torch.Tensor) -> torch.Tensor:
+        """
+        The loss of ``view0 = z[:N]``, ``view1 = z[N:]`` for one ``(2N, D)`` tensor ``z = [view0 ; view1]``, as a
+        training loop gets it from ONE batched call of the encoder on both views (``z = model(torch.cat([x0, x1]))``
+        instead of the two calls at main.py:112-113).  The halves are used in place -- no split or concatenation
+        copies in forward, one ``(2N, D)`` gradient in backward -- and the result equals ``forward(z[:N], z[N:])``
+        bit for bit.  Opt-in: batching the two views through the encoder changes its BatchNorm statistics (one
+        joint batch instead of one batch per view), which is a change of the training recipe, not of this loss.
+
+        :param z: Feature representations of both views, shape (2N, D): rows [0, N) are the first view.
+        :return: same as ``forward``.
+        """
+        if z.dim() != 2 or z.shape[0] % 2 != 0 or z.shape[0] < 2 or z.shape[1] < 1:
+            raise RuntimeError(f"forward_cat expects one (2N, D) tensor, got {tuple(z.shape)}")
+        if z.dtype not in (torch.float32, torch.bfloat16):
+            raise TypeError(f"NT_Xent (B200) supports float32 and bfloat16 inputs, got {z.dtype}")
+        _require_cuda(z)
+        world, rank, group = 1, 0, None
+        if self.gather and dist.is_available() and dist.is_initialized():
+            group = self.process_group
+            world, rank = dist.get_world_size(group), dist.get_rank(group)
+        rows_dtype = self.compute_dtype or z.dtype
+        with _device_of(z):
+            return NTXentFunction.apply(z.contiguous(), None, float(self.temperature), self.reduction, rows_dtype,
+                                        group, world, rank, world > 1 and self.gather_backend == "peer", True)
+
     def forward_hidden(self, h0: torch.Tensor, h1: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
         """
         The loss of ``z0 = h0 @ weight.T``, ``z1 = h1 @ weight.T`` without materialising ``z0``, ``z1``: the last
@@ -305,6 +353,23 @@ class NT_Xent(torch.nn.Module):
         with _device_of(h0):
             return NTXentHiddenFunction.apply(h0.contiguous(), h1.contiguous(), weight.contiguous(),
                                               float(self.temperature), self.reduction)
+
+    def forward_hidden_cat(self, h: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
+        """``forward_hidden`` for one ``(2N, H)`` tensor ``h = [h0 ; h1]`` (both views batched through the encoder,
+        see ``forward_cat``): halves used in place, one ``(2N, H)`` gradient.
+
+        :param h: activations in front of the head's last layer for both views, shape (2N, H).
+        :param weight: that layer's ``weight``, shape (D, H).
+        :return: same as ``forward``.
+        """
+        if h.dim() != 2 or h.shape[0] % 2 != 0 or h.shape[0] < 2 or weight.dim() != 2 or weight.shape[1] != h.shape[1]:
+            raise RuntimeError(f"forward_hidden_cat expects (2N, H), (D, H); got {tuple(h.shape)}, {tuple(weight.shape)}")
+        if not (h.dtype == weight.dtype == torch.bfloat16):
+            raise TypeError("forward_hidden_cat runs on the bf16 tensor-core path: h and weight must be bfloat16")
+        _require_cuda(h)
+        with _device_of(h):
+            return NTXentHiddenFunction.apply(h.contiguous(), None, weight.contiguous(), float(self.temperature),
+                                              self.reduction, True)
 
     def extra_repr(self) -> str:
         return (f"temperature={self.temperature}, reduction={self.reduction!r}, gather={self.gather}, "

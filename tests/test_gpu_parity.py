@@ -370,6 +370,34 @@ def test_first_cuda_call_of_a_thread_may_be_the_library(dev):
     assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("reduction", ["mean", "none"])
+def test_forward_cat_equals_forward_on_the_halves(dtype, reduction, dev):
+    """one (2N, D) tensor from a single batched encoder call instead of main.py:112-113's two.
+    forward_cat(z) must be forward(z[:N], z[N:]) bit for bit, loss and gradient, and match the oracle."""
+    from simclr_b200 import NT_Xent
+    n, d, tau = 333, 96, 0.3
+    g = torch.Generator().manual_seed(21)
+    z = torch.randn(2 * n, d, generator=g).to(dtype)
+    crit = NT_Xent(tau, reduction)
+    zc = z.to(dev).requires_grad_(True)
+    a, b = z[:n].to(dev).requires_grad_(True), z[n:].to(dev).requires_grad_(True)
+    out_c, out_s = crit.forward_cat(zc), crit(a, b)
+    up = torch.rand(out_s.shape, generator=g).to(dtype).to(dev) if reduction == "none" else None
+    out_c.backward(up)
+    out_s.backward(up)
+    assert torch.equal(out_c, out_s)
+    assert zc.grad.shape == (2 * n, d)
+    assert torch.equal(zc.grad[:n], a.grad) and torch.equal(zc.grad[n:], b.grad)
+    w = orc.weights_for(reduction, n, up.double().cpu().numpy() if up is not None else None)
+    ref = orc.ntxent_rows_fp64(z[:n].double().numpy(), z[n:].double().numpy(), tau, weights=w)
+    tol = FP32_TOL if dtype == torch.float32 else BF16_TOL
+    want = np.concatenate([ref["dview0"], ref["dview1"]])
+    assert np.abs(zc.grad.float().cpu().numpy() - want).max() / np.abs(want).max() < tol
+    with pytest.raises(RuntimeError):
+        crit.forward_cat(z[:2 * n - 1].to(dev))          # odd number of rows: not two views
+
+
 def test_training_step_call_pattern(dev):
     """main.py:104-122 call pattern: model(view0), model(view1), loss, backward, SGD step.  Every step
     the reference-form oracle runs on the same projections z0, z1 as the checker: the loss value and
@@ -557,3 +585,33 @@ def test_forward_hidden_matches_linear_plus_loss(n, hdim, d, tau, reduction, dev
     for name, t in (("h0", t0), ("h1", t1), ("w", tw)):
         scale = np.abs(want[name]).max()
         assert np.abs(t.grad.float().cpu().numpy() - want[name]).max() / scale < 2 * BF16_TOL, name
+
+
+@pytest.mark.parametrize("n,hdim,d", [(8192, 512, 128), (300, 512, 128), (77, 2048, 128), (130, 64, 64), (64, 192, 96),
+                                       (5, 512, 8)])
+def test_project_bwd_matches_the_two_gemms(n, hdim, d, dev):
+    """ntx_project_bwd through the C ABI: dh = dz @ W and dW = dz.T @ [h0 ; h1] against fp32 matmuls of the same
+    bf16 inputs (bf16 outputs: 1e-2 of the largest entry; the accumulation is fp32).  Ragged n (tiles that end
+    inside a view), d below 128 (zero-filled feature columns), hdim of 1 to 16 column tiles."""
+    from simclr_b200 import _cabi
+    be = _cabi.Backend()
+    g = torch.Generator().manual_seed(9)
+    dz = (torch.randn(2 * n, d, generator=g) * 0.1).bfloat16().to(dev)
+    h0 = torch.randn(n, hdim, generator=g).bfloat16().to(dev)
+    h1 = torch.randn(n, hdim, generator=g).bfloat16().to(dev)
+    w = (torch.randn(d, hdim, generator=g) / hdim ** 0.5).bfloat16().to(dev)
+    dh = torch.full((2 * n, hdim), 7.0, dtype=torch.bfloat16, device=dev)
+    dw = torch.full((d, hdim), 7.0, dtype=torch.bfloat16, device=dev)
+    ws = torch.empty(be.project_bwd_workspace_bytes(n, hdim), dtype=torch.uint8, device=dev)
+    be.project_bwd(dz, h0, h1, w, dh[:n], dh[n:], dw, ws)
+    want_dh = dz.float() @ w.float()
+    want_dw = dz.float().t() @ torch.cat([h0, h1]).float()
+    assert float((dh.float() - want_dh).abs().max()) <= BF16_TOL * float(want_dh.abs().max())
+    assert float((dw.float() - want_dw).abs().max()) <= BF16_TOL * float(want_dw.abs().max())
+    dh2, dw2 = torch.empty_like(dh), torch.empty_like(dw)
+    be.project_bwd(dz, h0, h1, w, dh2[:n], dh2[n:], dw2, ws)
+    assert torch.equal(dh, dh2) and torch.equal(dw, dw2)          # deterministic (fixed-order partial sums)
+    with pytest.raises(_cabi.NtxError, match="d <= 128"):
+        be.project_bwd(torch.empty(2 * n, 256, dtype=torch.bfloat16, device=dev), h0, h1,
+                       torch.empty(256, hdim, dtype=torch.bfloat16, device=dev), dh[:n], dh[n:],
+                       torch.empty(256, hdim, dtype=torch.bfloat16, device=dev), ws)
