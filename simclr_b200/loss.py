@@ -243,7 +243,9 @@ class NT_Xent(torch.nn.Module):
                  process_group=None, compute_dtype: torch.dtype | None = None,
                  gather_backend: str | None = None) -> None:
         """
-        :param temperature: Temperature parameter. The value must be positive.
+        :param temperature: Temperature parameter. The value must be positive.  The kernels use a fixed-shift
+            logsumexp and refuse temperatures below 0.0235 (exp((cos - 1) / temperature) would leave fp32 range);
+            the reference has no such floor.
         :param reduction: Same to PyTorch's `reduction` in losses.
         :param device: PyTorch's device instance (kept for signature compatibility).
         :param gather: keyword-only. True = negatives from every rank of ``process_group``;
@@ -301,11 +303,20 @@ class NT_Xent(torch.nn.Module):
         if self.gather and dist.is_available() and dist.is_initialized():
             group = self.process_group
             world, rank = dist.get_world_size(group), dist.get_rank(group)
-        rows_dtype = self.compute_dtype or view0.dtype
+        rows_dtype = self._rows_dtype(view0)
         with _device_of(view0):
             return NTXentFunction.apply(view0.contiguous(), view1.contiguous(), float(self.temperature),
                                         self.reduction, rows_dtype, group, world, rank,
                                         world > 1 and self.gather_backend == "peer")
+
+    def _rows_dtype(self, x: torch.Tensor) -> torch.dtype:
+        """dtype of the normalised rows: ``compute_dtype``, else the input dtype -- except that bf16 rows wider than
+        the tensor-core kernels' 256 features per tile fall back to fp32 rows on the CUDA-core kernels (any D), so
+        the module accepts every feature size the reference does."""
+        dt = self.compute_dtype or x.dtype
+        if dt == torch.bfloat16 and x.shape[1] > 256:
+            return torch.float32
+        return dt
 
     def forward_cat(self, z: torch.Tensor) -> torch.Tensor:
         """
@@ -328,7 +339,7 @@ class NT_Xent(torch.nn.Module):
         if self.gather and dist.is_available() and dist.is_initialized():
             group = self.process_group
             world, rank = dist.get_world_size(group), dist.get_rank(group)
-        rows_dtype = self.compute_dtype or z.dtype
+        rows_dtype = self._rows_dtype(z)
         with _device_of(z):
             return NTXentFunction.apply(z.contiguous(), None, float(self.temperature), self.reduction, rows_dtype,
                                         group, world, rank, world > 1 and self.gather_backend == "peer", True)

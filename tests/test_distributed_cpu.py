@@ -30,22 +30,6 @@ def _init(rank, port):
     return du
 
 
-def _worker_gather(rank, port, out):
-    du = _init(rank, port)
-    torch.manual_seed(0)
-    full = torch.randn(WORLD * 3, 4, dtype=torch.float64)
-    mine = full[rank * 3:(rank + 1) * 3].clone().requires_grad_(True)
-    gathered = du.gather_rows_with_grad(mine)
-    assert torch.equal(gathered.detach(), full)                      # rank-major order
-    weight = torch.arange(1, WORLD * 3 * 4 + 1, dtype=torch.float64).view(WORLD * 3, 4) * (rank + 1)
-    (gathered * weight).sum().backward()
-    # SUM reduce-scatter: rank r's rows collect the weights every rank applied to its chunk
-    want = sum(torch.arange(1, WORLD * 3 * 4 + 1, dtype=torch.float64).view(WORLD * 3, 4)[rank * 3:(rank + 1) * 3] * (k + 1)
-               for k in range(WORLD))
-    out[rank] = bool(torch.allclose(mine.grad, want))
-    du.cleanup()
-
-
 def _worker_loss(rank, port, reduction, out):
     _init(rank, port)
     import simclr_b200.loss as loss_mod
@@ -76,11 +60,6 @@ def _spawn(fn, *args):
     out = mgr.dict()
     mp.spawn(fn, args=(_free_port(), *args, out), nprocs=WORLD, join=True)
     return dict(out)
-
-
-def test_gather_rows_forward_and_reduce_scatter_backward():
-    out = _spawn(_worker_gather)
-    assert out == {0: True, 1: True}
 
 
 def test_gathered_loss_matches_reference_on_concatenated_batch():
