@@ -66,6 +66,7 @@ def parse():
 
 
 GATHER_BACKEND = "nccl"
+PEER_MULTICAST = False
 
 
 def workload_config(world, eager=False):
@@ -73,7 +74,9 @@ def workload_config(world, eager=False):
                         f"tau={TAU}, bf16 (BASELINE configs[{3 if N_GLOBAL == 8192 else 4}])",
             "global_batch": N_GLOBAL, "d": DIM, "temperature": TAU,
             "parallelism": (f"rows sharded over {world} rank(s), keys gathered by "
-                            + ("the kernels' own peer-memory stores and flag words (NVLink), no barrier kernel"
+                            + ("the kernels' own peer-memory stores and flag words (NVLink"
+                               + (", multimem.st through the NVSwitch multicast mapping" if PEER_MULTICAST else "")
+                               + "), no barrier kernel"
                                if GATHER_BACKEND == "peer" else "NCCL all-gather")) if world > 1 else "single GPU",
             "l2": "flushed between timed steps (256 MiB write)",
             "launch": "eager" if eager else "one CUDA graph of the module's forward + backward "
@@ -339,7 +342,9 @@ def run_ours(args):
         if ok.item():
             try:
                 ld = _cabi.Backend().row_pitch(DIM, torch.bfloat16)
-                peer_exchange.exchange_for(_cabi.Backend(), None, 2 * n_local, ld, torch.bfloat16, dev)
+                ex = peer_exchange.exchange_for(_cabi.Backend(), None, 2 * n_local, ld, torch.bfloat16, dev)
+                global PEER_MULTICAST
+                PEER_MULTICAST = bool(ex.multicast)
             except Exception as e:  # noqa: BLE001
                 print(f"[bench] rank {rank}: peer-memory gather unavailable ({e!r}); using NCCL", file=sys.stderr)
                 ok.zero_()

@@ -137,6 +137,9 @@ int ntx_project_l2norm(const void* h0, const void* h1, const void* weight, int n
 #define NTX_MAX_PEERS 8
 typedef struct NtxPeerBlocks {
     void* base[NTX_MAX_PEERS];
+    void* multicast; /* optional: multicast (NVSwitch / NVLS) mapping of all the blocks, or NULL.  With it a producer
+                      * issues ONE multimem.st per datum and the switch replicates it into every rank's block, instead
+                      * of one store per rank over NVLink */
     int32_t world;
     int32_t rank;
 } NtxPeerBlocks;

@@ -32,7 +32,8 @@ class NtxLayout(ctypes.Structure):
 
 
 class NtxPeerBlocks(ctypes.Structure):
-    _fields_ = [("base", ctypes.c_void_p * MAX_PEERS), ("world", ctypes.c_int32), ("rank", ctypes.c_int32)]
+    _fields_ = [("base", ctypes.c_void_p * MAX_PEERS), ("multicast", ctypes.c_void_p), ("world", ctypes.c_int32),
+                ("rank", ctypes.c_int32)]
 
 
 class NtxLarcParam(ctypes.Structure):
@@ -168,8 +169,9 @@ class Backend:
         return int(load().ntx_peer_block_bytes(q_rows, ld, DTYPES[rows_dtype], world))
 
     @staticmethod
-    def peer_blocks(ptrs, rank: int) -> NtxPeerBlocks:
+    def peer_blocks(ptrs, rank: int, multicast: int = 0) -> NtxPeerBlocks:
         pb = NtxPeerBlocks()
+        pb.multicast = multicast or None
         if not 1 <= len(ptrs) <= MAX_PEERS:
             raise ValueError(f"peer exchange: world {len(ptrs)} outside [1, {MAX_PEERS}] (one node)")
         for p, addr in enumerate(ptrs):

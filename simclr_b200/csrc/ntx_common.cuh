@@ -204,6 +204,8 @@ NTX_HD NtxPeerGeom ntx_peer_geom(int q_rows, int ld, int esz, int world) {
 // What a kernel needs to store into every rank's block and to raise the flags there.
 struct NtxPeerOut {
     uint8_t* base[NTX_MAX_PEERS];   // block of rank p as mapped into this process; base[rank] is this rank's own
+    uint8_t* mc;                    // multicast mapping of the blocks (one multimem.st lands in EVERY rank's block:
+                                    // the NVSwitch replicates it), or NULL: one store per rank instead
     int world, rank;                // world == 0: no exchange
 };
 // What a kernel needs to wait for data other ranks store into this rank's block.
@@ -229,10 +231,40 @@ __device__ __forceinline__ void ntx_fence_sys() { asm volatile("fence.acq_rel.sy
 __device__ __forceinline__ void ntx_st_relaxed_sys(uint32_t* p, uint32_t v) {
     asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+// stores that land at the same offset of every rank's block: one multimem.st through the multicast mapping
+__device__ __forceinline__ void ntx_mc_st_u32(uint8_t* mc, size_t off, uint32_t v) {
+    asm volatile("multimem.st.relaxed.sys.global.u32 [%0], %1;" ::"l"(mc + off), "r"(v) : "memory");
+}
+__device__ __forceinline__ void ntx_mc_st_f32(uint8_t* mc, size_t off, float v) {
+    asm volatile("multimem.st.weak.global.f32 [%0], %1;" ::"l"(mc + off), "f"(v) : "memory");
+}
+__device__ __forceinline__ void ntx_mc_st_16B(uint8_t* mc, size_t off, uint4 v) {
+    asm volatile("multimem.st.weak.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc + off), "f"(__uint_as_float(v.x)),
+                 "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w))
+                 : "memory");
+}
+__device__ __forceinline__ void ntx_mc_st_8B(uint8_t* mc, size_t off, uint2 v) {
+    asm volatile("multimem.st.weak.global.v2.f32 [%0], {%1, %2};" ::"l"(mc + off), "f"(__uint_as_float(v.x)),
+                 "f"(__uint_as_float(v.y))
+                 : "memory");
+}
+// one float to the same place of every rank's block
+__device__ __forceinline__ void ntx_peer_st_f32(const NtxPeerOut& peers, size_t off, float v) {
+    if (peers.mc) {
+        ntx_mc_st_f32(peers.mc, off, v);
+    } else {
+        for (int p = 0; p < peers.world; ++p) *reinterpret_cast<float*>(peers.base[p] + off) = v;
+    }
+}
 __device__ __forceinline__ void ntx_raise_flags(const NtxPeerOut& peers, int word, uint32_t step) {
     ntx_fence_sys();
-    for (int p = 0; p < peers.world; ++p)
-        ntx_st_relaxed_sys(reinterpret_cast<uint32_t*>(peers.base[p]) + word + peers.rank, step);
+    const size_t off = (size_t)(word + peers.rank) * sizeof(uint32_t);
+    if (peers.mc) {
+        ntx_mc_st_u32(peers.mc, off, step);
+    } else {
+        for (int p = 0; p < peers.world; ++p)
+            ntx_st_relaxed_sys(reinterpret_cast<uint32_t*>(peers.base[p] + off), step);
+    }
 }
 __device__ __forceinline__ uint32_t ntx_ld_relaxed(const uint32_t* p) {
     uint32_t v;

@@ -15,7 +15,7 @@
 namespace {
 
 constexpr int kThreads = 512;        // backward finalize / generic kernels
-constexpr int kFwdThreads = 1024;    // forward finalize: few blocks -> few serialized tickets
+constexpr int kFwdThreads = 1024;    // forward finalize: few blocks -> few serialized tickets (256 when that leaves SMs idle)
 
 __device__ __forceinline__ float ldf(const float* p, size_t i) { return __ldg(p + i); }
 __device__ __forceinline__ float ldf(const __nv_bfloat16* p, size_t i) { return __bfloat162float(p[i]); }
@@ -65,12 +65,13 @@ fwd_finalize_kernel(const T* __restrict__ q, NtxDims dm, int lanes, int tile_row
     // colpart != NULL: the symmetric forward's upper-triangle partition (Tt, G describe that one).
     __shared__ int ns_sh;
     if (threadIdx.x == 0) {
-        const int rb0 = (int)((long long)blockIdx.x * (kFwdThreads / lanes) / tile_rows);
+        const int rb0 = (int)((long long)blockIdx.x * ((int)blockDim.x / lanes) / tile_rows);
         ns_sh = colpart ? ntx_tri_num_slots(Tt, G, key_tiles, rb0) : ntx_num_slots(Tt, G, key_tiles, rb0);
     }
     __syncthreads();
     double my_loss = 0.0;
-    const int rows_per_block = kFwdThreads / lanes;
+    const int nthreads = (int)blockDim.x;                    // kFwdThreads or 256
+    const int rows_per_block = nthreads / lanes;
     // Row sums first, with the block laid out rows-fastest so that a warp reads 32 consecutive rows of one
     // slot (or of one row block's column partials): thread t adds the terms part, part + lanes, ... of row
     // t % rows_per_block; the `lanes` parts of a row are then added in part order.
@@ -123,8 +124,8 @@ fwd_finalize_kernel(const T* __restrict__ q, NtxDims dm, int lanes, int tile_row
             pos_logit[r] = pos;
             row_loss[r] = l;
             my_loss = (double)l;
-            for (int p = 0; p < peers.world; ++p)
-                reinterpret_cast<float*>(peers.base[p] + rowsum_off)[(size_t)peers.rank * dm.q_rows + r] = R;
+            if (peers.world > 0)
+                ntx_peer_st_f32(peers, rowsum_off + ((size_t)peers.rank * dm.q_rows + r) * sizeof(float), R);
         }
     }
     // Block sums in a fixed order, then the last block standing adds the block sums in block
@@ -138,7 +139,7 @@ fwd_finalize_kernel(const T* __restrict__ q, NtxDims dm, int lanes, int tile_row
     __syncthreads();
     if (threadIdx.x == 0) {
         double v = 0.0;
-        for (int w = 0; w < kFwdThreads / 32; ++w) v += part[w];
+        for (int w = 0; w < nthreads / 32; ++w) v += part[w];
         block_sums[blockIdx.x] = v;
         __threadfence();                                     // also orders the block's peer stores (barrier above)
         is_last = atomicAdd(counter, 1u) == gridDim.x - 1;
@@ -147,14 +148,14 @@ fwd_finalize_kernel(const T* __restrict__ q, NtxDims dm, int lanes, int tile_row
     if (!is_last) return;
     __threadfence();
     acc = 0.0;
-    for (int i = threadIdx.x; i < (int)gridDim.x; i += kFwdThreads) acc += __ldcg(block_sums + i);
+    for (int i = threadIdx.x; i < (int)gridDim.x; i += nthreads) acc += __ldcg(block_sums + i);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
     if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = acc;
     __syncthreads();
     if (threadIdx.x == 0) {
         double v = 0.0;
-        for (int w = 0; w < kFwdThreads / 32; ++w) v += part[w];
+        for (int w = 0; w < nthreads / 32; ++w) v += part[w];
         loss_sum[0] = (float)v;                              // reduction="sum"
         loss_sum[1] = (float)(v / (double)dm.q_rows);        // reduction="mean": sum / N * 0.5, rows = 2N
         *counter = 0;
@@ -188,7 +189,7 @@ bwd_finalize_vec_kernel(BwdFinArgs A, int lanes, const TIn* __restrict__ view0,
     ntx_dep_trigger();
     ntx_dep_wait();
     const NtxDims& dm = A.dm;
-    const int rows_per_block = kThreads / lanes;
+    const int rows_per_block = (int)blockDim.x / lanes;      // kThreads, or fewer when that leaves SMs idle
     // rows of one block share a row block (tile_rows is a multiple of rows_per_block): one slot count
     __shared__ int ns_sh;
     if (threadIdx.x == 0)
@@ -310,10 +311,13 @@ int launch_bwd_finalize(const BwdFinArgs& A, const void* view0, const void* view
                      reinterpret_cast<uintptr_t>(dview0) % 16 == 0 && reinterpret_cast<uintptr_t>(dview1) % 16 == 0;
     if (vec) {
         const int lanes = lanes_for(d / 4);
-        const int grid = (A.dm.q_rows + kThreads / lanes - 1) / (kThreads / lanes);
+        // latency-bound: with few rows (one of several ranks) smaller blocks keep every SM busy
+        int threads = kThreads;
+        while (threads > 128 && (A.dm.q_rows + threads / lanes - 1) / (threads / lanes) < 296) threads >>= 1;
+        const int grid = (A.dm.q_rows + threads / lanes - 1) / (threads / lanes);
         const int per_thread = (d / 4 + lanes - 1) / lanes;          // float4 groups each thread covers
 #define NTX_BWD_FIN(V)                                                                                        \
-    NTX_CUDA(ntx_launch_dep(bwd_finalize_vec_kernel<TIn, V>, grid, kThreads, 0, st, A, lanes, (const TIn*)view0, \
+    NTX_CUDA(ntx_launch_dep(bwd_finalize_vec_kernel<TIn, V>, grid, threads, 0, st, A, lanes, (const TIn*)view0, \
                             (const TIn*)view1, (TIn*)dview0, (TIn*)dview1))
         if (per_thread <= 1) NTX_BWD_FIN(1);
         else if (per_thread <= 2) NTX_BWD_FIN(2);
@@ -340,9 +344,17 @@ int ntx_debug_indices_launch(int n_local, int rank, int32_t* self_col, int32_t* 
     return NTX_OK;
 }
 
+// threads per block of the forward finalize: kFwdThreads, or 256 when that would leave most SMs without a block
+// (one of several ranks: 2048 rows are 32 blocks of 1024 threads)
+static int fwd_finalize_threads(int q_rows, int lanes) {
+    const int blocks = (q_rows + kFwdThreads / lanes - 1) / (kFwdThreads / lanes);
+    return blocks < 148 ? 256 : kFwdThreads;
+}
+
 int ntx_fwd_finalize_blocks(int q_rows, int ld) {
     const int lanes = lanes_for(ld / 4);
-    return (q_rows + kFwdThreads / lanes - 1) / (kFwdThreads / lanes);
+    const int threads = fwd_finalize_threads(q_rows, lanes);
+    return (q_rows + threads / lanes - 1) / (threads / lanes);
 }
 
 int ntx_fwd_finalize_launch(const void* q, int dtype, const NtxDims& dm, const NtxPlan& plan,
@@ -356,13 +368,14 @@ int ntx_fwd_finalize_launch(const void* q, int dtype, const NtxDims& dm, const N
     const int rows_pad = plan.row_blocks * plan.tile_rows;
     const int lanes = lanes_for(dm.ld / 4);
     const int grid = ntx_fwd_finalize_blocks(dm.q_rows, dm.ld);
+    const int threads = fwd_finalize_threads(dm.q_rows, lanes);
     if (dtype == NTX_F32)
-        NTX_CUDA(ntx_launch_dep(fwd_finalize_kernel<float>, grid, kFwdThreads, 0, st, (const float*)q, dm, lanes,
+        NTX_CUDA(ntx_launch_dep(fwd_finalize_kernel<float>, grid, threads, 0, st, (const float*)q, dm, lanes,
                                 plan.tile_rows, plan.key_tiles, T, G, rows_pad, partial, colpart, counter,
                                 block_sums, rowsum, pos_logit, row_loss, loss_sum, peers, rowsum_off, gate,
                                 key_buf_elems));
     else
-        NTX_CUDA(ntx_launch_dep(fwd_finalize_kernel<__nv_bfloat16>, grid, kFwdThreads, 0, st,
+        NTX_CUDA(ntx_launch_dep(fwd_finalize_kernel<__nv_bfloat16>, grid, threads, 0, st,
                                 (const __nv_bfloat16*)q, dm, lanes, plan.tile_rows, plan.key_tiles, T, G, rows_pad,
                                 partial, colpart, counter, block_sums, rowsum, pos_logit, row_loss, loss_sum, peers,
                                 rowsum_off, gate, key_buf_elems));

@@ -123,7 +123,21 @@ l2norm_kernel(const TIn* __restrict__ view0, const TIn* __restrict__ view1, int 
 #pragma unroll
                     for (int i = 0; i < V; ++i) v[i] = 0.f;
                 }
-                for (int p = 0; p < ndst; ++p) storev<V>(dst_rows(p) + dst_off + c, v);
+                if (peers.world > 0 && peers.mc) {            // multicast stores: 16 bytes each (8 for 4 bf16 values)
+                    __align__(16) TOut tmp[V];
+                    storev<V>(tmp, v);
+                    constexpr int kBytes = V * (int)sizeof(TOut);
+                    const size_t at = dst_bytes + (dst_off + c) * sizeof(TOut);
+                    if constexpr (kBytes == 8) {
+                        ntx_mc_st_8B(peers.mc, at, *reinterpret_cast<const uint2*>(tmp));
+                    } else {
+#pragma unroll
+                        for (int q = 0; q < kBytes / 16; ++q)
+                            ntx_mc_st_16B(peers.mc, at + q * 16, reinterpret_cast<const uint4*>(tmp)[q]);
+                    }
+                } else {
+                    for (int p = 0; p < ndst; ++p) storev<V>(dst_rows(p) + dst_off + c, v);
+                }
             }
         } else {
             for (int c = sub; c < ld; c += lanes) {
@@ -185,15 +199,13 @@ post_weights_kernel(const float* __restrict__ w, int w_stride, int w_bf16, int q
     ntx_dep_trigger();
     ntx_dep_wait();
     if (w_stride == 0) {
-        if (threadIdx.x < peers.world)
-            reinterpret_cast<float*>(peers.base[threadIdx.x] + weight_off)[peers.rank] = ntx_ld_weight(w, 0, w_bf16);
+        if (threadIdx.x == 0)
+            ntx_peer_st_f32(peers, weight_off + (size_t)peers.rank * sizeof(float), ntx_ld_weight(w, 0, w_bf16));
     } else {
         const int r = blockIdx.x * blockDim.x + threadIdx.x;
-        if (r < q_rows) {
-            const float v = ntx_ld_weight(w, r, w_bf16);
-            for (int p = 0; p < peers.world; ++p)
-                reinterpret_cast<float*>(peers.base[p] + weight_off)[(size_t)peers.rank * q_rows + r] = v;
-        }
+        if (r < q_rows)
+            ntx_peer_st_f32(peers, weight_off + ((size_t)peers.rank * q_rows + r) * sizeof(float),
+                            ntx_ld_weight(w, r, w_bf16));
     }
     __syncthreads();
     if (threadIdx.x == 0) {

@@ -22,6 +22,8 @@ Hazards and how they are closed:
 """
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -51,7 +53,13 @@ class PeerExchange:
         self.block = symm_mem.empty(nbytes, dtype=torch.uint8, device=device)
         self.block.zero_()                                   # flags, step count and key buffers start at zero
         self.handle = symm_mem.rendezvous(self.block, group=self.group.group_name)
-        self.blocks = be.peer_blocks([int(p) for p in self.handle.buffer_ptrs], self.rank)
+        # NVSwitch multicast mapping of the blocks when the platform has one (0 otherwise): one multimem.st per datum
+        # instead of one store per rank.  NTXENT_PEER_MULTICAST=0 turns it off.
+        mc = int(getattr(self.handle, "multicast_ptr", 0) or 0)
+        if os.environ.get("NTXENT_PEER_MULTICAST", "1").lower() in ("0", "false", "no", "off"):
+            mc = 0
+        self.multicast = mc
+        self.blocks = be.peer_blocks([int(p) for p in self.handle.buffer_ptrs], self.rank, mc)
         torch.cuda.synchronize(device)
         dist.barrier(group=self.group)                       # every block is zeroed before any rank stores into one
         self.outstanding = 0                                 # forwards whose backward has not run yet

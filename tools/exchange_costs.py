@@ -8,11 +8,9 @@ this box (BASELINE configs[3]: N = 8192 pairs, D = 128):
 
     python -m torch.distributed.run --nproc-per-node W --master-addr 127.0.0.1 tools/exchange_costs.py
 
-Rank 0 prints one JSON line with the median time of each collective (CUDA-graph replays of the single collective,
-CUDA events, max over ranks), so that the numbers carry no host launch time."""
+Rank 0 prints one JSON line with the time per collective (50 back to back between two CUDA events, max over ranks)."""
 import json
 import os
-import statistics
 import sys
 
 import torch
@@ -42,22 +40,18 @@ def main():
     out = {"world": world, "bytes": {"all_gather_keys_bf16": keys.numel() * 2, "reduce_scatter_dK_fp32": dk.numel() * 4,
                                      "all_gather_rowsum_fp32": rs_all.numel() * 4}}
     for name, fn in ops.items():
-        for _ in range(5):
+        for _ in range(10):
             fn()
         torch.cuda.synchronize()
-        graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(graph):
+        # 50 back-to-back collectives between two events: the GPU-side cost per collective once the launch queue
+        # is full (host launch time hidden behind the previous collective)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(50):
             fn()
-        times = []
-        for _ in range(30):
-            dist.barrier()
-            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a.record()
-            graph.replay()
-            b.record()
-            torch.cuda.synchronize()
-            times.append(a.elapsed_time(b) * 1e3)
-        t = torch.tensor([statistics.median(times)], device=dev)
+        b.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([a.elapsed_time(b) * 1e3 / 50], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         out[name + "_us"] = round(float(t), 2)
     if rank == 0:

@@ -43,6 +43,9 @@ def forward(k):
     be.fwd(q, keys, d, (nl, world, k), 0.5, stats[k, 1], stats[k, 2], stats[k, 3], loss_sum, ws)
 
 
+for k in range(world - 1, 0, -1):                 # every rank's rows first, then their forward passes
+    be.l2norm(views[k][0], views[k][1], keys[k * q_rows:(k + 1) * q_rows], stats[k, 0])
+be.l2norm(views[0][0], views[0][1], keys[:q_rows], stats[0, 0])
 for k in range(world - 1, 0, -1):
     forward(k)
 for _ in range(steps):
