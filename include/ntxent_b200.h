@@ -76,7 +76,7 @@ typedef struct NtxPlan {
     int32_t fwd_symmetric; /* 1: keys == rows, bf16, d_pad <= 128 -> only tiles (rb, kt >= rb) are computed */
     int32_t fwd_grid;      /* CTAs of the symmetric forward kernel */
     int32_t fwd_max_slots; /* its row-sum slots per row block */
-    int32_t reserved;
+    int32_t segments;      /* (CTA, row block) pairs of the main kernels: sum over row blocks of their slot counts */
 } NtxPlan;
 
 int ntx_version(void);

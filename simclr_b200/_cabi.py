@@ -49,7 +49,7 @@ class NtxPlan(ctypes.Structure):
         ("d_pad", ctypes.c_int32), ("tensor_cores", ctypes.c_int32),
         ("fwd_ws_bytes", ctypes.c_uint64), ("bwd_ws_bytes", ctypes.c_uint64),
         ("fwd_ws_bytes_min", ctypes.c_uint64), ("fwd_symmetric", ctypes.c_int32),
-        ("fwd_grid", ctypes.c_int32), ("fwd_max_slots", ctypes.c_int32), ("reserved", ctypes.c_int32),
+        ("fwd_grid", ctypes.c_int32), ("fwd_max_slots", ctypes.c_int32), ("segments", ctypes.c_int32),
     ]
 
 

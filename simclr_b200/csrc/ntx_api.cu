@@ -96,6 +96,16 @@ int make_dims(int q_rows, int k_rows, int d, int ld, int dtype, const NtxLayout*
     return NTX_OK;
 }
 
+// do the tensor-core kernels finish their rows themselves?  (see fwd_impl)
+bool fold_wanted(const NtxPlan& plan) {
+    static const int forced = [] {
+        const char* e = getenv("NTXENT_FOLD");
+        return e && e[0] ? (e[0] != '0' ? 1 : 0) : -1;
+    }();
+    if (forced >= 0) return forced == 1;
+    return plan.max_slots >= 7;
+}
+
 int aligned16(const void* p, const char* what) {
     NTX_CHECK_ARG(p != nullptr, "%s is NULL", what);
     NTX_CHECK_ARG(reinterpret_cast<uintptr_t>(p) % 16 == 0, "%s must be 16-byte aligned", what);
@@ -153,18 +163,23 @@ int ntx_plan(int q_rows, int k_rows, int d, int dtype, int sm_count, NtxPlan* pl
         const long long aligned = ctas / plan->row_blocks * plan->row_blocks;
         if (aligned * 100 >= ctas * 95) plan->grid = (int)aligned;
     }
-    int max_slots = 1;
+    int max_slots = 1, segments = 0;
     for (int rb = 0; rb < plan->row_blocks; ++rb) {
         const int s = ntx_num_slots(T, plan->grid, plan->key_tiles, rb);
         if (s > max_slots) max_slots = s;
+        segments += s;
     }
     plan->max_slots = max_slots;
+    plan->segments = segments;
     const uint64_t rows_pad = (uint64_t)plan->row_blocks * plan->tile_rows;
-    // row-sum partials + finalize ticket + one fp64 block sum per finalize block
+    // forward scratch: row-sum partials + either the fold counters and share losses of the tensor-core kernel that
+    // finishes its rows itself, or the finalize kernel's ticket and one fp64 block sum per finalize block
     const uint64_t fin_bytes = 16 + (((uint64_t)ntx_fwd_finalize_blocks(q_rows, ntx_row_pitch(d, dtype)) * 8 + 15) & ~15ull);
-    plan->fwd_ws_bytes_min = (uint64_t)max_slots * rows_pad * sizeof(float) + fin_bytes;
+    const uint64_t fold_bytes = ntx_fold_ctl_bytes(plan->row_blocks) + ntx_fold_seg_bytes(plan->row_blocks, plan->grid);
+    plan->fwd_ws_bytes_min = (uint64_t)max_slots * rows_pad * sizeof(float) + fin_bytes + (plan->tensor_cores ? fold_bytes : 0);
     plan->fwd_ws_bytes = plan->fwd_ws_bytes_min;
-    plan->bwd_ws_bytes = (uint64_t)max_slots * rows_pad * plan->d_pad * sizeof(float);
+    plan->bwd_ws_bytes = (uint64_t)max_slots * rows_pad * plan->d_pad * sizeof(float) +
+                         (plan->tensor_cores ? ntx_fold_ctl_bytes(plan->row_blocks) : 0);
 
     // Symmetric forward: the keys are the rows themselves (one rank), so S = S^T and only the tiles
     // (rb, kt >= rb) need computing.  Needs one column partial per (row block, key) besides the slots.
@@ -250,6 +265,38 @@ int fwd_impl(const void* q, const void* k, int q_rows, int k_rows, int d, int ld
     // the symmetric kernel needs q and k to be the same buffer and the larger scratch
     const bool sym = plan.fwd_symmetric && q == k && layout->world == 1 && workspace_bytes >= plan.fwd_ws_bytes;
     const uint64_t rows_pad = (uint64_t)plan.row_blocks * plan.tile_rows;
+    if (plan.tensor_cores && !sym) {
+        // full-tile tensor-core forward.  When many CTAs share a row block (a small shard of a large key set: one of
+        // 8 ranks at config 4 has 9 per row block) the kernel finishes the rows itself, each CTA a small share
+        // (NtxFoldScratch at the head of the scratch): measured 82 against 88 us per step of the 1-of-8 shapes.  With
+        // few CTAs per row block the shares are large and the separate, fully occupied finalize kernel is faster
+        // (1 GPU: 220 against 226 us).  NTXENT_FOLD=1 / 0 forces the choice.
+        const bool no_fold = !fold_wanted(plan);
+        char* ws = (char*)workspace;
+        const uint64_t head = ntx_fold_ctl_bytes(plan.row_blocks) + ntx_fold_seg_bytes(plan.row_blocks, plan.grid);
+        const uint64_t partial_bytes = (uint64_t)plan.max_slots * rows_pad * sizeof(float);
+        float* partial = (float*)(ws + head);
+        unsigned int* counter = (unsigned int*)(ws + head + partial_bytes);
+        double* block_sums = (double*)(ws + head + partial_bytes + 16);
+        NtxFoldScratch fold;
+        fold.tag = (unsigned int*)ws;
+        fold.done_total = (unsigned int*)(ws + 4);
+        fold.arrive = (unsigned int*)(ws + 64);
+        fold.seg_loss = (double*)(ws + ntx_fold_ctl_bytes(plan.row_blocks));
+        fold.n_segments = plan.segments;
+        fold.row_blocks = plan.row_blocks;
+        fold.enabled = no_fold ? 0 : 1;
+        fold.legacy_ticket = counter;
+        const NtxFwdOut out{rowsum, pos_logit, row_loss, loss_sum, ex.out, ex.geom.rowsum_off};
+        {
+            ProfScope prof(0, st);
+            rc = ntx_tc_fwd_launch((const __nv_bfloat16*)q, (const __nv_bfloat16*)k, dm, plan, partial, fold, out,
+                                   ex.gate, ex.key_buf_elems, st);
+        }
+        if (rc || !no_fold) return rc;
+        return ntx_fwd_finalize_launch(q, dtype, dm, plan, partial, nullptr, counter, block_sums, rowsum, pos_logit,
+                                       row_loss, loss_sum, ex.out, ex.geom.rowsum_off, ex.gate, ex.key_buf_elems, st);
+    }
     const uint64_t partial_bytes = (uint64_t)(sym ? plan.fwd_max_slots : plan.max_slots) * rows_pad * sizeof(float);
     const uint64_t fin_bytes = 16 + (((uint64_t)ntx_fwd_finalize_blocks(q_rows, ld) * 8 + 15) & ~15ull);
     float* partial = (float*)workspace;
@@ -260,9 +307,6 @@ int fwd_impl(const void* q, const void* k, int q_rows, int k_rows, int d, int ld
         ProfScope prof(0, st);
         if (sym)
             rc = ntx_tc_fwd_sym_launch((const __nv_bfloat16*)q, dm, plan, partial, colpart, counter, st);
-        else if (plan.tensor_cores)
-            rc = ntx_tc_fwd_launch((const __nv_bfloat16*)q, (const __nv_bfloat16*)k, dm, plan, partial,
-                                   counter, ex.gate, ex.key_buf_elems, st);
         else
             rc = ntx_simt_fwd_launch((const float*)q, (const float*)k, dm, plan, partial, counter, ex.gate,
                                      ex.key_buf_elems, st);
@@ -310,17 +354,34 @@ static int bwd_impl(const void* q, const void* k, int q_rows, int k_rows, int d,
     }
     if ((rc = aligned16(workspace, "workspace"))) return rc;
     cudaStream_t st = (cudaStream_t)stream;
-    float* partial = (float*)workspace;
     const NtxWeights wt{rowsum_q, rowsum_k, (const float*)w_q, (const float*)w_k, w_stride, w_scale, w_chunk,
                         w_dtype == NTX_BF16 ? 1 : 0};
+    const int row_pitch_in = in_ld > 0 ? in_ld : d;
+    if (plan.tensor_cores) {
+        // the tensor-core kernel also finishes the rows (fold counters at the head of the scratch) whenever the
+        // vectorised finalize applies; odd shapes keep the separate, unaligned finalize kernel
+        auto al16 = [](const void* p) { return reinterpret_cast<uintptr_t>(p) % 16 == 0; };
+        const bool no_fold = !fold_wanted(plan);
+        const bool fused = !no_fold && d % 4 == 0 && row_pitch_in % 4 == 0 && al16(view0) && al16(view1) && al16(dview0) &&
+                           al16(dview1);
+        char* ws = (char*)workspace;
+        float* partial = (float*)(ws + ntx_fold_ctl_bytes(plan.row_blocks));
+        const NtxBwdOut o{view0, view1, dview0, dview1, inv_norm, (unsigned int*)ws, (unsigned int*)(ws + 4),
+                          (unsigned int*)(ws + 64), plan.row_blocks, row_pitch_in, normalised,
+                          in_dtype == NTX_BF16 ? 1 : 0, fused ? 1 : 0};
+        {
+            ProfScope prof(1, st);
+            rc = ntx_tc_bwd_launch((const __nv_bfloat16*)q, (const __nv_bfloat16*)k, dm, plan, wt, partial, ex.gate,
+                                   ex.key_buf_elems, o, st);
+        }
+        if (rc || fused) return rc;
+        return ntx_bwd_finalize_launch(dm, plan, partial, wt, view0, view1, in_dtype, inv_norm, dview0, dview1, st, in_ld,
+                                       normalised);
+    }
+    float* partial = (float*)workspace;
     {
         ProfScope prof(1, st);
-        if (plan.tensor_cores)
-            rc = ntx_tc_bwd_launch((const __nv_bfloat16*)q, (const __nv_bfloat16*)k, dm, plan, wt, partial, ex.gate,
-                                   ex.key_buf_elems, st);
-        else
-            rc = ntx_simt_bwd_launch((const float*)q, (const float*)k, dm, plan, wt, partial, ex.gate,
-                                     ex.key_buf_elems, st);
+        rc = ntx_simt_bwd_launch((const float*)q, (const float*)k, dm, plan, wt, partial, ex.gate, ex.key_buf_elems, st);
     }
     if (rc) return rc;
     return ntx_bwd_finalize_launch(dm, plan, partial, wt, view0, view1, in_dtype, inv_norm, dview0,

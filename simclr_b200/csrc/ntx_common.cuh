@@ -282,6 +282,58 @@ __device__ __forceinline__ void ntx_gate_wait(const uint32_t* ctl, int word, uin
 }
 #endif
 
+// ---------------------------------------------------------------------------
+// finalize work folded into the tensor-core kernels
+// ---------------------------------------------------------------------------
+// The CTAs that share a row block each write a partial into their slot, announce it on the row block's arrival
+// counter, and -- once they have run out of tiles -- wait until the row block is complete and finish an equal
+// share of its rows (slot s of ns takes rows [128 s / ns, 128 (s + 1) / ns)): slots are added in slot order, so
+// the result does not depend on who finishes when.  No second kernel, no launch gap, and the wait is short
+// because the CTAs of a row block own equally long tile ranges that they started together.
+// The counters live at the head of the caller's scratch, which arrives uninitialised: word 0 is a tag.  At kernel
+// start every CTA looks at it; unless it holds NTX_CTR_MAGIC, CTA 0 zeroes the counters and then writes the tag
+// while the others wait for it (all CTAs of these kernels are co-resident, and the first arrival comes a whole
+// tile later).  After that the counters are plain atomicAdd words (a compare-and-swap counter serialises ~150
+// simultaneous arrivals at one L2 round trip each), and the last CTA through a counter stores 0 again, so the next
+// launch -- a replayed CUDA graph included -- starts from clean words and skips the initialisation.
+#define NTX_CTR_MAGIC 0x4E585443u
+struct NtxFoldScratch {
+    unsigned int* tag;                // NTX_CTR_MAGIC once the counters below have been zeroed
+    unsigned int* done_total;         // segments (CTA, row block) finished in this launch
+    unsigned int* arrive;             // [row_blocks]
+    double* seg_loss;                 // forward: loss of each finished share, indexed first_owner(rb) + slot + rb
+    int n_segments;                   // sum over row blocks of their slot counts
+    int row_blocks;
+    int enabled;                      // 0: the kernel only writes its slots (NTXENT_NO_FOLD=1: separate finalize kernel)
+    unsigned int* legacy_ticket;      // the finalize kernel's ticket, zeroed by the main kernel when !enabled
+};
+NTX_HD size_t ntx_fold_ctl_bytes(int row_blocks) { return (64 + (size_t)row_blocks * 4 + 255) & ~(size_t)255; }
+NTX_HD size_t ntx_fold_seg_bytes(int row_blocks, int grid) {
+    return ((size_t)(row_blocks + grid) * 8 + 255) & ~(size_t)255;
+}
+#ifdef __CUDACC__
+__device__ __forceinline__ unsigned int ntx_ld_acquire_gpu(const unsigned int* p) {
+    unsigned int v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+// called by ONE thread of every CTA before the CTA's first arrival
+__device__ __forceinline__ void ntx_fold_init(unsigned int* tag, unsigned int* done_total, unsigned int* arrive,
+                                              int row_blocks, int cta) {
+    // the tag also names how many counters were zeroed: a launch with another number of row blocks starts over
+    const unsigned int want = NTX_CTR_MAGIC + (unsigned int)row_blocks;
+    if (ntx_ld_acquire_gpu(tag) == want) return;
+    if (cta == 0) {
+        *done_total = 0u;
+        for (int i = 0; i < row_blocks; ++i) arrive[i] = 0u;
+        __threadfence();
+        asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(tag), "r"(want) : "memory");
+    } else {
+        while (ntx_ld_acquire_gpu(tag) != want) __nanosleep(64);
+    }
+}
+#endif
+
 // launch helpers implemented per translation unit
 int ntx_l2norm_launch(const void* v0, const void* v1, int n, int d, int in_dtype, void* rows, const NtxPeerOut& peers,
                       size_t keys_off, size_t key_buf_bytes, uint32_t* step_out, int ld, int rows_dtype,
@@ -299,14 +351,36 @@ int ntx_simt_fwd_launch(const float* q, const float* k, const NtxDims& dm, const
 int ntx_simt_bwd_launch(const float* q, const float* k, const NtxDims& dm, const NtxPlan& plan,
                         const NtxWeights& w, float* partial, const NtxGate& gate, size_t key_buf_elems,
                         cudaStream_t st);
+// the full-tile forward finishes its rows itself (no finalize kernel): outputs and fold scratch go in
+struct NtxFwdOut {
+    float* rowsum;
+    float* pos_logit;
+    float* row_loss;
+    float* loss_sum;
+    NtxPeerOut peers;      // world > 0: row sums also into every rank's block, rflag raised at the end
+    size_t rowsum_off;
+};
 int ntx_tc_fwd_launch(const __nv_bfloat16* q, const __nv_bfloat16* k, const NtxDims& dm,
-                      const NtxPlan& plan, float* partial, unsigned int* counter, const NtxGate& gate,
-                      size_t key_buf_elems, cudaStream_t st);
+                      const NtxPlan& plan, float* partial, const NtxFoldScratch& fold, const NtxFwdOut& out,
+                      const NtxGate& gate, size_t key_buf_elems, cudaStream_t st);
 int ntx_tc_fwd_sym_launch(const __nv_bfloat16* rows, const NtxDims& dm, const NtxPlan& plan, float* partial,
                           float* colpart, unsigned int* counter, cudaStream_t st);
+// enabled: the backward kernel finishes its rows itself (dview0 / dview1 written, no finalize kernel)
+struct NtxBwdOut {
+    const void* view0;
+    const void* view1;
+    void* dview0;
+    void* dview1;
+    const float* inv_norm;
+    unsigned int* tag;              // fold counters at the head of the scratch (NtxFoldScratch)
+    unsigned int* done_total;
+    unsigned int* arrive;
+    int row_blocks;
+    int in_ld, normalised, in_bf16, enabled;
+};
 int ntx_tc_bwd_launch(const __nv_bfloat16* q, const __nv_bfloat16* k, const NtxDims& dm,
                       const NtxPlan& plan, const NtxWeights& w, float* partial, const NtxGate& gate,
-                      size_t key_buf_elems, cudaStream_t st);
+                      size_t key_buf_elems, const NtxBwdOut& out, cudaStream_t st);
 int ntx_fwd_finalize_blocks(int q_rows, int ld);   // grid of the forward finalize (one fp64 block sum each)
 // colpart != NULL: symmetric forward (upper-triangle partition, column partials added per row)
 // peers.world > 0: the row sums also go to every rank's block (rowsum_off) and the last block raises rflag

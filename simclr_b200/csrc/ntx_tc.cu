@@ -151,6 +151,17 @@ __device__ __forceinline__ bool edge_tile(int rb, int kt, const NtxDims& dm) {
     return (col0 + 128 > dm.k_rows) || (self_lo <= col0 + 127 && self_lo + 127 >= col0);
 }
 
+// does key tile kt hold the positive column of some row of row block rb?  The positives of rows [r0, r1] are the
+// columns ntx_pos_col(r): consecutive, except where the block straddles the two views (r0 < n_local <= r1).
+__device__ __forceinline__ bool positive_tile(int rb, int kt, const NtxDims& dm) {
+    const int r0 = rb * 128, r1 = min(rb * 128 + 127, dm.q_rows - 1);
+    auto hit = [&](int a, int b) {      // rows a..b on one side of the view boundary
+        return ntx_pos_col(a, dm.n_local, dm.rank) / 128 <= kt && kt <= ntx_pos_col(b, dm.n_local, dm.rank) / 128;
+    };
+    if (r0 < dm.n_local && r1 >= dm.n_local) return hit(r0, dm.n_local - 1) || hit(dm.n_local, r1);
+    return hit(r0, r1);
+}
+
 // S = Q . K^T for one key tile: NDB blocks of 64 features, 4 MMAs (K = 16) per block
 template <int NDB>
 __device__ __forceinline__ void issue_gemm1(uint32_t d_tmem, const uint8_t* q_smem, const uint8_t* k_tile) {
@@ -231,7 +242,9 @@ template <int NDB> struct FwdCfg { static constexpr int NS = NDB == 4 ? 2 : 4; }
 template <int NS> struct FwdCtl {
     uint64_t q_full, q_empty, k_full[NS], k_empty[NS], s_full[kFwdWG], s_empty[kFwdWG];
     uint32_t tmem_base;
+    uint32_t fin_last;                 // finish phase: this CTA took the launch's last segment
     alignas(16) float xch[2][kFwdWG - 1][128];
+    alignas(16) double fin_sum[4];     // finish phase: per-warp loss sums of group 0
 };
 
 template <int NDB>
@@ -239,7 +252,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1)
 tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
               const __grid_constant__ CUtensorMap tmap_q1, const __grid_constant__ CUtensorMap tmap_k1,
               NtxDims dm, int key_tiles, long long T, int rows_pad, float* __restrict__ partial,
-              unsigned int* __restrict__ done_counter, NtxGate gate) {
+              NtxFoldScratch fold, NtxFwdOut out, NtxGate gate) {
     constexpr int NS = FwdCfg<NDB>::NS;
     constexpr uint32_t kTileBytes = NDB * kBlkBytes;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -280,7 +293,6 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     constexpr uint32_t tmem_base = 0;
     // everything above overlapped the tail of the previous kernel on the stream; from here on its results are read
     ntx_dep_wait();
-    if (threadIdx.x == 0 && cta == 0) *done_counter = 0;    // ticket of the finalize kernel
 
     if (warp == kProducerWarp) {
         if (elect_one()) {
@@ -365,11 +377,24 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
                 for (int o = 0; o < kFwdWG - 1; ++o) rs += x[o][row_in_tile];
                 const int slot = cta - ntx_first_owner(T, G, key_tiles, rb);
                 partial[(size_t)slot * rows_pad + rb * 128 + row_in_tile] = rs;
+                // this CTA's part of the row block is out (its positive logits too: the barrier above orders every
+                // group's stores before this thread): announce it
+                if (fold.enabled) {
+                    named_bar_sync(3, 128);
+                    if (threadIdx.x == 0) {
+                        __threadfence();
+                        atomicAdd(fold.arrive + rb, 1u);
+                    }
+                }
             }
             ++flushes;
             acc[0] = acc[1] = acc[2] = acc[3] = 0.f;
         };
 
+        if (threadIdx.x == 0) {
+            if (fold.enabled) ntx_fold_init(fold.tag, fold.done_total, fold.arrive, fold.row_blocks, cta);
+            else if (cta == 0) *fold.legacy_ticket = 0;          // ticket of the finalize kernel
+        }
         int rb = (int)(t_begin / key_tiles), kt = (int)(t_begin % key_tiles);
         int own = 0, turn = 0;
         for (int i = 0; i < n_tiles; ++i) {
@@ -378,8 +403,14 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
                 { NTX_TIC(te_wait); mbar_wait(&ctl->s_full[g], own & 1); NTX_TOC(te_wait); }
                 ++own;
                 tc_fence_after();
-                const bool edge = edge_tile(rb, kt, dm);
+                // tiles that hold a positive column go through the masked path too: the positive logit of a row
+                // is taken from the similarity tile itself (the same MMA value its exponential uses)
+                const bool has_pos = positive_tile(rb, kt, dm);
+                const bool edge = edge_tile(rb, kt, dm) || has_pos;
                 const int self = ntx_self_col(rb * 128 + row_in_tile, dm.n_local, dm.rank);
+                const int my_row = rb * 128 + row_in_tile;
+                const int my_pos = my_row < dm.q_rows ? ntx_pos_col(my_row, dm.n_local, dm.rank) : -1;
+                float pos_val = 0.f;
                 uint32_t v[2][32];
                 tmem_ld_32x32(taddr, v[0]);
 #pragma unroll
@@ -408,10 +439,12 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
                             const int col = kt * 128 + ch * 32 + j;
                             float e = ex2(fmaf(__uint_as_float(v[ch & 1][j]), c1, nc1));
                             if (col == self || col >= dm.k_rows) e = 0.f;   // mask of loss.py:38,46-47
+                            if (col == my_pos) pos_val = __uint_as_float(v[ch & 1][j]);
                             acc[j & 3] += e;
                         }
                     }
                 }
+                if (has_pos && my_pos >= 0 && my_pos / 128 == kt) out.pos_logit[my_row] = pos_val * dm.inv_tau;
             }
             if (last_of_seg) flush(rb);
             if (++kt == key_tiles) { kt = 0; ++rb; }
@@ -419,6 +452,77 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         }
         NTX_TOC(te_total);
         if (threadIdx.x == 0) { NTX_TSAVE(4, te_total); NTX_TSAVE(5, te_wait); }
+
+        // ---------------------------------------------------------------- finish: this CTA's share of its row blocks
+        // (loss.py:54-65: logsumexp - positive per row, then the reduction).  Group 0, one thread per row.
+        if (fold.enabled && g == 0 && n_tiles > 0) {
+            const int rb_first = (int)(t_begin / key_tiles), rb_last = (int)((t_begin + n_tiles - 1) / key_tiles);
+            const int tid = threadIdx.x;                       // 0..127
+            for (int frb = rb_first; frb <= rb_last; ++frb) {
+                const int first = ntx_first_owner(T, G, key_tiles, frb);
+                const int ns = ntx_num_slots(T, G, key_tiles, frb), slot = cta - first;
+                if (tid == 0) {
+                    while (ntx_ld_acquire_gpu(fold.arrive + frb) < (unsigned)ns) __nanosleep(32);
+                }
+                named_bar_sync(3, 128);
+                const int lo = slot * 128 / ns, hi = (slot + 1) * 128 / ns;
+                const int row = frb * 128 + lo + tid;
+                double my_loss = 0.0;
+                if (lo + tid < hi && row < dm.q_rows) {
+                    float R = 0.f;
+                    for (int s0 = 0; s0 < ns; s0 += 8) {       // slot order, eight loads in flight
+                        float t[8];
+#pragma unroll
+                        for (int u = 0; u < 8; ++u)
+                            t[u] = s0 + u < ns ? __ldcg(partial + (size_t)(s0 + u) * rows_pad + row) : 0.f;
+#pragma unroll
+                        for (int u = 0; u < 8; ++u) R += t[u];
+                    }
+                    const float pos = __ldcg(out.pos_logit + row);
+                    const float l = logf(R) + dm.inv_tau - pos;
+                    out.rowsum[row] = R;
+                    out.row_loss[row] = l;
+                    if (out.peers.world > 0)
+                        ntx_peer_st_f32(out.peers, out.rowsum_off + ((size_t)out.peers.rank * dm.q_rows + row) * sizeof(float), R);
+                    my_loss = (double)l;
+                }
+                // the share's loss: lanes, then the four warps, in a fixed order
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) my_loss += __shfl_xor_sync(0xffffffffu, my_loss, o);
+                if (lane == 0) ctl->fin_sum[warp] = my_loss;
+                named_bar_sync(3, 128);
+                if (tid == 0) {
+                    fold.seg_loss[first + slot + frb] = (ctl->fin_sum[0] + ctl->fin_sum[1]) + (ctl->fin_sum[2] + ctl->fin_sum[3]);
+                    __threadfence();
+                    // second pass over the row block's counter: the last CTA out leaves it clean for the next launch
+                    if (atomicAdd(fold.arrive + frb, 1u) == 2u * (unsigned)ns - 1u) fold.arrive[frb] = 0u;
+                    ctl->fin_last = atomicAdd(fold.done_total, 1u) == (unsigned)fold.n_segments - 1u ? 1u : 0u;
+                }
+                named_bar_sync(3, 128);
+                if (ctl->fin_last) {
+                    // every share of every row block is done: add the share losses in (row block, slot) order
+                    __threadfence();
+                    const int row_blocks = (dm.q_rows + 127) / 128;
+                    double part = 0.0;
+                    for (int b = tid; b < row_blocks; b += 128) {
+                        const int f = ntx_first_owner(T, G, key_tiles, b), n2 = ntx_num_slots(T, G, key_tiles, b);
+                        for (int s2 = 0; s2 < n2; ++s2) part += __ldcg(fold.seg_loss + f + s2 + b);
+                    }
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+                    if (lane == 0) ctl->fin_sum[warp] = part;
+                    named_bar_sync(3, 128);
+                    if (tid == 0) {
+                        const double v = (ctl->fin_sum[0] + ctl->fin_sum[1]) + (ctl->fin_sum[2] + ctl->fin_sum[3]);
+                        out.loss_sum[0] = (float)v;                              // reduction="sum"
+                        out.loss_sum[1] = (float)(v / (double)dm.q_rows);        // reduction="mean": sum / N * 0.5, rows = 2N
+                        *fold.done_total = 0u;
+                        if (out.peers.world > 0)                                 // every rank's row sums are out
+                            ntx_raise_flags(out.peers, NTX_CTL_RFLAG, gate.step ? *gate.step : 0u);
+                    }
+                }
+            }
+        }
     }
 
     tc_fence_before();
@@ -793,6 +897,42 @@ struct BwdWeights {
     int w_bf16;         // weights are bf16 values
 };
 
+// The rows of a finished row block, turned into dview0 / dview1 inside the backward kernel (see ntx_common.cuh,
+// "finalize work folded into the tensor-core kernels"): what bwd_finalize_vec_kernel does, with the input dtype a
+// run-time flag.  enabled == 0: the kernel only writes its slots and the separate finalize kernel runs.
+struct BwdFuse {
+    const void* view0;
+    const void* view1;
+    void* dview0;
+    void* dview1;
+    const float* inv_norm;
+    unsigned int* tag;              // fold counters at the head of the scratch (NtxFoldScratch)
+    unsigned int* done_total;
+    unsigned int* arrive;           // [row_blocks]
+    int row_blocks;
+    int in_ld, normalised, in_bf16, d, enabled;
+};
+__device__ __forceinline__ float4 ld4_any(const void* base, size_t i, int bf16) {     // 4 elements from index i
+    if (bf16) {
+        const uint2 t = __ldg(reinterpret_cast<const uint2*>(static_cast<const __nv_bfloat16*>(base) + i));
+        const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&t.x));
+        const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&t.y));
+        return make_float4(a.x, a.y, b.x, b.y);
+    }
+    return __ldg(reinterpret_cast<const float4*>(static_cast<const float*>(base) + i));
+}
+__device__ __forceinline__ void st4_any(void* base, size_t i, float4 v, int bf16) {
+    if (bf16) {
+        __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
+        uint2 t;
+        t.x = *reinterpret_cast<uint32_t*>(&a);
+        t.y = *reinterpret_cast<uint32_t*>(&b);
+        *reinterpret_cast<uint2*>(static_cast<__nv_bfloat16*>(base) + i) = t;
+    } else {
+        *reinterpret_cast<float4*>(static_cast<float*>(base) + i) = v;
+    }
+}
+
 // 32 similarity values of one row -> 32 coefficients, packed bf16x2
 template <bool kEdge>
 __device__ __forceinline__ void coef_chunk(const uint32_t (&v)[32], uint32_t (&pk)[16], const float* bt,
@@ -829,7 +969,7 @@ __global__ void __launch_bounds__(BwdCfg<NDB>::kThreads, 1)
 tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
               const __grid_constant__ CUtensorMap tmap_q1, const __grid_constant__ CUtensorMap tmap_k1,
               NtxDims dm, int key_tiles, long long T, int rows_pad, BwdWeights wt,
-              float* __restrict__ partial, NtxGate gate) {
+              float* __restrict__ partial, NtxGate gate, BwdFuse fuse) {
     using Cfg = BwdCfg<NDB>;
 #ifdef NTX_TIMELINE
     const long long t_entry = clock64();
@@ -995,6 +1135,13 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&ctl->dz_empty);
+            if (fuse.enabled) {          // every group's part of the slot is stored: announce it on the row block
+                named_bar_sync(6, NWG * 128);
+                if (threadIdx.x == 0) {
+                    __threadfence();
+                    atomicAdd(fuse.arrive + rb, 1u);
+                }
+            }
         };
 
         // w_c and R_c of one key are fetched a whole tile ahead (raw: the division waits until the
@@ -1031,6 +1178,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
             }
         };
         int rb = (int)(t_begin / key_tiles), kt = (int)(t_begin % key_tiles);
+        if (fuse.enabled && threadIdx.x == 0) ntx_fold_init(fuse.tag, fuse.done_total, fuse.arrive, fuse.row_blocks, cta);
         int seg = 0, own = 0, turn = 0;
         bool new_seg = true;
         if (g < n_tiles) fetch_beta((kt + g) % key_tiles);
@@ -1094,6 +1242,87 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
 #ifdef NTX_TIMELINE
         if (threadIdx.x == 0) g_ntx_timers[blockIdx.x % 148][2] = clock64() - t_entry;
 #endif
+
+        // ---------------------------------------------------------------- finish: this CTA's share of its row blocks
+        // add the dZ slots in slot order, subtract the positive-pair term, 1/tau, Jacobian of x / max(||x||, eps)
+        // (loss.py:33-34 backward), write dview0 / dview1.  16 threads per row, up to DP / 64 float4 each.
+        if (fuse.enabled && n_tiles > 0) {
+            constexpr int kLanes = 16, kRowsPerPass = NWG * 128 / kLanes, kV = DP / 64;
+            const int tid = threadIdx.x, sub = tid % kLanes;
+            const int n = dm.n_local, d = fuse.d;
+            const size_t slot_stride = (size_t)rows_pad * DP;
+            const int rb_first = (int)(t_begin / key_tiles), rb_last = (int)((t_begin + n_tiles - 1) / key_tiles);
+            for (int frb = rb_first; frb <= rb_last; ++frb) {
+                const int first = ntx_first_owner(T, G, key_tiles, frb);
+                const int ns = ntx_num_slots(T, G, key_tiles, frb), slot = cta - first;
+                if (tid == 0) {
+                    while (ntx_ld_acquire_gpu(fuse.arrive + frb) < (unsigned)ns) __nanosleep(32);
+                }
+                named_bar_sync(6, NWG * 128);
+                const int lo = slot * 128 / ns, hi = (slot + 1) * 128 / ns;
+                for (int r0 = lo; r0 < hi; r0 += kRowsPerPass) {
+                    const int rl = r0 + tid / kLanes;
+                    const bool live = rl < hi && frb * 128 + rl < dm.q_rows;
+                    const int r = min(frb * 128 + min(rl, hi - 1), dm.q_rows - 1);   // keep every lane in the shuffles
+                    const int p = ntx_pos_row(r, n);
+                    const void* zr_base = r < n ? fuse.view0 : fuse.view1;
+                    const void* zp_base = p < n ? fuse.view0 : fuse.view1;
+                    const size_t zr_off = (size_t)(r < n ? r : r - n) * fuse.in_ld, zp_off = (size_t)(p < n ? p : p - n) * fuse.in_ld;
+                    const float inr = __ldg(fuse.inv_norm + r), inp = __ldg(fuse.inv_norm + p);
+                    const float sr = fuse.normalised ? 1.f : inr, sp = fuse.normalised ? 1.f : inp;
+                    const float wpair = (ntx_ld_weight(wt.w_q, (size_t)r * wt.w_stride, wt.w_bf16) +
+                                         ntx_ld_weight(wt.w_q, (size_t)p * wt.w_stride, wt.w_bf16)) * wt.w_scale;
+                    const float* part = partial + (size_t)r * DP;
+                    float4 gq[kV], zh[kV];
+                    float proj = 0.f;
+#pragma unroll
+                    for (int v = 0; v < kV; ++v) {
+                        const int c = (sub + v * kLanes) * 4;
+                        if (c < d) {
+                            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+                            for (int s0 = 0; s0 < ns; s0 += 4) {           // slot order, four loads in flight
+                                float4 t[4];
+#pragma unroll
+                                for (int u = 0; u < 4; ++u)
+                                    t[u] = s0 + u < ns ? __ldcg(reinterpret_cast<const float4*>(part + (s0 + u) * slot_stride + c))
+                                                       : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                                for (int u = 0; u < 4; ++u) { acc.x += t[u].x; acc.y += t[u].y; acc.z += t[u].z; acc.w += t[u].w; }
+                            }
+                            const float4 zpv = ld4_any(zp_base, zp_off + c, fuse.in_bf16);
+                            const float4 zrv = ld4_any(zr_base, zr_off + c, fuse.in_bf16);
+                            const float k = wpair * sp, it = dm.inv_tau;
+                            gq[v] = make_float4((acc.x - k * zpv.x) * it, (acc.y - k * zpv.y) * it, (acc.z - k * zpv.z) * it,
+                                                (acc.w - k * zpv.w) * it);
+                            zh[v] = make_float4(zrv.x * sr, zrv.y * sr, zrv.z * sr, zrv.w * sr);
+                            proj = fmaf(zh[v].x, gq[v].x, fmaf(zh[v].y, gq[v].y, fmaf(zh[v].z, gq[v].z, fmaf(zh[v].w, gq[v].w, proj))));
+                        }
+                    }
+#pragma unroll
+                    for (int o = kLanes >> 1; o > 0; o >>= 1) proj += __shfl_xor_sync(0xffffffffu, proj, o);
+                    const bool clamped = inr >= 1e12f;    // ||z|| <= eps: denominator was the constant eps
+                    void* out_base = r < n ? fuse.dview0 : fuse.dview1;
+                    const size_t out_off = (size_t)(r < n ? r : r - n) * d;
+#pragma unroll
+                    for (int v = 0; v < kV; ++v) {
+                        const int c = (sub + v * kLanes) * 4;
+                        if (c < d && live) {
+                            float4 o4;
+                            if (clamped) {
+                                o4 = make_float4(gq[v].x * inr, gq[v].y * inr, gq[v].z * inr, gq[v].w * inr);
+                            } else {
+                                o4 = make_float4((gq[v].x - zh[v].x * proj) * inr, (gq[v].y - zh[v].y * proj) * inr,
+                                                 (gq[v].z - zh[v].z * proj) * inr, (gq[v].w - zh[v].w * proj) * inr);
+                            }
+                            st4_any(out_base, out_off + c, o4, fuse.in_bf16);
+                        }
+                    }
+                }
+                // second pass over the row block's counter: the last CTA out leaves it clean for the next launch
+                named_bar_sync(6, NWG * 128);
+                if (tid == 0 && atomicAdd(fuse.arrive + frb, 1u) == 2u * (unsigned)ns - 1u) fuse.arrive[frb] = 0u;
+            }
+        }
     }
 
     tc_fence_before();
@@ -1185,31 +1414,32 @@ int make_row_maps(RowMaps* m, const __nv_bfloat16* q, const __nv_bfloat16* k, co
 }
 
 template <int NDB>
-int launch_fwd(const RowMaps& m, const NtxDims& dm, const NtxPlan& plan, float* partial, unsigned int* counter,
-               const NtxGate& gate, cudaStream_t st) {
+int launch_fwd(const RowMaps& m, const NtxDims& dm, const NtxPlan& plan, float* partial, const NtxFoldScratch& fold,
+               const NtxFwdOut& out, const NtxGate& gate, cudaStream_t st) {
     const size_t smem = fwd_smem_bytes<NDB>();
     NTX_SMEM_OPT_IN(tc_fwd_kernel<NDB>, smem);
     const long long T = (long long)plan.row_blocks * plan.key_tiles;
     NTX_CUDA(ntx_launch_dep(tc_fwd_kernel<NDB>, plan.grid, kFwdThreads, smem, st, m.q[0], m.k[0], m.q[1], m.k[1], dm,
-                            plan.key_tiles, T, plan.row_blocks * plan.tile_rows, partial, counter, gate));
+                            plan.key_tiles, T, plan.row_blocks * plan.tile_rows, partial, fold, out, gate));
     return NTX_OK;
 }
 
 template <int NDB, bool kGate>
 int launch_bwd_g(const RowMaps& m, const NtxDims& dm, const NtxPlan& plan, const BwdWeights& wt, float* partial,
-                 const NtxGate& gate, cudaStream_t st) {
+                 const NtxGate& gate, const BwdFuse& fuse, cudaStream_t st) {
     const size_t smem = bwd_smem_bytes<NDB>();
     NTX_SMEM_OPT_IN((tc_bwd_kernel<NDB, kGate>), smem);
     const long long T = (long long)plan.row_blocks * plan.key_tiles;
     NTX_CUDA(ntx_launch_dep(tc_bwd_kernel<NDB, kGate>, plan.grid, BwdCfg<NDB>::kThreads, smem, st, m.q[0], m.k[0],
-                            m.q[1], m.k[1], dm, plan.key_tiles, T, plan.row_blocks * plan.tile_rows, wt, partial, gate));
+                            m.q[1], m.k[1], dm, plan.key_tiles, T, plan.row_blocks * plan.tile_rows, wt, partial, gate,
+                            fuse));
     return NTX_OK;
 }
 template <int NDB>
 int launch_bwd(const RowMaps& m, const NtxDims& dm, const NtxPlan& plan, const BwdWeights& wt, float* partial,
-               const NtxGate& gate, cudaStream_t st) {
-    return gate.step ? launch_bwd_g<NDB, true>(m, dm, plan, wt, partial, gate, st)
-                     : launch_bwd_g<NDB, false>(m, dm, plan, wt, partial, gate, st);
+               const NtxGate& gate, const BwdFuse& fuse, cudaStream_t st) {
+    return gate.step ? launch_bwd_g<NDB, true>(m, dm, plan, wt, partial, gate, fuse, st)
+                     : launch_bwd_g<NDB, false>(m, dm, plan, wt, partial, gate, fuse, st);
 }
 
 }  // namespace
@@ -1226,15 +1456,15 @@ extern "C" int ntx_debug_timers(long long* host_out) {   // 148 x 16 cycle count
 #endif
 
 int ntx_tc_fwd_launch(const __nv_bfloat16* q, const __nv_bfloat16* k, const NtxDims& dm,
-                      const NtxPlan& plan, float* partial, unsigned int* counter, const NtxGate& gate,
-                      size_t key_buf_elems, cudaStream_t st) {
+                      const NtxPlan& plan, float* partial, const NtxFoldScratch& fold, const NtxFwdOut& out,
+                      const NtxGate& gate, size_t key_buf_elems, cudaStream_t st) {
     RowMaps m;
     int rc = make_row_maps(&m, q, k, dm, gate, key_buf_elems);
     if (rc) return rc;
     switch (plan.d_pad) {
-        case 64: return launch_fwd<1>(m, dm, plan, partial, counter, gate, st);
-        case 128: return launch_fwd<2>(m, dm, plan, partial, counter, gate, st);
-        case 256: return launch_fwd<4>(m, dm, plan, partial, counter, gate, st);
+        case 64: return launch_fwd<1>(m, dm, plan, partial, fold, out, gate, st);
+        case 128: return launch_fwd<2>(m, dm, plan, partial, fold, out, gate, st);
+        case 256: return launch_fwd<4>(m, dm, plan, partial, fold, out, gate, st);
     }
     ntx_set_error("tensor-core forward: padded feature dim %d not built", plan.d_pad);
     return NTX_E_UNSUPPORTED;
@@ -1267,15 +1497,17 @@ int ntx_tc_fwd_sym_launch(const __nv_bfloat16* rows, const NtxDims& dm, const Nt
 
 int ntx_tc_bwd_launch(const __nv_bfloat16* q, const __nv_bfloat16* k, const NtxDims& dm,
                       const NtxPlan& plan, const NtxWeights& w, float* partial, const NtxGate& gate,
-                      size_t key_buf_elems, cudaStream_t st) {
+                      size_t key_buf_elems, const NtxBwdOut& o, cudaStream_t st) {
     RowMaps m;
     int rc = make_row_maps(&m, q, k, dm, gate, key_buf_elems);
     if (rc) return rc;
     BwdWeights wt{w.rowsum_q, w.rowsum_k, w.w_q, w.w_k, w.w_stride, w.w_scale, w.w_chunk, w.w_bf16};
+    const BwdFuse fuse{o.view0, o.view1, o.dview0, o.dview1, o.inv_norm, o.tag, o.done_total, o.arrive, o.row_blocks,
+                       o.in_ld, o.normalised, o.in_bf16, dm.d, o.enabled};
     switch (plan.d_pad) {
-        case 64: return launch_bwd<1>(m, dm, plan, wt, partial, gate, st);
-        case 128: return launch_bwd<2>(m, dm, plan, wt, partial, gate, st);
-        case 256: return launch_bwd<4>(m, dm, plan, wt, partial, gate, st);
+        case 64: return launch_bwd<1>(m, dm, plan, wt, partial, gate, fuse, st);
+        case 128: return launch_bwd<2>(m, dm, plan, wt, partial, gate, fuse, st);
+        case 256: return launch_bwd<4>(m, dm, plan, wt, partial, gate, fuse, st);
     }
     ntx_set_error("tensor-core backward: padded feature dim %d not built", plan.d_pad);
     return NTX_E_UNSUPPORTED;

@@ -72,7 +72,7 @@ def test_plan_partition_is_exact(q_rows, k_rows, d, dtype, sms):
     assert p.max_slots == slots
     rows_pad = p.row_blocks * p.tile_rows
     assert p.fwd_ws_bytes >= slots * rows_pad * 4 + 16      # + the finalize kernel's ticket and block sums
-    assert p.bwd_ws_bytes == slots * rows_pad * p.d_pad * 4
+    assert p.bwd_ws_bytes >= slots * rows_pad * p.d_pad * 4       # + the fold counters of the tensor-core kernel
     assert p.tensor_cores == (1 if dtype == torch.bfloat16 else 0)
 
 

@@ -458,7 +458,9 @@ def test_symmetric_forward_matches_full_tile_forward_and_oracle(n, d, tau, dev):
         outs.append((out.cpu().numpy(), out_sum.cpu().numpy()))
     (sym, sym_sum), (full, full_sum) = outs
     assert np.isfinite(sym).all() and np.isfinite(full).all()
-    assert np.array_equal(sym[1], full[1])                                # positive logits: same arithmetic
+    # positive logits: a direct fp32 dot of the two bf16 rows (finalize kernel) against the tensor core's fp32
+    # accumulation of the same products (taken from the similarity tile): equal up to summation order
+    assert rel_err(sym[1], full[1]) < 1e-5
     assert rel_err(sym[0], full[0]) < 4e-3                                # row sums: bf16 column contributions
     assert rel_err(sym[2], full[2]) < 4e-3
     ref = orc.ntxent_rows_fp64(a.float().numpy(), b.float().numpy(), tau, weights=orc.weights_for("mean", n))
