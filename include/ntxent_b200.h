@@ -46,6 +46,12 @@ extern "C" {
 #define NTX_E_CUDA (-3)      /* a CUDA runtime / driver call failed */
 #define NTX_E_UNSUPPORTED (-4)
 
+/* Below this temperature the fixed-shift logsumexp of the fast kernels (exp(s - 1/tau), |cos| <= 1) would leave fp32
+ * range.  fp32 rows then run a max-shifted form (two exponentials per logit in backward) and the "rowsum" vectors of
+ * ntx_fwd / ntx_bwd hold lse_r = log sum_{c != r} exp(s_rc) instead of sum exp(s_rc - 1/tau); bf16 rows are refused
+ * with NTX_E_UNSUPPORTED (the module switches to fp32 rows by itself).  The reference accepts any tau > 0 (loss.py:16). */
+#define NTX_MIN_TEMPERATURE 0.0235f
+
 /* Where this rank's rows sit among the keys.
  * n_local : pairs held by this rank (N of loss.py:36 when world == 1)
  * world   : number of ranks whose rows form the keys (1 = the reference's local loss)

@@ -84,26 +84,32 @@ int make_dims(int q_rows, int k_rows, int d, int ld, int dtype, const NtxLayout*
     NTX_CHECK_ARG(ld == ntx_row_pitch(d, dtype), "ld=%d must be ntx_row_pitch(d=%d)=%d", ld, d,
                   ntx_row_pitch(d, dtype));
     NTX_CHECK_ARG(temperature > 0.f, "temperature must be positive (loss.py:16)");
-    NTX_CHECK_ARG(temperature >= NTX_MIN_TEMPERATURE,
-                  "temperature %g is below %g: the fixed-shift logsumexp would underflow fp32",
-                  (double)temperature, (double)NTX_MIN_TEMPERATURE);
+    if (temperature < NTX_MIN_TEMPERATURE && dtype == NTX_BF16) {
+        ntx_set_error("temperature %g is below %g: the tensor-core kernels' fixed-shift logsumexp would leave fp32 "
+                      "range; use fp32 rows, whose kernels switch to a max-shifted form",
+                      (double)temperature, (double)NTX_MIN_TEMPERATURE);
+        return NTX_E_UNSUPPORTED;
+    }
     int rc = check_layout(L, q_rows, k_rows);
     if (rc) return rc;
     dm->q_rows = q_rows; dm->k_rows = k_rows; dm->d = d; dm->ld = ld;
     dm->n_local = L->n_local; dm->rank = L->rank;
     dm->inv_tau = 1.0f / temperature;
     dm->c1 = NTX_LOG2E / temperature;
+    dm->stable = temperature < NTX_MIN_TEMPERATURE ? 1 : 0;
     return NTX_OK;
 }
 
-// do the tensor-core kernels finish their rows themselves?  (see fwd_impl)
+// Do the tensor-core kernels finish their rows themselves (see fwd_impl)?  Opt-in, NTXENT_FOLD=1: the folded form
+// makes the CTAs of one launch wait for each other, which is only safe while the whole grid is resident (it is on
+// a GPU of its own; an MPS share or green context with fewer SMs than the device reports would stall it), and it
+// pays only where many CTAs share a row block.
 bool fold_wanted(const NtxPlan& plan) {
-    static const int forced = [] {
+    static const bool on = [] {
         const char* e = getenv("NTXENT_FOLD");
-        return e && e[0] ? (e[0] != '0' ? 1 : 0) : -1;
+        return e && e[0] && e[0] != '0';
     }();
-    if (forced >= 0) return forced == 1;
-    return plan.max_slots >= 7;
+    return on && plan.max_slots >= 2;
 }
 
 int aligned16(const void* p, const char* what) {
@@ -176,7 +182,9 @@ int ntx_plan(int q_rows, int k_rows, int d, int dtype, int sm_count, NtxPlan* pl
     // finishes its rows itself, or the finalize kernel's ticket and one fp64 block sum per finalize block
     const uint64_t fin_bytes = 16 + (((uint64_t)ntx_fwd_finalize_blocks(q_rows, ntx_row_pitch(d, dtype)) * 8 + 15) & ~15ull);
     const uint64_t fold_bytes = ntx_fold_ctl_bytes(plan->row_blocks) + ntx_fold_seg_bytes(plan->row_blocks, plan->grid);
-    plan->fwd_ws_bytes_min = (uint64_t)max_slots * rows_pad * sizeof(float) + fin_bytes + (plan->tensor_cores ? fold_bytes : 0);
+    // fp32 rows: a slot entry may be a (max, sum) pair (temperatures below NTX_MIN_TEMPERATURE)
+    plan->fwd_ws_bytes_min = (uint64_t)max_slots * rows_pad * (plan->tensor_cores ? sizeof(float) : 2 * sizeof(float)) +
+                             fin_bytes + (plan->tensor_cores ? fold_bytes : 0);
     plan->fwd_ws_bytes = plan->fwd_ws_bytes_min;
     plan->bwd_ws_bytes = (uint64_t)max_slots * rows_pad * plan->d_pad * sizeof(float) +
                          (plan->tensor_cores ? ntx_fold_ctl_bytes(plan->row_blocks) : 0);
@@ -266,11 +274,12 @@ int fwd_impl(const void* q, const void* k, int q_rows, int k_rows, int d, int ld
     const bool sym = plan.fwd_symmetric && q == k && layout->world == 1 && workspace_bytes >= plan.fwd_ws_bytes;
     const uint64_t rows_pad = (uint64_t)plan.row_blocks * plan.tile_rows;
     if (plan.tensor_cores && !sym) {
-        // full-tile tensor-core forward.  When many CTAs share a row block (a small shard of a large key set: one of
-        // 8 ranks at config 4 has 9 per row block) the kernel finishes the rows itself, each CTA a small share
-        // (NtxFoldScratch at the head of the scratch): measured 82 against 88 us per step of the 1-of-8 shapes.  With
-        // few CTAs per row block the shares are large and the separate, fully occupied finalize kernel is faster
-        // (1 GPU: 220 against 226 us).  NTXENT_FOLD=1 / 0 forces the choice.
+        // full-tile tensor-core forward.  With NTXENT_FOLD=1 the kernel finishes the rows itself, each CTA of a row
+        // block a share of its rows (NtxFoldScratch at the head of the scratch).  Measured on B200, eager launches of
+        // one rank's shapes at config 4: 82 against 88 us per step for 1 of 8 ranks (9 CTAs per row block, 14-row
+        // shares), equal for 1 of 4, 168 against 164 us for 1 of 2 and 226 against 220 us on one GPU, where the
+        // shares are large and the separate, fully occupied finalize kernel is faster; 83.3 against 85.0 us per
+        // step in the 8-GPU bench.  Default: the separate finalize kernel.
         const bool no_fold = !fold_wanted(plan);
         char* ws = (char*)workspace;
         const uint64_t head = ntx_fold_ctl_bytes(plan.row_blocks) + ntx_fold_seg_bytes(plan.row_blocks, plan.grid);
@@ -297,7 +306,8 @@ int fwd_impl(const void* q, const void* k, int q_rows, int k_rows, int d, int ld
         return ntx_fwd_finalize_launch(q, dtype, dm, plan, partial, nullptr, counter, block_sums, rowsum, pos_logit,
                                        row_loss, loss_sum, ex.out, ex.geom.rowsum_off, ex.gate, ex.key_buf_elems, st);
     }
-    const uint64_t partial_bytes = (uint64_t)(sym ? plan.fwd_max_slots : plan.max_slots) * rows_pad * sizeof(float);
+    const uint64_t partial_bytes = (uint64_t)(sym ? plan.fwd_max_slots : plan.max_slots) * rows_pad *
+                                   (plan.tensor_cores ? sizeof(float) : 2 * sizeof(float));
     const uint64_t fin_bytes = 16 + (((uint64_t)ntx_fwd_finalize_blocks(q_rows, ld) * 8 + 15) & ~15ull);
     float* partial = (float*)workspace;
     unsigned int* counter = (unsigned int*)((char*)workspace + partial_bytes);

@@ -126,14 +126,15 @@ inline cudaError_t ntx_launch_dep(void (*kernel)(KArgs...), dim3 grid, dim3 bloc
 // log2(e) / tau and friends live in one place so every kernel shifts identically:
 // e_rc = exp(s_rc - 1/tau) = exp2(dot_rc * c1 - c1),  c1 = log2(e) / tau.
 #define NTX_LOG2E 1.4426950408889634f
-// exp2 argument range is [-2*c1, 0]; keep it inside fp32 normal range.
-#define NTX_MIN_TEMPERATURE 0.0235f
+// exp2 argument range is [-2*c1, 0]: NTX_MIN_TEMPERATURE (public header) keeps it inside fp32 normal range.
 
 struct NtxDims {
     int q_rows, k_rows, d, ld;
     int n_local, rank;
     float c1;        // log2e / tau
     float inv_tau;
+    int stable;      // temperature below NTX_MIN_TEMPERATURE (fp32 rows only): max-shifted logsumexp, and the
+                     // "rowsum" vectors hold lse_r = log sum_c exp(s_rc) instead of sum_c exp(s_rc - 1/tau)
 };
 
 // Backward weights: alpha_r = w_q[r*stride]*scale / rowsum_q[r],  beta_c = w_k[c*stride]*scale / rowsum_k[c]

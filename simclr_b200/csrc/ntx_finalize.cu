@@ -96,8 +96,24 @@ fwd_finalize_kernel(const T* __restrict__ q, NtxDims dm, int lanes, int tile_row
             return acc;
         };
         float c = 0.f;
-        if (colpart) c = strided_sum(colpart, r2 / tile_rows);   // symmetric forward: what the tiles ABOVE this row's block saw in this row's column
-        c += strided_sum(partial, ns_sh);
+        if (dm.stable) {
+            // max-shifted form (small temperatures, fp32 rows): a slot holds (max, sum of exp2(x - max)); merged by
+            // one thread per row into lse in log2 units, the other parts add nothing
+            if (part == 0) {
+                const float2* p2 = reinterpret_cast<const float2*>(partial);
+                float M = -INFINITY;
+                for (int sl = 0; sl < ns_sh; ++sl) M = fmaxf(M, p2[(size_t)sl * rows_pad + r2].x);
+                float S = 0.f;
+                for (int sl = 0; sl < ns_sh; ++sl) {
+                    const float2 t = p2[(size_t)sl * rows_pad + r2];
+                    if (t.x > -INFINITY) S += t.y * exp2f(t.x - M);
+                }
+                c = M + log2f(S);
+            }
+        } else {
+            if (colpart) c = strided_sum(colpart, r2 / tile_rows);   // symmetric forward: what the tiles ABOVE this row's block saw in this row's column
+            c += strided_sum(partial, ns_sh);
+        }
         rs_sh[part * rows_per_block + row_local] = c;
     }
     __syncthreads();
@@ -119,7 +135,13 @@ fwd_finalize_kernel(const T* __restrict__ q, NtxDims dm, int lanes, int tile_row
             float R = 0.f;
             for (int part = 0; part < lanes; ++part) R += rs_sh[part * rows_per_block + threadIdx.x / lanes];
             const float pos = dot * dm.inv_tau;
-            const float l = logf(R) + dm.inv_tau - pos;
+            float l;
+            if (dm.stable) {
+                R *= 0.6931471805599453f;                    // lse_r in natural-log units: what "rowsum" holds in this mode
+                l = R - pos;
+            } else {
+                l = logf(R) + dm.inv_tau - pos;
+            }
             rowsum[r] = R;
             pos_logit[r] = pos;
             row_loss[r] = l;

@@ -88,6 +88,10 @@ __device__ __forceinline__ size_t simt_gate(const NtxGate& gate, bool backward, 
     return (step_sh & 1u) ? key_buf_elems : 0;
 }
 
+// kStable (temperature below NTX_MIN_TEMPERATURE): the fixed shift 1/tau would push every term of a row out of fp32
+// range, so each thread keeps a running maximum with its sum (log2 domain) and a slot holds the pair (max, sum);
+// the finalize kernel merges the pairs into lse_r.  Same tiles, same masks; one more max / rescale per tile.
+template <bool kStable>
 __global__ void __launch_bounds__(NT)
 simt_fwd_kernel(const float* __restrict__ q, const float* __restrict__ k, NtxDims dm, int key_tiles,
                 long long T, int rows_pad, float* __restrict__ partial,
@@ -106,16 +110,29 @@ simt_fwd_kernel(const float* __restrict__ q, const float* __restrict__ k, NtxDim
 
     int cur_rb = -1;
     float rowsum[4] = {0.f, 0.f, 0.f, 0.f};
+    float rowmax[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};      // kStable only
     auto flush = [&](int rb) {
         const int slot = cta - ntx_first_owner(T, G, key_tiles, rb);
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             float v = rowsum[i];
-            v += __shfl_xor_sync(0xffffffffu, v, 1);
-            v += __shfl_xor_sync(0xffffffffu, v, 2);
-            v += __shfl_xor_sync(0xffffffffu, v, 4);
-            v += __shfl_xor_sync(0xffffffffu, v, 8);
-            if (tx == 0) partial[(size_t)slot * rows_pad + rb * BM + ty * 4 + i] = v;
+            if constexpr (kStable) {
+                float m = rowmax[i];
+#pragma unroll
+                for (int o = 1; o < 16; o <<= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+                v = rowmax[i] == -INFINITY ? 0.f : v * exp2f(rowmax[i] - m);
+#pragma unroll
+                for (int o = 1; o < 16; o <<= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                if (tx == 0)
+                    reinterpret_cast<float2*>(partial)[(size_t)slot * rows_pad + rb * BM + ty * 4 + i] = make_float2(m, v);
+                rowmax[i] = -INFINITY;
+            } else {
+                v += __shfl_xor_sync(0xffffffffu, v, 1);
+                v += __shfl_xor_sync(0xffffffffu, v, 2);
+                v += __shfl_xor_sync(0xffffffffu, v, 4);
+                v += __shfl_xor_sync(0xffffffffu, v, 8);
+                if (tx == 0) partial[(size_t)slot * rows_pad + rb * BM + ty * 4 + i] = v;
+            }
             rowsum[i] = 0.f;
         }
     };
@@ -131,18 +148,39 @@ simt_fwd_kernel(const float* __restrict__ q, const float* __restrict__ k, NtxDim
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const int self = ntx_self_col(rb * BM + ty * 4 + i, dm.n_local, dm.rank);
+            if constexpr (kStable) {
+                float x[4], tmax = -INFINITY;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const int col = kt * BN + tx * 4 + j;
-                float e = exp2f(fmaf(acc[i][j], dm.c1, -dm.c1));
-                if (col == self || col >= dm.k_rows) e = 0.f;   // mask of loss.py:38,46-47
-                rowsum[i] += e;
+                for (int j = 0; j < 4; ++j) {
+                    const int col = kt * BN + tx * 4 + j;
+                    x[j] = (col == self || col >= dm.k_rows) ? -INFINITY : acc[i][j] * dm.c1;   // mask of loss.py:38,46-47
+                    tmax = fmaxf(tmax, x[j]);
+                }
+                if (tmax > -INFINITY) {
+                    const float mnew = fmaxf(rowmax[i], tmax);
+                    float sum = rowsum[i] * exp2f(rowmax[i] - mnew);          // exp2(-inf) = 0 on the first tile
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) sum += exp2f(x[j] - mnew);
+                    rowsum[i] = sum;
+                    rowmax[i] = mnew;
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int col = kt * BN + tx * 4 + j;
+                    float e = exp2f(fmaf(acc[i][j], dm.c1, -dm.c1));
+                    if (col == self || col >= dm.k_rows) e = 0.f;   // mask of loss.py:38,46-47
+                    rowsum[i] += e;
+                }
             }
         }
     }
     if (cur_rb >= 0) flush(cur_rb);
 }
 
+// kStable: the row sums arrive as lse_r (see simt_fwd_kernel): C_rc = w_r exp(s_rc - lse_r) + w_c exp(s_rc - lse_c),
+// two exponentials per logit instead of one, neither of which can overflow (s_rc <= lse_r and s_rc <= lse_c)
+template <bool kStable>
 __global__ void __launch_bounds__(NT)
 simt_bwd_kernel(const float* __restrict__ q, const float* __restrict__ k, NtxDims dm, int key_tiles,
                 long long T, int rows_pad, int d_pad, NtxWeights wt, float* __restrict__ partial, NtxGate gate,
@@ -193,22 +231,38 @@ simt_bwd_kernel(const float* __restrict__ q, const float* __restrict__ k, NtxDim
 
         // coefficient tile  C_rc = e_rc * (w_r/R_r + w_c/R_c), zero on self / out-of-range
         float alpha[4], beta[4];
+        float alpha_l[4] = {0.f, 0.f, 0.f, 0.f}, beta_l[4] = {0.f, 0.f, 0.f, 0.f};   // kStable: lse of rows / keys, log2 units
         int self[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const int r = rb * BM + ty * 4 + i;
-            alpha[i] = r < dm.q_rows
-                           ? ntx_ld_weight(wt.w_q, (size_t)r * wt.w_stride, wt.w_bf16) * wt.w_scale / __ldg(wt.rowsum_q + r)
-                           : 0.f;
+            if constexpr (kStable) {
+                alpha[i] = r < dm.q_rows ? ntx_ld_weight(wt.w_q, (size_t)r * wt.w_stride, wt.w_bf16) * wt.w_scale : 0.f;
+                alpha_l[i] = r < dm.q_rows ? __ldg(wt.rowsum_q + r) * NTX_LOG2E : 0.f;
+            } else {
+                alpha[i] = r < dm.q_rows
+                               ? ntx_ld_weight(wt.w_q, (size_t)r * wt.w_stride, wt.w_bf16) * wt.w_scale / __ldg(wt.rowsum_q + r)
+                               : 0.f;
+            }
             self[i] = ntx_self_col(r, dm.n_local, dm.rank);
         }
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const int c = kt * BN + tx * 4 + j;
             const size_t wi = ntx_key_weight_index(c, wt.w_stride, wt.w_chunk);
-            if (c >= dm.k_rows) beta[j] = 0.f;
-            else if (gate.step) beta[j] = ntx_ld_weight(wt.w_k, wi, wt.w_bf16, true) * wt.w_scale / ntx_ld_l2(wt.rowsum_k + c);   // written by peers
-            else beta[j] = ntx_ld_weight(wt.w_k, wi, wt.w_bf16) * wt.w_scale / __ldg(wt.rowsum_k + c);
+            if (c >= dm.k_rows) {
+                beta[j] = 0.f;
+            } else {
+                // with a peer exchange both values were written by other ranks during the step: skip L1
+                const float wv = gate.step ? ntx_ld_weight(wt.w_k, wi, wt.w_bf16, true) : ntx_ld_weight(wt.w_k, wi, wt.w_bf16);
+                const float rv = gate.step ? ntx_ld_l2(wt.rowsum_k + c) : __ldg(wt.rowsum_k + c);
+                if constexpr (kStable) {
+                    beta[j] = wv * wt.w_scale;
+                    beta_l[j] = rv * NTX_LOG2E;
+                } else {
+                    beta[j] = wv * wt.w_scale / rv;
+                }
+            }
         }
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -216,9 +270,15 @@ simt_bwd_kernel(const float* __restrict__ q, const float* __restrict__ k, NtxDim
             float cv[4];
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-                float e = exp2f(fmaf(acc[i][j], dm.c1, -dm.c1));
-                if (col == self[i] || col >= dm.k_rows || rb * BM + ty * 4 + i >= dm.q_rows) e = 0.f;
-                cv[i] = e * (alpha[i] + beta[j]);
+                const bool masked = col == self[i] || col >= dm.k_rows || rb * BM + ty * 4 + i >= dm.q_rows;
+                if constexpr (kStable) {
+                    const float x = acc[i][j] * dm.c1;
+                    cv[i] = masked ? 0.f : alpha[i] * exp2f(x - alpha_l[i]) + beta[j] * exp2f(x - beta_l[j]);
+                } else {
+                    float e = exp2f(fmaf(acc[i][j], dm.c1, -dm.c1));
+                    if (masked) e = 0.f;
+                    cv[i] = e * (alpha[i] + beta[j]);
+                }
             }
             *reinterpret_cast<float4*>(&Ct[tx * 4 + j][ty * 4]) = make_float4(cv[0], cv[1], cv[2], cv[3]);
         }
@@ -264,8 +324,12 @@ int ntx_simt_fwd_launch(const float* q, const float* k, const NtxDims& dm, const
     const long long T = (long long)plan.row_blocks * plan.key_tiles;
     const int rows_pad = plan.row_blocks * plan.tile_rows;
     ntx_note_launch();
-    simt_fwd_kernel<<<plan.grid, NT, 0, st>>>(q, k, dm, plan.key_tiles, T, rows_pad, partial, counter, gate,
-                                              key_buf_elems);
+    if (dm.stable)
+        simt_fwd_kernel<true><<<plan.grid, NT, 0, st>>>(q, k, dm, plan.key_tiles, T, rows_pad, partial, counter, gate,
+                                                        key_buf_elems);
+    else
+        simt_fwd_kernel<false><<<plan.grid, NT, 0, st>>>(q, k, dm, plan.key_tiles, T, rows_pad, partial, counter, gate,
+                                                         key_buf_elems);
     NTX_CUDA(cudaGetLastError());
     return NTX_OK;
 }
@@ -277,8 +341,12 @@ int ntx_simt_bwd_launch(const float* q, const float* k, const NtxDims& dm, const
     const int rows_pad = plan.row_blocks * plan.tile_rows;
     dim3 grid(plan.grid, (plan.d_pad + BD - 1) / BD);
     ntx_note_launch();
-    simt_bwd_kernel<<<grid, NT, 0, st>>>(q, k, dm, plan.key_tiles, T, rows_pad, plan.d_pad, wt, partial, gate,
-                                         key_buf_elems);
+    if (dm.stable)
+        simt_bwd_kernel<true><<<grid, NT, 0, st>>>(q, k, dm, plan.key_tiles, T, rows_pad, plan.d_pad, wt, partial, gate,
+                                                   key_buf_elems);
+    else
+        simt_bwd_kernel<false><<<grid, NT, 0, st>>>(q, k, dm, plan.key_tiles, T, rows_pad, plan.d_pad, wt, partial, gate,
+                                                    key_buf_elems);
     NTX_CUDA(cudaGetLastError());
     return NTX_OK;
 }

@@ -22,6 +22,7 @@ import torch.distributed as dist
 
 from . import _cabi, peer_exchange
 
+MIN_TC_TEMPERATURE = 0.0235         # NTX_MIN_TEMPERATURE of the library: below it only fp32 rows are served
 _backend = _cabi.Backend()          # tests may swap in a stand-in with the same methods
 _workspaces: dict = {}
 _shapes: dict = {}
@@ -243,9 +244,9 @@ class NT_Xent(torch.nn.Module):
                  process_group=None, compute_dtype: torch.dtype | None = None,
                  gather_backend: str | None = None) -> None:
         """
-        :param temperature: Temperature parameter. The value must be positive.  The kernels use a fixed-shift
-            logsumexp and refuse temperatures below 0.0235 (exp((cos - 1) / temperature) would leave fp32 range);
-            the reference has no such floor.
+        :param temperature: Temperature parameter. The value must be positive.  Below 0.0235 the kernels' fixed-shift
+            logsumexp would leave fp32 range (exp((cos - 1) / temperature)): such temperatures run on fp32 rows with
+            a max-shifted logsumexp, slower but exact for any positive value, like the reference.
         :param reduction: Same to PyTorch's `reduction` in losses.
         :param device: PyTorch's device instance (kept for signature compatibility).
         :param gather: keyword-only. True = negatives from every rank of ``process_group``;
@@ -311,10 +312,11 @@ class NT_Xent(torch.nn.Module):
 
     def _rows_dtype(self, x: torch.Tensor) -> torch.dtype:
         """dtype of the normalised rows: ``compute_dtype``, else the input dtype -- except that bf16 rows wider than
-        the tensor-core kernels' 256 features per tile fall back to fp32 rows on the CUDA-core kernels (any D), so
-        the module accepts every feature size the reference does."""
+        the tensor-core kernels' 256 features per tile, or at a temperature below their fixed-shift range, fall back
+        to fp32 rows on the CUDA-core kernels (any D, any temperature > 0), so the module accepts every feature size
+        and temperature the reference does."""
         dt = self.compute_dtype or x.dtype
-        if dt == torch.bfloat16 and x.shape[1] > 256:
+        if dt == torch.bfloat16 and (x.shape[1] > 256 or self.temperature < MIN_TC_TEMPERATURE):
             return torch.float32
         return dt
 

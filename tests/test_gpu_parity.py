@@ -155,8 +155,13 @@ def test_module_behaviour_on_device(dev):
     assert abs(float(out.detach()) - want) < 1e-5 * abs(want)
     assert NT_Xent(0.5)(a.bfloat16(), a.bfloat16()).dtype == torch.bfloat16   # dtype follows the input
     from simclr_b200 import _cabi
-    with pytest.raises(_cabi.NtxError):
-        NT_Xent(0.001)(a, a)                                       # below the fixed-shift range
+    be = _cabi.Backend()
+    rows = torch.empty(16, 64, dtype=torch.bfloat16, device=dev)
+    st = torch.empty(4, 16, device=dev)
+    be.l2norm(a, a, rows, st[0])
+    with pytest.raises(_cabi.NtxError, match="fp32 rows"):        # C level: bf16 rows keep the fixed-shift range
+        be.fwd(rows, rows, 8, (8, 1, 0), 0.001, st[1], st[2], st[3], torch.empty(2, device=dev),
+               torch.empty(1 << 16, dtype=torch.uint8, device=dev))
 
 
 @pytest.mark.parametrize("dtype,tol", [(torch.float32, FP32_TOL), (torch.bfloat16, BF16_TOL)])
@@ -652,3 +657,136 @@ def test_wide_bf16_inputs_fall_back_to_fp32_rows(dev):
     assert loss.dtype == torch.bfloat16
     assert abs(float(loss) - ref["loss"].mean()) < BF16_TOL * ref["loss"].mean()
     assert np.abs(ta.grad.float().cpu().numpy() - ref["dview0"]).max() < BF16_TOL * np.abs(ref["dview0"]).max()
+
+
+def test_folded_finalize_matches_separate_finalize(dev):
+    """NTXENT_FOLD=1 (the tensor-core kernels finish their rows themselves; read once per process, hence the child
+    process): same losses and gradients as the default separate finalize kernels, on a shard-shaped problem where
+    many CTAs share a row block and on a single-rank D = 256 problem, three calls in a row on one scratch buffer
+    (the fold counters must come back clean)."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = r"""
+import sys, torch, numpy as np
+sys.path.insert(0, %r)
+from simclr_b200 import _cabi
+be = _cabi.Backend(); dev = torch.device('cuda:0')
+out = {}
+for name, (n, d, world) in {'shard': (2048, 128, 8), 'wide': (700, 256, 1)}.items():
+    g = torch.Generator().manual_seed(3)
+    v0 = torch.randn(n, d, generator=g).bfloat16().to(dev); v1 = torch.randn(n, d, generator=g).bfloat16().to(dev)
+    nl = n // world; ql = 2 * nl; ld = be.row_pitch(d, torch.bfloat16)
+    rows = torch.empty(2 * n, ld, dtype=torch.bfloat16, device=dev); inv = torch.empty(2 * n, device=dev)
+    be.l2norm(v0, v1, rows, inv)
+    plan = be.plan(ql, 2 * n, d, torch.bfloat16)
+    ws = torch.empty(max(plan.fwd_ws_bytes, plan.bwd_ws_bytes), dtype=torch.uint8, device=dev).random_(0, 255)
+    st = torch.empty(3, ql, device=dev); ls = torch.empty(2, device=dev)
+    g0 = torch.empty(nl, d, dtype=torch.bfloat16, device=dev); g1 = torch.empty_like(g0)
+    one = torch.ones(1, device=dev); rsk = torch.full((2 * n,), 900.0, device=dev)
+    for _ in range(3):
+        be.fwd(rows[:ql], rows, d, (nl, world, 0), 0.5, st[0], st[1], st[2], ls, ws)
+        be.bwd(rows[:ql], rows, d, (nl, world, 0), 0.5, st[0], rsk if world > 1 else st[0], one, one, 0, 1.0 / ql,
+               v0[:nl], v1[:nl], inv[:ql], g0, g1, ws)
+    torch.cuda.synchronize()
+    out[name] = [st.cpu().numpy(), ls.cpu().numpy(), g0.float().cpu().numpy(), g1.float().cpu().numpy()]
+np.savez(sys.argv[1], **{k + str(i): a for k, v in out.items() for i, a in enumerate(v)})
+""" % root
+    import tempfile
+    res = {}
+    with tempfile.TemporaryDirectory() as td:
+        for fold in ("0", "1"):
+            path = os.path.join(td, f"fold{fold}.npz")
+            env = dict(os.environ, NTXENT_FOLD=fold)
+            subprocess.run([sys.executable, "-c", code, path], check=True, env=env, timeout=300)
+            res[fold] = dict(np.load(path))
+    for key, a in res["0"].items():
+        b = res["1"][key]
+        assert np.isfinite(b).all(), key
+        # same partial sums in the same order; only the positive logit differs in the last bits (taken from the
+        # similarity tile instead of a separate dot product)
+        assert np.abs(a - b).max() <= 2e-5 * max(1.0, np.abs(a).max()), key
+
+
+@pytest.mark.parametrize("tau", [0.02, 0.005, 0.0011])
+@pytest.mark.parametrize("reduction", ["mean", "none"])
+def test_small_temperatures_use_the_max_shifted_kernels(tau, reduction, dev):
+    """The reference accepts any temperature > 0 (loss.py:16).  Below 0.0235 the fixed shift 1/tau would push whole
+    rows out of fp32 range, so the module takes fp32 rows and the library a max-shifted logsumexp (two exponentials
+    per logit in backward): fp32 inputs against the fp64 oracle, bf16 inputs (fp32 rows of the same values) at the
+    bf16 output's 1e-2, clustered inputs included (cosines near 1: huge logit spread).  Tolerance for fp32: 1e-5
+    scaled by 0.05 / tau -- the logits s = cos / tau carry the fp32 rounding of cos multiplied by 1 / tau (at
+    tau = 0.0011 an absolute 1e-4), which no fp32 evaluation, the reference's included, can avoid."""
+    from simclr_b200 import NT_Xent
+    n, d = 150, 48
+    g = torch.Generator().manual_seed(31)
+    centres = torch.randn(10, d, generator=g)
+    a = centres[torch.randint(0, 10, (n,), generator=g)] + 0.05 * torch.randn(n, d, generator=g)
+    b = centres[torch.randint(0, 10, (n,), generator=g)] + 0.05 * torch.randn(n, d, generator=g)
+    b[: n // 2] = torch.randn(n // 2, d, generator=g)
+    up = None
+    w = orc.weights_for(reduction, n)
+    if reduction == "none":
+        up = torch.rand(2, n, generator=g) / n
+        w = up.double().numpy()
+    ref = orc.ntxent_rows_fp64(a.numpy(), b.numpy(), tau, weights=w)
+    ta, tb = a.to(dev).requires_grad_(True), b.to(dev).requires_grad_(True)
+    out = NT_Xent(tau, reduction)(ta, tb)
+    out.backward(up.to(dev) if up is not None else None)
+    want = ref["loss"] if reduction == "none" else ref["loss"].mean()
+    tol = FP32_TOL * max(1.0, 0.05 / tau)
+    assert rel_err(out.detach().cpu().numpy(), want) < tol
+    scale = max(np.abs(ref["dview0"]).max(), np.abs(ref["dview1"]).max())
+    assert np.abs(ta.grad.cpu().numpy() - ref["dview0"]).max() / scale < tol
+    assert np.abs(tb.grad.cpu().numpy() - ref["dview1"]).max() / scale < tol
+    # bf16 inputs: same path on the bf16-rounded values
+    ha, hb = a.bfloat16(), b.bfloat16()
+    ref16 = orc.ntxent_rows_fp64(ha.float().numpy(), hb.float().numpy(), tau, weights=w)
+    xa, xb = ha.to(dev).requires_grad_(True), hb.to(dev).requires_grad_(True)
+    out16 = NT_Xent(tau, reduction)(xa, xb)
+    out16.backward(up.bfloat16().to(dev) if up is not None else None)
+    want16 = ref16["loss"] if reduction == "none" else ref16["loss"].mean()
+    assert out16.dtype == torch.bfloat16 and rel_err(out16.detach().float().cpu().numpy(), want16) < BF16_TOL
+    if reduction == "mean":
+        scale16 = np.abs(ref16["dview0"]).max()
+        assert np.abs(xa.grad.float().cpu().numpy() - ref16["dview0"]).max() / scale16 < BF16_TOL
+
+
+def test_small_temperature_sharded_one_gpu(dev):
+    """Two ranks emulated on one GPU at tau = 0.01: the per-key vectors exchanged between ranks are lse values in the
+    max-shifted mode; result = the oracle on the concatenated batch."""
+    from simclr_b200 import _cabi
+    be = _cabi.Backend()
+    n, d, tau, world = 96, 40, 0.01, 2
+    g = torch.Generator().manual_seed(41)
+    v0, v1 = torch.randn(n, d, generator=g), torch.randn(n, d, generator=g)
+    ref = orc.ntxent_rows_fp64(v0.numpy(), v1.numpy(), tau, weights=orc.weights_for("mean", n))
+    nl = n // world
+    q_rows = 2 * nl
+    ld = be.row_pitch(d, torch.float32)
+    keys = torch.empty(world * q_rows, ld, device=dev)
+    inv = torch.empty(world, q_rows, device=dev)
+    views = []
+    for k in range(world):
+        a, b = v0[k * nl:(k + 1) * nl].to(dev), v1[k * nl:(k + 1) * nl].to(dev)
+        views.append((a, b))
+        be.l2norm(a, b, keys[k * q_rows:(k + 1) * q_rows], inv[k])
+    plan = be.plan(q_rows, world * q_rows, d, torch.float32)
+    ws = torch.empty(max(plan.fwd_ws_bytes, plan.bwd_ws_bytes, 16), dtype=torch.uint8, device=dev)
+    st = torch.empty(world, 3, q_rows, device=dev)
+    ls = torch.empty(world, 2, device=dev)
+    for k in range(world):
+        be.fwd(keys[k * q_rows:(k + 1) * q_rows], keys, d, (nl, world, k), tau, st[k, 0], st[k, 1], st[k, 2], ls[k], ws)
+    assert abs(float(ls[:, 1].mean()) - ref["loss"].mean()) < FP32_TOL * ref["loss"].mean()
+    lse_k = st[:, 0, :].reshape(-1).contiguous()
+    one = torch.ones(1, device=dev)
+    for k in range(world):
+        a, b = views[k]
+        d0, d1 = torch.empty_like(a), torch.empty_like(b)
+        be.bwd(keys[k * q_rows:(k + 1) * q_rows], keys, d, (nl, world, k), tau, st[k, 0], lse_k, one, one, 0, 0.5 / n, a, b,
+               inv[k], d0, d1, ws)
+        sl = slice(k * nl, (k + 1) * nl)
+        scale = np.abs(ref["dview0"]).max()
+        assert np.abs(d0.cpu().numpy() - ref["dview0"][sl]).max() / scale < FP32_TOL
+        assert np.abs(d1.cpu().numpy() - ref["dview1"][sl]).max() / scale < FP32_TOL
