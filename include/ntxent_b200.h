@@ -251,7 +251,7 @@ int ntx_project_bwd(const void* dz, const void* h0, const void* h1, const void* 
  * chunk = chunk_elems elements, listed tensor by tensor in order) live in DEVICE memory and are built once by the
  * caller; a tensor's momentum buffer must start at zero (that reproduces SGD's first step).  The workspace
  * (ntx_larc_workspace_bytes) must be zeroed once before the first call and is left ready for the next one.
- * Deterministic: chunk sums are added in chunk order.  One cooperative launch; no host synchronisation (the
+ * Deterministic: chunk sums are added in a fixed order.  One cooperative launch; no host synchronisation (the
  * reference syncs twice per tensor through `norm != 0`). */
 typedef struct NtxLarcParam {
     float* param;

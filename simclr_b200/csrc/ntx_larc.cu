@@ -11,7 +11,7 @@
 //   m = momentum * m + g';  p = p - lr * m          (a zero-initialised m reproduces SGD's first step: m = g')
 // The reference launches ~10 small kernels per tensor (two norms with a host sync each through `!= 0`, the in-place
 // gradient edits, the SGD update); here a cooperative grid walks a chunk list: sums of squares per chunk, a grid
-// barrier, per-tensor totals added in chunk order (deterministic), a second barrier, the update.  HBM-bound:
+// barrier, per-tensor totals added in a fixed order (deterministic), a second barrier, the update.  HBM-bound:
 // 3 reads + 2 writes of 4 bytes per element in the update, the norm pass re-reads p and g (mostly from L2).
 #include "ntx_common.cuh"
 
@@ -86,16 +86,26 @@ larc_sgd_kernel(const NtxLarcParam* __restrict__ table, int n_tensors, const int
     }
     grid_barrier(bar, (unsigned)G);
 
-    // ---- pass 1.5: per-tensor totals, chunk partials added in chunk order by one thread per tensor
-    for (int t = cta * kThreads + threadIdx.x; t < n_tensors; t += G * kThreads) {
-        const NtxLarcParam P = table[t];
-        double pp = 0.0, gg = 0.0;
-        for (int c = 0; c < P.n_chunks; ++c) {
-            const Partial q = partial[P.first_chunk + c];
-            pp += q.pp;
-            gg += q.gg;
+    // ---- pass 1.5: per-tensor totals by one warp per tensor: lane l adds chunks l, l + 32, ... in order, then a
+    // fixed shuffle tree adds the 32 lane sums -- the same order in every run
+    {
+        const int lane = threadIdx.x & 31;
+        const int warps = G * (kThreads / 32);
+        for (int t = cta * (kThreads / 32) + (threadIdx.x >> 5); t < n_tensors; t += warps) {
+            const NtxLarcParam P = table[t];
+            double pp = 0.0, gg = 0.0;
+            for (int c = lane; c < P.n_chunks; c += 32) {
+                const Partial q = partial[P.first_chunk + c];
+                pp += q.pp;
+                gg += q.gg;
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                pp += __shfl_xor_sync(0xffffffffu, pp, o);
+                gg += __shfl_xor_sync(0xffffffffu, gg, o);
+            }
+            if (lane == 0) totals[t] = Partial{pp, gg};
         }
-        totals[t] = Partial{pp, gg};
     }
     grid_barrier(bar, 2u * (unsigned)G);
 

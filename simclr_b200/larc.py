@@ -23,7 +23,7 @@ import torch
 
 from . import _cabi
 
-CHUNK_ELEMS = 8192          # elements per work item of the kernel (32 KB of each tensor)
+CHUNK_ELEMS = 2048          # elements per work item of the kernel (8 KB of each tensor): ~5 items per CTA on a ResNet-18
 
 
 class LARC:
