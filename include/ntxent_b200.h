@@ -268,6 +268,22 @@ int ntx_larc_sgd_step(const NtxLarcParam* table, int n_tensors, const int32_t* c
                       float lr, float momentum, float trust_coefficient, float eps, int clip, void* workspace,
                       size_t workspace_bytes, void* stream);
 
+/* SimCLR's two-view augmentation for a batch of uint8 images already on the device.
+ * Replaces SimCLRTransforms.__call__ (dataset.py:42-50) applied per image by the data-loader workers:
+ * RandomResizedCrop(out_size) -> RandomHorizontalFlip(0.5) -> RandomApply([ColorJitter(0.8 s, 0.8 s, 0.8 s, 0.2 s)], 0.8)
+ * -> RandomGrayscale(0.2) -> ToTensor (dataset.py:19-39), drawn twice per image.
+ *   images : (batch, height, width, 3) uint8, HWC as CIFAR stores them; height, width <= 64
+ *   view0 / view1 : (batch, 3, out_size, out_size) float32 in [0, 1]
+ *   seed, offset : the random parameters of (image i, view v) come from Philox4x32-10 keyed by seed with counter
+ *                  (2 i + v, offset); pass a new offset on every call
+ *   params_out : optional (batch, 2, 16) floats: top, left, h, w, flip, jitter applied, brightness, contrast,
+ *                saturation, hue factors, grayscale, the order of the four adjustments; NULL to skip
+ * The pixel arithmetic follows PIL's 8-bit paths (antialiased bilinear resize, Image.blend truncation, 8-bit HSV),
+ * so replaying the written parameters through torchvision gives the same images up to the last bit of a few pixels. */
+int ntx_simclr_augment(const void* images, int batch, int height, int width, float strength, unsigned long long seed,
+                       unsigned long long offset, int out_size, float* view0, float* view1, float* params_out,
+                       void* stream);
+
 /* Test entry: the self and positive column of every row, computed on the device by
  * the same helper the kernels use (bit-exact contract on loss.py:37-38 indexing). */
 int ntx_debug_indices(const NtxLayout* layout, int32_t* self_col, int32_t* pos_col, void* stream);

@@ -22,6 +22,7 @@ EXPORTS = (
     "ntx_bwd", "ntx_debug_indices", "ntx_profile_next", "ntx_fwd_static", "ntx_peer_block_bytes",
     "ntx_peer_l2norm", "ntx_peer_fwd", "ntx_peer_post_weights", "ntx_peer_bwd", "ntx_project_l2norm", "ntx_bwd_rows", "ntx_launch_count",
     "ntx_larc_workspace_bytes", "ntx_larc_sgd_step", "ntx_project_bwd_workspace_bytes", "ntx_project_bwd",
+    "ntx_simclr_augment",
 )
 
 MAX_PEERS = 8
@@ -91,6 +92,7 @@ def _declare(lib):
     lib.ntx_project_bwd_workspace_bytes.argtypes = [i, i, i]
     lib.ntx_project_bwd_workspace_bytes.restype = ctypes.c_size_t
     lib.ntx_project_bwd.argtypes = [vp, vp, vp, vp, i, i, i, vp, vp, vp, vp, sz, vp]
+    lib.ntx_simclr_augment.argtypes = [vp, i, i, i, f, ctypes.c_ulonglong, ctypes.c_ulonglong, i, vp, vp, vp, vp]
     lib.ntx_larc_workspace_bytes.argtypes = [i, i]
     lib.ntx_larc_sgd_step.argtypes = [vp, i, vp, i, i, f, f, f, f, i, vp, sz, vp]
     lib.ntx_launch_count.restype = ctypes.c_longlong
@@ -263,6 +265,15 @@ class Backend:
         _check(load().ntx_project_bwd(dz.data_ptr(), h0.data_ptr(), h1.data_ptr(), weight.data_ptr(), n, hdim,
                                       weight.shape[0], dh0.data_ptr(), dh1.data_ptr(), dweight.data_ptr(),
                                       workspace.data_ptr(), workspace.numel() * workspace.element_size(), _stream(dz)))
+
+    def simclr_augment(self, images, strength, seed, offset, out_size, view0, view1, params_out=None):
+        """ntx_simclr_augment: two augmented float views of a (B, H, W, 3) uint8 batch (dataset.py:19-50 on the GPU)."""
+        b, h, w, c = images.shape
+        if c != 3 or images.dtype != torch.uint8 or not images.is_contiguous():
+            raise TypeError("images must be a contiguous (B, H, W, 3) uint8 tensor")
+        _check(load().ntx_simclr_augment(images.data_ptr(), b, h, w, float(strength), int(seed), int(offset), int(out_size),
+                                         view0.data_ptr(), view1.data_ptr(),
+                                         params_out.data_ptr() if params_out is not None else None, _stream(images)))
 
     def larc_sgd_step(self, table_dev, n_tensors, chunks_dev, n_chunks, chunk_elems, lr, momentum, trust, eps, clip,
                       workspace):

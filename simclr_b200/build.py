@@ -13,7 +13,7 @@ import sys
 PKG = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG, "csrc")
 LIB = os.path.join(PKG, "libntxent_b200.so")
-SOURCES = ["ntx_api.cu", "ntx_l2norm.cu", "ntx_simt.cu", "ntx_finalize.cu", "ntx_tc.cu", "ntx_project.cu", "ntx_project_bwd.cu", "ntx_larc.cu"]
+SOURCES = ["ntx_api.cu", "ntx_l2norm.cu", "ntx_simt.cu", "ntx_finalize.cu", "ntx_tc.cu", "ntx_project.cu", "ntx_project_bwd.cu", "ntx_larc.cu", "ntx_augment.cu"]
 HEADERS = ["ntx_common.cuh", "ntx_umma.cuh", os.path.join("..", "..", "include", "ntxent_b200.h")]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",   # explicit: -arch=sm_100a would add a plain compute_100 pass

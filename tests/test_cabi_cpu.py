@@ -116,6 +116,11 @@ def test_newer_entry_points_validate_before_touching_the_device():
     assert b"step" in lib.ntx_last_error()
     assert lib.ntx_peer_post_weights(ctypes.byref(good), 4, 8, 0, 4096, 4096, 2, 0, None) == -1
     assert b"w_stride" in lib.ntx_last_error()
+    # augmentation: image staged in shared memory (<= 64 x 64), output side, strength like main.py:49
+    assert lib.ntx_simclr_augment(4096, 4, 80, 32, 0.5, 0, 0, 32, 4096, 4096, None, None) == -1
+    assert b"shared memory" in lib.ntx_last_error()
+    assert lib.ntx_simclr_augment(4096, 4, 32, 32, 0.0, 0, 0, 32, 4096, 4096, None, None) == -1
+    assert lib.ntx_simclr_augment(4096, 4, 32, 32, 0.5, 0, 0, 100, 4096, 4096, None, None) == -1
     # projection: hidden size in whole TMA blocks, row pitch of bf16 rows, d <= 256
     assert lib.ntx_project_l2norm(4096, 4096, 4096, 4, 100, 64, 4096, 64, 4096, None) == -1
     assert b"multiple of 64" in lib.ntx_last_error()
