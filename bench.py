@@ -371,7 +371,8 @@ def run_ours(args):
     with torch.no_grad():
         rows = torch.empty(q_rows, ld, dtype=torch.bfloat16, device=dev)
         stats = torch.empty(4, q_rows, device=dev)
-        be.l2norm(d0, d1, rows, stats[0])
+        rs = be.row_scale(TAU, torch.bfloat16)             # what the module stores into bf16 rows
+        be.l2norm(d0, d1, rows, stats[0], row_scale=rs)
         keys = rows
         if world > 1:
             keys = torch.empty(world * q_rows, ld, dtype=torch.bfloat16, device=dev)
@@ -380,7 +381,7 @@ def run_ours(args):
         plan = be.plan(q_rows, keys.shape[0], DIM, torch.bfloat16)
         ws = torch.empty(max(plan.fwd_ws_bytes, plan.bwd_ws_bytes), dtype=torch.uint8, device=dev)
         loss_sum = torch.empty(2, device=dev)
-        lay = (n_local, world, rank)
+        lay = (n_local, world, rank, rs)
         g0, g1 = torch.empty_like(d0), torch.empty_like(d1)
         one = torch.ones(1, device=dev)
         kt = {0: [], 1: []}

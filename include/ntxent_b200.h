@@ -63,6 +63,12 @@ typedef struct NtxLayout {
     int32_t n_local;
     int32_t world;
     int32_t rank;
+    float row_scale; /* what the rows were multiplied by when they were normalised: 0 or 1 = unit rows; for bf16
+                      * rows also ntx_row_scale(temperature, NTX_BF16) = sqrt(log2(e) / temperature), with which a
+                      * similarity value is the exponent of its logit and the tensor-core kernels skip the scaling
+                      * of every logit (about 2 % of the step; results agree to bf16 rounding) */
+    int32_t loss_dtype; /* element type of the two values ntx_fwd writes to loss_sum: NTX_F32 (0, the default) or
+                         * NTX_BF16 -- a bf16 loss comes out ready, without a conversion kernel behind the call */
 } NtxLayout;
 
 /* How a launch is cut into work: pure integer arithmetic, no device needed.
@@ -91,6 +97,10 @@ const char* ntx_last_error(void);
  * bench.py counts the launches of one step with it.  No counterpart in the reference. */
 long long ntx_launch_count(void);
 
+/* The factor NT_Xent's module stores into bf16 rows (see NtxLayout.row_scale): sqrt(log2(e) / temperature) for
+ * NTX_BF16 rows at temperature >= NTX_MIN_TEMPERATURE, 1 otherwise. */
+float ntx_row_scale(float temperature, int dtype);
+
 /* Leading dimension (elements per row) the library wants for normalised rows of
  * feature size d in dtype NTX_F32 / NTX_BF16: d rounded up to 4 (fp32) or 64 (bf16). */
 int ntx_row_pitch(int d, int dtype);
@@ -102,9 +112,10 @@ int ntx_plan(int q_rows, int k_rows, int d, int dtype, int sm_count, NtxPlan* pl
 /* L2-normalise both views into one [2n x ld] row buffer: rows [0,n) from view0,
  * rows [n,2n) from view1, zero padded from d to ld.  Replaces the two
  * F.normalize calls at loss.py:33-34 (x / max(||x||_2, 1e-12)).
- * inv_norm[r] = 1 / max(||row r||, 1e-12).  view pointers are (n x d), contiguous. */
+ * inv_norm[r] = 1 / max(||row r||, 1e-12).  view pointers are (n x d), contiguous.
+ * row_scale (0 = 1): the rows are stored multiplied by it; pass the same value in NtxLayout.row_scale later. */
 int ntx_l2norm(const void* view0, const void* view1, int n, int d, int in_dtype,
-               void* rows, int ld, int rows_dtype, float* inv_norm, void* stream);
+               void* rows, int ld, int rows_dtype, float* inv_norm, float row_scale, void* stream);
 
 /* ntx_l2norm with the projection head's last layer in front of it:
  *   rows = normalize([h0 ; h1] . weight^T),  h0/h1: (n x hdim) bf16, weight: (d x hdim) bf16 as nn.Linear stores it.
@@ -113,7 +124,7 @@ int ntx_l2norm(const void* view0, const void* view1, int n, int d, int in_dtype,
  * ld = ntx_row_pitch(d, NTX_BF16)) and inv_norm.  hdim must be a multiple of 64, d <= 256.  One tcgen05 GEMM tile
  * per 128 rows with the normalisation as its epilogue. */
 int ntx_project_l2norm(const void* h0, const void* h1, const void* weight, int n, int hdim, int d, void* rows,
-                       int ld, float* inv_norm, void* stream);
+                       int ld, float* inv_norm, float row_scale, void* stream);
 
 /* Multi-rank exchange without a collective library call (one node, NVLink / NVSwitch peer memory).
  * Every rank owns one EXCHANGE BLOCK of ntx_peer_block_bytes() bytes that is mapped into every process
@@ -151,14 +162,14 @@ typedef struct NtxPeerBlocks {
 } NtxPeerBlocks;
 size_t ntx_peer_block_bytes(int q_rows, int ld, int rows_dtype, int world);
 int ntx_peer_l2norm(const void* view0, const void* view1, int n, int d, int in_dtype, const NtxPeerBlocks* blocks,
-                    int ld, int rows_dtype, float* inv_norm, uint32_t* step, void* stream);
+                    int ld, int rows_dtype, float* inv_norm, float row_scale, uint32_t* step, void* stream);
 int ntx_peer_fwd(const NtxPeerBlocks* blocks, int n_local, int d, int ld, int dtype, float temperature,
-                 const uint32_t* step, float* rowsum, float* pos_logit, float* row_loss, float* loss_sum,
+                 float row_scale, int loss_dtype, const uint32_t* step, float* rowsum, float* pos_logit, float* row_loss, float* loss_sum,
                  void* workspace, size_t workspace_bytes, void* stream);
 int ntx_peer_post_weights(const NtxPeerBlocks* blocks, int n_local, int ld, int dtype, const uint32_t* step,
                           const void* w, int w_stride, int w_dtype, void* stream);
 int ntx_peer_bwd(const NtxPeerBlocks* blocks, int n_local, int d, int ld, int dtype, float temperature,
-                 const uint32_t* step, const float* rowsum_q, int w_stride, float w_scale, const void* view0,
+                 float row_scale, const uint32_t* step, const float* rowsum_q, int w_stride, float w_scale, const void* view0,
                  const void* view1, int in_dtype, const float* inv_norm, void* dview0, void* dview1, void* workspace,
                  size_t workspace_bytes, void* stream);
 
@@ -168,6 +179,7 @@ int ntx_peer_bwd(const NtxPeerBlocks* blocks, int n_local, int d, int ld, int dt
  *   row_loss[r] = log(rowsum[r]) + 1/tau - pos_logit[r]     (layout (2, n_local): loss.py:55-58)
  *   loss_sum[0] = sum of row_loss                             (loss.py:60-61)
  *   loss_sum[1] = loss_sum[0] / q_rows                        (loss.py:65, "mean")
+ *                 (two floats, or two bf16 values when layout->loss_dtype == NTX_BF16)
  * Replaces loss.py:36-61: the three similarity GEMMs (:42,43,49), the boolean-mask
  * diagonal removal (:38,46-47), the concatenations (:51-52) and both cross-entropies
  * (:56-61); the 2N x 2N logits are never written to memory.

@@ -18,7 +18,7 @@ NTX_F32, NTX_BF16 = 0, 1
 DTYPES = {torch.float32: NTX_F32, torch.bfloat16: NTX_BF16}
 
 EXPORTS = (
-    "ntx_version", "ntx_last_error", "ntx_row_pitch", "ntx_plan", "ntx_l2norm", "ntx_fwd",
+    "ntx_version", "ntx_last_error", "ntx_row_pitch", "ntx_row_scale", "ntx_plan", "ntx_l2norm", "ntx_fwd",
     "ntx_bwd", "ntx_debug_indices", "ntx_profile_next", "ntx_fwd_static", "ntx_peer_block_bytes",
     "ntx_peer_l2norm", "ntx_peer_fwd", "ntx_peer_post_weights", "ntx_peer_bwd", "ntx_project_l2norm", "ntx_bwd_rows", "ntx_launch_count",
     "ntx_larc_workspace_bytes", "ntx_larc_sgd_step", "ntx_project_bwd_workspace_bytes", "ntx_project_bwd",
@@ -29,7 +29,8 @@ MAX_PEERS = 8
 
 
 class NtxLayout(ctypes.Structure):
-    _fields_ = [("n_local", ctypes.c_int32), ("world", ctypes.c_int32), ("rank", ctypes.c_int32)]
+    _fields_ = [("n_local", ctypes.c_int32), ("world", ctypes.c_int32), ("rank", ctypes.c_int32),
+                ("row_scale", ctypes.c_float), ("loss_dtype", ctypes.c_int32)]
 
 
 class NtxPeerBlocks(ctypes.Structure):
@@ -69,25 +70,26 @@ def _declare(lib):
     lib.ntx_version.restype = i
     lib.ntx_last_error.restype = ctypes.c_char_p
     lib.ntx_row_pitch.argtypes = [i, i]
+    lib.ntx_row_scale.argtypes = [f, i]
     lib.ntx_plan.argtypes = [i, i, i, i, i, ctypes.POINTER(NtxPlan)]
-    lib.ntx_l2norm.argtypes = [vp, vp, i, i, i, vp, i, i, vp, vp]
+    lib.ntx_l2norm.argtypes = [vp, vp, i, i, i, vp, i, i, vp, f, vp]
     lib.ntx_fwd.argtypes = [vp, vp, i, i, i, i, i, ctypes.POINTER(NtxLayout), f, vp, vp, vp, vp, vp, sz, vp]
     lib.ntx_bwd.argtypes = [vp, vp, i, i, i, i, i, ctypes.POINTER(NtxLayout), f, vp, vp, vp, vp, i, i, f,
                             vp, vp, i, vp, vp, vp, vp, sz, vp]
     lib.ntx_fwd_static.argtypes = [vp, vp, i, i, i, i, i, ctypes.POINTER(NtxLayout), f, vp, vp, vp, vp, vp]
     pb = ctypes.POINTER(NtxPeerBlocks)
     lib.ntx_peer_block_bytes.argtypes = [i, i, i, i]
-    lib.ntx_peer_l2norm.argtypes = [vp, vp, i, i, i, pb, i, i, vp, vp, vp]
-    lib.ntx_peer_fwd.argtypes = [pb, i, i, i, i, f, vp, vp, vp, vp, vp, vp, sz, vp]
+    lib.ntx_peer_l2norm.argtypes = [vp, vp, i, i, i, pb, i, i, vp, f, vp, vp]
+    lib.ntx_peer_fwd.argtypes = [pb, i, i, i, i, f, f, i, vp, vp, vp, vp, vp, vp, sz, vp]
     lib.ntx_peer_post_weights.argtypes = [pb, i, i, i, vp, vp, i, i, vp]
-    lib.ntx_peer_bwd.argtypes = [pb, i, i, i, i, f, vp, vp, i, f, vp, vp, i, vp, vp, vp, vp, sz, vp]
-    lib.ntx_project_l2norm.argtypes = [vp, vp, vp, i, i, i, vp, i, vp, vp]
+    lib.ntx_peer_bwd.argtypes = [pb, i, i, i, i, f, f, vp, vp, i, f, vp, vp, i, vp, vp, vp, vp, sz, vp]
+    lib.ntx_project_l2norm.argtypes = [vp, vp, vp, i, i, i, vp, i, vp, f, vp]
     lib.ntx_bwd_rows.argtypes = [vp, vp, i, i, i, i, i, ctypes.POINTER(NtxLayout), f, vp, vp, vp, vp, i, i, f, vp, vp,
                                  vp, sz, vp]
     lib.ntx_debug_indices.argtypes = [ctypes.POINTER(NtxLayout), vp, vp, vp]
     lib.ntx_profile_next.argtypes = [i, vp, vp]
     for name in EXPORTS:
-        if name != "ntx_last_error":
+        if name not in ("ntx_last_error", "ntx_row_scale"):
             getattr(lib, name).restype = i
     lib.ntx_project_bwd_workspace_bytes.argtypes = [i, i, i]
     lib.ntx_project_bwd_workspace_bytes.restype = ctypes.c_size_t
@@ -96,6 +98,7 @@ def _declare(lib):
     lib.ntx_larc_workspace_bytes.argtypes = [i, i]
     lib.ntx_larc_sgd_step.argtypes = [vp, i, vp, i, i, f, f, f, f, i, vp, sz, vp]
     lib.ntx_launch_count.restype = ctypes.c_longlong
+    lib.ntx_row_scale.restype = ctypes.c_float
     lib.ntx_larc_workspace_bytes.restype = ctypes.c_size_t
     lib.ntx_peer_block_bytes.restype = ctypes.c_size_t
 
@@ -146,6 +149,11 @@ class Backend:
         """Kernels the library has launched (or recorded under stream capture) so far in this process."""
         return int(load().ntx_launch_count())
 
+    def row_scale(self, temperature: float, dtype: torch.dtype) -> float:
+        """Factor to store into normalised rows of `dtype` so that the tensor-core kernels skip the per-logit scaling
+        (sqrt(log2 e / temperature) for bf16 rows, 1 otherwise); goes to ``l2norm`` and into the layout tuple."""
+        return float(load().ntx_row_scale(float(temperature), DTYPES[dtype]))
+
     def row_pitch(self, d: int, dtype: torch.dtype) -> int:
         return load().ntx_row_pitch(d, DTYPES[dtype])
 
@@ -154,17 +162,18 @@ class Backend:
         _check(load().ntx_plan(q_rows, k_rows, d, DTYPES[dtype], sm_count, ctypes.byref(p)))
         return p
 
-    def l2norm(self, view0, view1, rows, inv_norm):
+    def l2norm(self, view0, view1, rows, inv_norm, row_scale: float = 1.0):
         n, d = view0.shape
         _check(load().ntx_l2norm(view0.data_ptr(), view1.data_ptr(), n, d, DTYPES[view0.dtype],
                                  rows.data_ptr(), rows.shape[1], DTYPES[rows.dtype],
-                                 inv_norm.data_ptr(), _stream(rows)))
+                                 inv_norm.data_ptr(), float(row_scale), _stream(rows)))
 
-    def project_l2norm(self, h0, h1, weight, rows, inv_norm):
+    def project_l2norm(self, h0, h1, weight, rows, inv_norm, row_scale: float = 1.0):
         """ntx_project_l2norm: rows = normalize([h0 ; h1] @ weight.T) (bf16), the projections never stored."""
         n, hdim = h0.shape
         _check(load().ntx_project_l2norm(h0.data_ptr(), h1.data_ptr(), weight.data_ptr(), n, hdim, weight.shape[0],
-                                         rows.data_ptr(), rows.shape[1], inv_norm.data_ptr(), _stream(rows)))
+                                         rows.data_ptr(), rows.shape[1], inv_norm.data_ptr(), float(row_scale),
+                                         _stream(rows)))
 
     # ---- peer exchange (include/ntxent_b200.h, "Multi-rank exchange"): `blocks` is an NtxPeerBlocks
     def peer_block_bytes(self, q_rows: int, ld: int, rows_dtype: torch.dtype, world: int) -> int:
@@ -181,18 +190,18 @@ class Backend:
         pb.world, pb.rank = len(ptrs), rank
         return pb
 
-    def peer_l2norm(self, view0, view1, blocks, ld, rows_dtype, inv_norm, step):
+    def peer_l2norm(self, view0, view1, blocks, ld, rows_dtype, inv_norm, step, row_scale: float = 1.0):
         """ntx_peer_l2norm: normalised rows into the step's key buffer of every rank's block; ``step`` (one int32
         on the device) receives the step number the later calls of this step take."""
         n, d = view0.shape
         _check(load().ntx_peer_l2norm(view0.data_ptr(), view1.data_ptr(), n, d, DTYPES[view0.dtype],
                                       ctypes.byref(blocks), ld, DTYPES[rows_dtype], inv_norm.data_ptr(),
-                                      step.data_ptr(), _stream(view0)))
+                                      float(row_scale), step.data_ptr(), _stream(view0)))
 
     def peer_fwd(self, blocks, n_local, d, ld, rows_dtype, temperature, step, rowsum, pos_logit, row_loss, loss_sum,
-                 workspace):
+                 workspace, row_scale: float = 1.0):
         _check(load().ntx_peer_fwd(ctypes.byref(blocks), n_local, d, ld, DTYPES[rows_dtype], float(temperature),
-                                   step.data_ptr(), rowsum.data_ptr(), pos_logit.data_ptr(), row_loss.data_ptr(),
+                                   float(row_scale), DTYPES[loss_sum.dtype], step.data_ptr(), rowsum.data_ptr(), pos_logit.data_ptr(), row_loss.data_ptr(),
                                    loss_sum.data_ptr(), workspace.data_ptr(),
                                    workspace.numel() * workspace.element_size(), _stream(rowsum)))
 
@@ -202,15 +211,16 @@ class Backend:
                                             w.data_ptr(), int(w_stride), DTYPES[w.dtype], _stream(w)))
 
     def peer_bwd(self, blocks, n_local, d, ld, rows_dtype, temperature, step, rowsum_q, w_stride, w_scale, view0,
-                 view1, inv_norm, dview0, dview1, workspace):
+                 view1, inv_norm, dview0, dview1, workspace, row_scale: float = 1.0):
         _check(load().ntx_peer_bwd(ctypes.byref(blocks), n_local, d, ld, DTYPES[rows_dtype], float(temperature),
-                                   step.data_ptr(), rowsum_q.data_ptr(), int(w_stride), float(w_scale),
+                                   float(row_scale), step.data_ptr(), rowsum_q.data_ptr(), int(w_stride), float(w_scale),
                                    view0.data_ptr(), view1.data_ptr(), DTYPES[view0.dtype], inv_norm.data_ptr(),
                                    dview0.data_ptr(), dview1.data_ptr(), workspace.data_ptr(),
                                    workspace.numel() * workspace.element_size(), _stream(view0)))
 
     def fwd(self, q, k, d, layout, temperature, rowsum, pos_logit, row_loss, loss_sum, workspace):
         lay = NtxLayout(*layout)
+        lay.loss_dtype = DTYPES[loss_sum.dtype]               # two floats, or two bf16 values written ready to return
         _check(load().ntx_fwd(q.data_ptr(), k.data_ptr(), q.shape[0], k.shape[0], d, q.shape[1],
                               DTYPES[q.dtype], ctypes.byref(lay), float(temperature), rowsum.data_ptr(),
                               pos_logit.data_ptr(), row_loss.data_ptr(), loss_sum.data_ptr(),
@@ -222,6 +232,7 @@ class Backend:
         cannot provide scratch memory.  Limited to problems needing at most 1 MiB of scratch; calls
         that may overlap on the GPU race on the shared array."""
         lay = NtxLayout(*layout)
+        lay.loss_dtype = DTYPES[loss_sum.dtype]
         _check(load().ntx_fwd_static(q.data_ptr(), k.data_ptr(), q.shape[0], k.shape[0], d, q.shape[1],
                                      DTYPES[q.dtype], ctypes.byref(lay), float(temperature),
                                      rowsum.data_ptr(), pos_logit.data_ptr(), row_loss.data_ptr(),

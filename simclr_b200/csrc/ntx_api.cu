@@ -97,6 +97,24 @@ int make_dims(int q_rows, int k_rows, int d, int ld, int dtype, const NtxLayout*
     dm->inv_tau = 1.0f / temperature;
     dm->c1 = NTX_LOG2E / temperature;
     dm->stable = temperature < NTX_MIN_TEMPERATURE ? 1 : 0;
+    NTX_CHECK_ARG(L->loss_dtype == NTX_F32 || L->loss_dtype == NTX_BF16, "layout.loss_dtype %d not supported", L->loss_dtype);
+    dm->loss_bf16 = L->loss_dtype == NTX_BF16 ? 1 : 0;
+    // rows that carry sqrt(log2e / tau): only the value ntx_row_scale() hands out, and only bf16 rows
+    const float rs = L->row_scale > 0.f ? L->row_scale : 1.0f;
+    dm->scaled = 0;
+    dm->rowsum_scale = 1.0f;
+    dm->pos_scale = dm->inv_tau;
+    dm->inv_rs = 1.0f;
+    if (rs != 1.0f) {
+        const float want = ntx_row_scale(temperature, dtype);
+        NTX_CHECK_ARG(dtype == NTX_BF16 && want != 1.0f && fabsf(rs - want) <= 1e-6f * want,
+                      "layout.row_scale=%g: rows must be unit rows (1) or, for bf16 rows, scaled by ntx_row_scale(%g)=%g",
+                      (double)rs, (double)temperature, (double)want);
+        dm->scaled = 1;
+        dm->rowsum_scale = exp2f(-dm->c1);
+        dm->pos_scale = 0.6931471805599453f * (dm->c1 / (rs * rs));     // ln 2 up to the rounding of rs
+        dm->inv_rs = 1.0f / rs;
+    }
     return NTX_OK;
 }
 
@@ -125,6 +143,11 @@ extern "C" {
 int ntx_version(void) { return NTX_VERSION; }
 long long ntx_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 const char* ntx_last_error(void) { return g_err; }
+
+float ntx_row_scale(float temperature, int dtype) {
+    if (dtype != NTX_BF16 || !(temperature >= NTX_MIN_TEMPERATURE)) return 1.0f;
+    return sqrtf(NTX_LOG2E / temperature);
+}
 
 int ntx_row_pitch(int d, int dtype) {
     if (d < 1) return 0;
@@ -213,7 +236,7 @@ int ntx_plan(int q_rows, int k_rows, int d, int dtype, int sm_count, NtxPlan* pl
 }
 
 int ntx_l2norm(const void* view0, const void* view1, int n, int d, int in_dtype, void* rows, int ld,
-               int rows_dtype, float* inv_norm, void* stream) {
+               int rows_dtype, float* inv_norm, float row_scale, void* stream) {
     NTX_CHECK_ARG(n >= 1 && d >= 1, "bad sizes n=%d d=%d", n, d);
     NTX_CHECK_ARG(view0 && view1 && rows && inv_norm, "NULL buffer");
     NTX_CHECK_ARG(in_dtype == NTX_F32 || in_dtype == NTX_BF16, "view dtype %d not supported", in_dtype);
@@ -221,12 +244,13 @@ int ntx_l2norm(const void* view0, const void* view1, int n, int d, int in_dtype,
                   rows_dtype);
     NTX_CHECK_ARG(ld >= ntx_row_pitch(d, rows_dtype) && ld % (rows_dtype == NTX_BF16 ? 64 : 4) == 0,
                   "ld=%d too small or misaligned for d=%d", ld, d);
+    NTX_CHECK_ARG(row_scale >= 0.f, "row_scale must not be negative");
     return ntx_l2norm_launch(view0, view1, n, d, in_dtype, rows, NtxPeerOut{}, 0, 0, nullptr, ld, rows_dtype, inv_norm,
-                             (cudaStream_t)stream);
+                             row_scale > 0.f ? row_scale : 1.0f, (cudaStream_t)stream);
 }
 
 int ntx_project_l2norm(const void* h0, const void* h1, const void* weight, int n, int hdim, int d, void* rows,
-                       int ld, float* inv_norm, void* stream) {
+                       int ld, float* inv_norm, float row_scale, void* stream) {
     NTX_CHECK_ARG(n >= 1 && d >= 1 && hdim >= 64, "bad sizes n=%d hdim=%d d=%d", n, hdim, d);
     NTX_CHECK_ARG(hdim % 64 == 0, "hidden size %d must be a multiple of 64 (one 128-byte TMA row of bf16)", hdim);
     NTX_CHECK_ARG(h0 && h1 && weight && rows && inv_norm, "NULL buffer");
@@ -236,7 +260,9 @@ int ntx_project_l2norm(const void* h0, const void* h1, const void* weight, int n
     NTX_CHECK_ARG(reinterpret_cast<uintptr_t>(h0) % 16 == 0 && reinterpret_cast<uintptr_t>(h1) % 16 == 0 &&
                       reinterpret_cast<uintptr_t>(weight) % 16 == 0 && reinterpret_cast<uintptr_t>(rows) % 16 == 0,
                   "buffers must be 16-byte aligned");
-    return ntx_project_launch(h0, h1, weight, n, hdim, d, rows, ld, inv_norm, (cudaStream_t)stream);
+    NTX_CHECK_ARG(row_scale >= 0.f, "row_scale must not be negative");
+    return ntx_project_launch(h0, h1, weight, n, hdim, d, rows, ld, inv_norm, row_scale > 0.f ? row_scale : 1.0f,
+                              (cudaStream_t)stream);
 }
 
 }  // extern "C"
@@ -286,7 +312,6 @@ int fwd_impl(const void* q, const void* k, int q_rows, int k_rows, int d, int ld
         const uint64_t partial_bytes = (uint64_t)plan.max_slots * rows_pad * sizeof(float);
         float* partial = (float*)(ws + head);
         unsigned int* counter = (unsigned int*)(ws + head + partial_bytes);
-        double* block_sums = (double*)(ws + head + partial_bytes + 16);
         NtxFoldScratch fold;
         fold.tag = (unsigned int*)ws;
         fold.done_total = (unsigned int*)(ws + 4);
@@ -303,7 +328,7 @@ int fwd_impl(const void* q, const void* k, int q_rows, int k_rows, int d, int ld
                                    ex.gate, ex.key_buf_elems, st);
         }
         if (rc || !no_fold) return rc;
-        return ntx_fwd_finalize_launch(q, dtype, dm, plan, partial, nullptr, counter, block_sums, rowsum, pos_logit,
+        return ntx_fwd_finalize_launch(q, dtype, dm, plan, partial, nullptr, counter, rowsum, pos_logit,
                                        row_loss, loss_sum, ex.out, ex.geom.rowsum_off, ex.gate, ex.key_buf_elems, st);
     }
     const uint64_t partial_bytes = (uint64_t)(sym ? plan.fwd_max_slots : plan.max_slots) * rows_pad *
@@ -311,7 +336,6 @@ int fwd_impl(const void* q, const void* k, int q_rows, int k_rows, int d, int ld
     const uint64_t fin_bytes = 16 + (((uint64_t)ntx_fwd_finalize_blocks(q_rows, ld) * 8 + 15) & ~15ull);
     float* partial = (float*)workspace;
     unsigned int* counter = (unsigned int*)((char*)workspace + partial_bytes);
-    double* block_sums = (double*)((char*)workspace + partial_bytes + 16);
     float* colpart = sym ? (float*)((char*)workspace + partial_bytes + fin_bytes) : nullptr;
     {
         ProfScope prof(0, st);
@@ -322,7 +346,7 @@ int fwd_impl(const void* q, const void* k, int q_rows, int k_rows, int d, int ld
                                      ex.key_buf_elems, st);
     }
     if (rc) return rc;
-    return ntx_fwd_finalize_launch(q, dtype, dm, plan, partial, colpart, counter, block_sums, rowsum,
+    return ntx_fwd_finalize_launch(q, dtype, dm, plan, partial, colpart, counter, rowsum,
                                    pos_logit, row_loss, loss_sum, ex.out, ex.geom.rowsum_off, ex.gate,
                                    ex.key_buf_elems, st);
 }
@@ -365,7 +389,7 @@ static int bwd_impl(const void* q, const void* k, int q_rows, int k_rows, int d,
     if ((rc = aligned16(workspace, "workspace"))) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     const NtxWeights wt{rowsum_q, rowsum_k, (const float*)w_q, (const float*)w_k, w_stride, w_scale, w_chunk,
-                        w_dtype == NTX_BF16 ? 1 : 0};
+                        w_dtype == NTX_BF16 ? 1 : 0, w_scale};
     const int row_pitch_in = in_ld > 0 ? in_ld : d;
     if (plan.tensor_cores) {
         // the tensor-core kernel also finishes the rows (fold counters at the head of the scratch) whenever the
@@ -380,8 +404,12 @@ static int bwd_impl(const void* q, const void* k, int q_rows, int k_rows, int d,
                           (unsigned int*)(ws + 64), plan.row_blocks, row_pitch_in, normalised,
                           in_dtype == NTX_BF16 ? 1 : 0, fused ? 1 : 0};
         {
+            // with scaled rows the kernel forms e' = e * 2^c1: the factor comes out of its coefficient weights; the
+            // positive-pair weight of the finish keeps the caller's scale
             ProfScope prof(1, st);
-            rc = ntx_tc_bwd_launch((const __nv_bfloat16*)q, (const __nv_bfloat16*)k, dm, plan, wt, partial, ex.gate,
+            NtxWeights wt_tc = wt;
+            wt_tc.coef_scale = w_scale * dm.rowsum_scale;
+            rc = ntx_tc_bwd_launch((const __nv_bfloat16*)q, (const __nv_bfloat16*)k, dm, plan, wt_tc, partial, ex.gate,
                                    ex.key_buf_elems, o, st);
         }
         if (rc || fused) return rc;
@@ -444,7 +472,7 @@ size_t ntx_peer_block_bytes(int q_rows, int ld, int rows_dtype, int world) {
 }
 
 int ntx_peer_l2norm(const void* view0, const void* view1, int n, int d, int in_dtype, const NtxPeerBlocks* blocks,
-                    int ld, int rows_dtype, float* inv_norm, uint32_t* step, void* stream) {
+                    int ld, int rows_dtype, float* inv_norm, float row_scale, uint32_t* step, void* stream) {
     NTX_CHECK_ARG(n >= 1 && d >= 1, "bad sizes n=%d d=%d", n, d);
     NTX_CHECK_ARG(view0 && view1 && inv_norm, "NULL buffer");
     NTX_CHECK_ARG(in_dtype == NTX_F32 || in_dtype == NTX_BF16, "view dtype %d not supported", in_dtype);
@@ -454,12 +482,13 @@ int ntx_peer_l2norm(const void* view0, const void* view1, int n, int d, int in_d
     Exchange ex;
     int rc = make_exchange(blocks, 2 * n, ld, rows_dtype, step, &ex, "ntx_peer_l2norm");
     if (rc) return rc;
+    NTX_CHECK_ARG(row_scale >= 0.f, "row_scale must not be negative");
     return ntx_l2norm_launch(view0, view1, n, d, in_dtype, nullptr, ex.out, ex.geom.keys_off, ex.geom.key_buf_bytes,
-                             step, ld, rows_dtype, inv_norm, (cudaStream_t)stream);
+                             step, ld, rows_dtype, inv_norm, row_scale > 0.f ? row_scale : 1.0f, (cudaStream_t)stream);
 }
 
 int ntx_peer_fwd(const NtxPeerBlocks* blocks, int n_local, int d, int ld, int dtype, float temperature,
-                 const uint32_t* step, float* rowsum, float* pos_logit, float* row_loss, float* loss_sum,
+                 float row_scale, int loss_dtype, const uint32_t* step, float* rowsum, float* pos_logit, float* row_loss, float* loss_sum,
                  void* workspace, size_t workspace_bytes, void* stream) {
     NTX_CHECK_ARG(n_local >= 1 && d >= 1, "bad sizes n_local=%d d=%d", n_local, d);
     NTX_CHECK_ARG(dtype == NTX_F32 || dtype == NTX_BF16, "rows dtype %d not supported", dtype);
@@ -467,7 +496,7 @@ int ntx_peer_fwd(const NtxPeerBlocks* blocks, int n_local, int d, int ld, int dt
     Exchange ex;
     int rc = make_exchange(blocks, q_rows, ld, dtype, step, &ex, "ntx_peer_fwd");
     if (rc) return rc;
-    const NtxLayout lay{n_local, blocks->world, blocks->rank};
+    const NtxLayout lay{n_local, blocks->world, blocks->rank, row_scale, loss_dtype};
     const size_t esz = dtype == NTX_BF16 ? 2 : 4;
     const uint8_t* keys = ex.out.base[blocks->rank] + ex.geom.keys_off;            // key buffer 0 of this rank's block
     const uint8_t* q = keys + (size_t)blocks->rank * q_rows * ld * esz;
@@ -490,7 +519,7 @@ int ntx_peer_post_weights(const NtxPeerBlocks* blocks, int n_local, int ld, int 
 }
 
 int ntx_peer_bwd(const NtxPeerBlocks* blocks, int n_local, int d, int ld, int dtype, float temperature,
-                 const uint32_t* step, const float* rowsum_q, int w_stride, float w_scale, const void* view0,
+                 float row_scale, const uint32_t* step, const float* rowsum_q, int w_stride, float w_scale, const void* view0,
                  const void* view1, int in_dtype, const float* inv_norm, void* dview0, void* dview1, void* workspace,
                  size_t workspace_bytes, void* stream) {
     NTX_CHECK_ARG(n_local >= 1 && d >= 1, "bad sizes n_local=%d d=%d", n_local, d);
@@ -500,7 +529,7 @@ int ntx_peer_bwd(const NtxPeerBlocks* blocks, int n_local, int d, int ld, int dt
     Exchange ex;
     int rc = make_exchange(blocks, q_rows, ld, dtype, step, &ex, "ntx_peer_bwd");
     if (rc) return rc;
-    const NtxLayout lay{n_local, blocks->world, blocks->rank};
+    const NtxLayout lay{n_local, blocks->world, blocks->rank, row_scale, NTX_F32};
     const size_t esz = dtype == NTX_BF16 ? 2 : 4;
     const uint8_t* own = ex.out.base[blocks->rank];
     const uint8_t* keys = own + ex.geom.keys_off;

@@ -135,7 +135,29 @@ struct NtxDims {
     float inv_tau;
     int stable;      // temperature below NTX_MIN_TEMPERATURE (fp32 rows only): max-shifted logsumexp, and the
                      // "rowsum" vectors hold lse_r = log sum_c exp(s_rc) instead of sum_c exp(s_rc - 1/tau)
+    // Rows stored as zhat * sqrt(log2e / tau) (NtxLayout.row_scale, bf16 rows): the similarity MMA then delivers the
+    // exponent log2e/tau * <q, k> itself and the tensor-core epilogues use e' = exp2(exponent) = e * 2^c1 without the
+    // scale-and-shift FFMA2.  The constant factors are taken out again where the sums are used:
+    int scaled;          // 1: rows carry the factor
+    float rowsum_scale;  // 2^-c1 : sums of e' -> sums of exp(s - 1/tau)                    (1 when not scaled)
+    float pos_scale;     // <row, partner row> -> positive logit s: ln 2                     (1/tau when not scaled)
+    float inv_rs;        // 1 / sqrt(c1) : dZ' = C . K' and the rows themselves -> unit rows (1 when not scaled)
+    int loss_bf16;       // loss_sum receives two bf16 values instead of two floats (NtxLayout.loss_dtype)
 };
+#ifdef __CUDACC__
+// loss.py:60-65: the reduced loss, sum and mean (= sum / N * 0.5 over the 2N rows), in the dtype the caller asked for
+__device__ __forceinline__ void ntx_store_loss(float* loss_sum, double total, int q_rows, int bf16) {
+    const float sum = (float)total, mean = (float)(total / (double)q_rows);
+    if (bf16) {
+        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(loss_sum);
+        o[0] = __float2bfloat16_rn(sum);
+        o[1] = __float2bfloat16_rn(mean);
+    } else {
+        loss_sum[0] = sum;
+        loss_sum[1] = mean;
+    }
+}
+#endif
 
 // Backward weights: alpha_r = w_q[r*stride]*scale / rowsum_q[r],  beta_c = w_k[c*stride]*scale / rowsum_k[c]
 struct NtxWeights {
@@ -147,6 +169,7 @@ struct NtxWeights {
     float w_scale;     // 1 / q_rows for mean, 1 otherwise
     int w_chunk;       // > 0 (peer exchange, one weight per RANK): the weight of key c is w_k[c / w_chunk]
     int w_bf16;        // 1: w_q / w_k point at bf16 values (the upstream gradient of a bf16 loss), 0: fp32
+    float coef_scale;  // scale of the weights inside the coefficients alpha, beta: w_scale, times 2^-c1 for scaled rows
 };
 #ifdef __CUDACC__
 // one weight, fp32 or bf16 (read-only for the kernel's lifetime unless `l2`, which skips L1: data written by a peer)
@@ -338,12 +361,12 @@ __device__ __forceinline__ void ntx_fold_init(unsigned int* tag, unsigned int* d
 // launch helpers implemented per translation unit
 int ntx_l2norm_launch(const void* v0, const void* v1, int n, int d, int in_dtype, void* rows, const NtxPeerOut& peers,
                       size_t keys_off, size_t key_buf_bytes, uint32_t* step_out, int ld, int rows_dtype,
-                      float* inv_norm, cudaStream_t st);
+                      float* inv_norm, float row_scale, cudaStream_t st);
 int ntx_post_weights_launch(const void* w, int w_stride, int w_bf16, int q_rows, const NtxPeerOut& peers, size_t weight_off,
                             const uint32_t* step, cudaStream_t st);
 int ntx_make_rows_tmap(void* map, const void* base, int rows, int ld, int box_rows);      // map = CUtensorMap*
 int ntx_project_launch(const void* h0, const void* h1, const void* weight, int n, int hdim, int d, void* rows, int ld,
-                       float* inv_norm, cudaStream_t st);
+                       float* inv_norm, float row_scale, cudaStream_t st);
 // q / k: the rows; with an exchange (gate.step != NULL) they point at key buffer 0 and buffer 1 lies key_buf_elems
 // elements further on -- the kernels pick the buffer of the step
 int ntx_simt_fwd_launch(const float* q, const float* k, const NtxDims& dm, const NtxPlan& plan,
@@ -382,12 +405,12 @@ struct NtxBwdOut {
 int ntx_tc_bwd_launch(const __nv_bfloat16* q, const __nv_bfloat16* k, const NtxDims& dm,
                       const NtxPlan& plan, const NtxWeights& w, float* partial, const NtxGate& gate,
                       size_t key_buf_elems, const NtxBwdOut& out, cudaStream_t st);
-int ntx_fwd_finalize_blocks(int q_rows, int ld);   // grid of the forward finalize (one fp64 block sum each)
+int ntx_fwd_finalize_blocks(int q_rows, int ld);   // grid of the forward finalize
 // colpart != NULL: symmetric forward (upper-triangle partition, column partials added per row)
 // peers.world > 0: the row sums also go to every rank's block (rowsum_off) and the last block raises rflag
 int ntx_fwd_finalize_launch(const void* q, int dtype, const NtxDims& dm, const NtxPlan& plan,
                             const float* partial, const float* colpart, unsigned int* counter,
-                            double* block_sums, float* rowsum, float* pos_logit, float* row_loss,
+                            float* rowsum, float* pos_logit, float* row_loss,
                             float* loss_sum, const NtxPeerOut& peers, size_t rowsum_off, const NtxGate& gate,
                             size_t key_buf_elems, cudaStream_t st);
 int ntx_debug_indices_launch(int n_local, int rank, int32_t* self_col, int32_t* pos_col,

@@ -52,7 +52,7 @@ __global__ void __launch_bounds__(kFwdThreads)
 fwd_finalize_kernel(const T* __restrict__ q, NtxDims dm, int lanes, int tile_rows, int key_tiles,
                     long long Tt, int G, int rows_pad, const float* __restrict__ partial,
                     const float* __restrict__ colpart, unsigned int* __restrict__ counter,
-                    double* __restrict__ block_sums, float* __restrict__ rowsum,
+                    float* __restrict__ rowsum,
                     float* __restrict__ pos_logit, float* __restrict__ row_loss,
                     float* __restrict__ loss_sum, NtxPeerOut peers, size_t rowsum_off, NtxGate gate,
                     size_t key_buf_elems) {
@@ -61,17 +61,30 @@ fwd_finalize_kernel(const T* __restrict__ q, NtxDims dm, int lanes, int tile_row
     // peer exchange: the rows sit in the key buffer of this step; the row sums also go to every rank's block
     const uint32_t step = gate.step ? *gate.step : 0u;      // written by the normalise kernel, earlier on the stream
     if (step & 1u) q += key_buf_elems;
-    // rows of one block share a row block (tile_rows is a multiple of rows_per_block): one slot count.
+    // rows of one block share a row block (tile_rows is a multiple of rows_per_block): one slot count, computed by
+    // every thread (cheaper than a broadcast through shared memory and its barrier).
     // colpart != NULL: the symmetric forward's upper-triangle partition (Tt, G describe that one).
-    __shared__ int ns_sh;
-    if (threadIdx.x == 0) {
-        const int rb0 = (int)((long long)blockIdx.x * ((int)blockDim.x / lanes) / tile_rows);
-        ns_sh = colpart ? ntx_tri_num_slots(Tt, G, key_tiles, rb0) : ntx_num_slots(Tt, G, key_tiles, rb0);
-    }
-    __syncthreads();
+    const int rb0 = (int)((long long)blockIdx.x * ((int)blockDim.x / lanes) / tile_rows);
+    const int ns_sh = colpart ? ntx_tri_num_slots(Tt, G, key_tiles, rb0) : ntx_num_slots(Tt, G, key_tiles, rb0);
     double my_loss = 0.0;
     const int nthreads = (int)blockDim.x;                    // kFwdThreads or 256
     const int rows_per_block = nthreads / lanes;
+    // The positive logit's operands first: their loads are in flight while the partial sums below are gathered
+    // (these kernels are chains of dependent memory round trips; every one that overlaps another is ~0.5 us).
+    const int sub = threadIdx.x % lanes;
+    const int r_raw = blockIdx.x * rows_per_block + threadIdx.x / lanes;
+    const bool live = r_raw < dm.q_rows;
+    const int r = live ? r_raw : dm.q_rows - 1;              // keep every lane in the shuffles
+    float dot = 0.f;
+    {
+        const int p = ntx_pos_row(r, dm.n_local);
+        const T* a = q + (size_t)r * dm.ld;
+        const T* b = q + (size_t)p * dm.ld;
+        for (int c = sub * 4; c < dm.ld; c += lanes * 4) {      // ld is a multiple of 4
+            const float4 x = ld4(a + c), y = ld4(b + c);
+            dot = fmaf(x.x, y.x, fmaf(x.y, y.y, fmaf(x.z, y.z, fmaf(x.w, y.w, dot))));
+        }
+    }
     // Row sums first, with the block laid out rows-fastest so that a warp reads 32 consecutive rows of one
     // slot (or of one row block's column partials): thread t adds the terms part, part + lanes, ... of row
     // t % rows_per_block; the `lanes` parts of a row are then added in part order.
@@ -117,24 +130,13 @@ fwd_finalize_kernel(const T* __restrict__ q, NtxDims dm, int lanes, int tile_row
         rs_sh[part * rows_per_block + row_local] = c;
     }
     __syncthreads();
-    const int sub = threadIdx.x % lanes;
-    const int r_raw = blockIdx.x * rows_per_block + threadIdx.x / lanes;
-    const bool live = r_raw < dm.q_rows;
-    const int r = live ? r_raw : dm.q_rows - 1;              // keep every lane in the shuffles
     {
-        const int p = ntx_pos_row(r, dm.n_local);
-        const T* a = q + (size_t)r * dm.ld;
-        const T* b = q + (size_t)p * dm.ld;
-        float dot = 0.f;
-        for (int c = sub * 4; c < dm.ld; c += lanes * 4) {      // ld is a multiple of 4
-            const float4 x = ld4(a + c), y = ld4(b + c);
-            dot = fmaf(x.x, y.x, fmaf(x.y, y.y, fmaf(x.z, y.z, fmaf(x.w, y.w, dot))));
-        }
         dot = group_sum(dot, lanes);
         if (sub == 0 && live) {
             float R = 0.f;
             for (int part = 0; part < lanes; ++part) R += rs_sh[part * rows_per_block + threadIdx.x / lanes];
-            const float pos = dot * dm.inv_tau;
+            const float pos = dot * dm.pos_scale;            // 1/tau, or ln 2 for rows that carry sqrt(log2e/tau)
+            R *= dm.rowsum_scale;                            // sums of e * 2^c1 -> sums of exp(s - 1/tau) (scaled rows)
             float l;
             if (dm.stable) {
                 R *= 0.6931471805599453f;                    // lse_r in natural-log units: what "rowsum" holds in this mode
@@ -150,9 +152,10 @@ fwd_finalize_kernel(const T* __restrict__ q, NtxDims dm, int lanes, int tile_row
                 ntx_peer_st_f32(peers, rowsum_off + ((size_t)peers.rank * dm.q_rows + r) * sizeof(float), R);
         }
     }
-    // Block sums in a fixed order, then the last block standing adds the block sums in block
-    // order: deterministic whichever block finishes last (loss.py:60-65).
-    __shared__ bool is_last;
+    // The block's loss sum, warps added in order, goes into ONE 64-bit word as fixed point (16 fractional bits, upper
+    // 44 bits) together with a count of arrived blocks (lower 20 bits): integer addition does not depend on the
+    // order of arrival, so the total is the same in every run, and the block that brings the count to the grid size
+    // holds the total in the value its own atomicAdd returned -- no second pass over per-block sums (loss.py:60-65).
     __shared__ double part[kFwdThreads / 32];
     double acc = my_loss;
 #pragma unroll
@@ -162,26 +165,17 @@ fwd_finalize_kernel(const T* __restrict__ q, NtxDims dm, int lanes, int tile_row
     if (threadIdx.x == 0) {
         double v = 0.0;
         for (int w = 0; w < nthreads / 32; ++w) v += part[w];
-        block_sums[blockIdx.x] = v;
-        __threadfence();                                     // also orders the block's peer stores (barrier above)
-        is_last = atomicAdd(counter, 1u) == gridDim.x - 1;
-    }
-    __syncthreads();
-    if (!is_last) return;
-    __threadfence();
-    acc = 0.0;
-    for (int i = threadIdx.x; i < (int)gridDim.x; i += nthreads) acc += __ldcg(block_sums + i);
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = acc;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        double v = 0.0;
-        for (int w = 0; w < nthreads / 32; ++w) v += part[w];
-        loss_sum[0] = (float)v;                              // reduction="sum"
-        loss_sum[1] = (float)(v / (double)dm.q_rows);        // reduction="mean": sum / N * 0.5, rows = 2N
-        *counter = 0;
-        if (peers.world > 0) ntx_raise_flags(peers, NTX_CTL_RFLAG, step);   // every block's row sums are out
+        const long long fixed = __double2ll_rn(v * 65536.0);
+        const unsigned long long add = ((unsigned long long)fixed << 20) + 1ull;
+        if (peers.world > 0) __threadfence();                // the block's peer stores (barrier above) before its arrival
+        unsigned long long* word = reinterpret_cast<unsigned long long*>(counter);
+        const unsigned long long old = atomicAdd(word, add);
+        if ((old & 0xFFFFFull) == (unsigned long long)gridDim.x - 1ull) {
+            const long long total = (long long)(old + add) >> 20;             // arithmetic shift keeps the sign
+            ntx_store_loss(loss_sum, (double)total / 65536.0, dm.q_rows, dm.loss_bf16);   // "sum" and "mean" (sum / N * 0.5)
+            *word = 0ull;
+            if (peers.world > 0) ntx_raise_flags(peers, NTX_CTL_RFLAG, step);   // every block's row sums are out
+        }
     }
 }
 
@@ -228,7 +222,8 @@ bwd_finalize_vec_kernel(BwdFinArgs A, int lanes, const TIn* __restrict__ view0,
     const TIn* zp = p < n ? view0 + (size_t)p * A.in_ld : view1 + (size_t)(p - n) * A.in_ld;
     TIn* out = r < n ? dview0 + (size_t)r * d : dview1 + (size_t)(r - n) * d;
     const float inr = __ldg(A.inv_norm + r), inp = __ldg(A.inv_norm + p);
-    const float sr = A.normalised ? 1.f : inr, sp = A.normalised ? 1.f : inp;   // input rows -> unit rows
+    // input rows -> unit rows: 1/||z|| for the caller's views, 1/sqrt(c1) for normalised rows that carry the scale
+    const float sr = A.normalised ? dm.inv_rs : inr, sp = A.normalised ? dm.inv_rs : inp;
     const float wpair = pair_weight(A.w, r, p);
     const float* part = A.partial + (size_t)r * A.d_pad;
     const size_t slot_stride = (size_t)A.rows_pad * A.d_pad;
@@ -250,9 +245,9 @@ bwd_finalize_vec_kernel(BwdFinArgs A, int lanes, const TIn* __restrict__ view0,
                 for (int u = 0; u < 4; ++u) { acc.x += t[u].x; acc.y += t[u].y; acc.z += t[u].z; acc.w += t[u].w; }
             }
             const float4 zpv = ld4(zp + c), zrv = ld4(zr + c);
-            const float k = wpair * sp, it = dm.inv_tau;
-            g[v] = make_float4((acc.x - k * zpv.x) * it, (acc.y - k * zpv.y) * it, (acc.z - k * zpv.z) * it,
-                               (acc.w - k * zpv.w) * it);
+            const float k = wpair * sp, it = dm.inv_tau, ir = dm.inv_rs;       // dZ' = C . K' carries sqrt(c1)
+            g[v] = make_float4((acc.x * ir - k * zpv.x) * it, (acc.y * ir - k * zpv.y) * it, (acc.z * ir - k * zpv.z) * it,
+                               (acc.w * ir - k * zpv.w) * it);
             zh[v] = make_float4(zrv.x * sr, zrv.y * sr, zrv.z * sr, zrv.w * sr);
             proj = fmaf(zh[v].x, g[v].x, fmaf(zh[v].y, g[v].y, fmaf(zh[v].z, g[v].z, fmaf(zh[v].w, g[v].w, proj))));
         }
@@ -291,7 +286,7 @@ bwd_finalize_kernel(BwdFinArgs A, const TIn* __restrict__ view0, const TIn* __re
     const TIn* zp = p < n ? view0 + (size_t)p * A.in_ld : view1 + (size_t)(p - n) * A.in_ld;
     TIn* out = r < n ? dview0 + (size_t)r * d : dview1 + (size_t)(r - n) * d;
     const float inr = __ldg(A.inv_norm + r), inp = __ldg(A.inv_norm + p);
-    const float sr = A.normalised ? 1.f : inr, sp = A.normalised ? 1.f : inp;
+    const float sr = A.normalised ? dm.inv_rs : inr, sp = A.normalised ? dm.inv_rs : inp;
     const float wpair = pair_weight(A.w, r, p);
     const float* part = A.partial + (size_t)r * A.d_pad;
     const size_t slot_stride = (size_t)A.rows_pad * A.d_pad;
@@ -299,7 +294,7 @@ bwd_finalize_kernel(BwdFinArgs A, const TIn* __restrict__ view0, const TIn* __re
     auto dzhat = [&](int c) {
         float acc = 0.f;
         for (int s = 0; s < ns; ++s) acc += __ldg(part + s * slot_stride + c);
-        return (acc - wpair * (ldf(zp, c) * sp)) * dm.inv_tau;
+        return (acc * dm.inv_rs - wpair * (ldf(zp, c) * sp)) * dm.inv_tau;
     };
     float proj = 0.f;
     for (int c = lane; c < d; c += 32) proj = fmaf(ldf(zr, c) * sr, dzhat(c), proj);
@@ -381,7 +376,7 @@ int ntx_fwd_finalize_blocks(int q_rows, int ld) {
 
 int ntx_fwd_finalize_launch(const void* q, int dtype, const NtxDims& dm, const NtxPlan& plan,
                             const float* partial, const float* colpart, unsigned int* counter,
-                            double* block_sums, float* rowsum, float* pos_logit, float* row_loss,
+                            float* rowsum, float* pos_logit, float* row_loss,
                             float* loss_sum, const NtxPeerOut& peers, size_t rowsum_off, const NtxGate& gate,
                             size_t key_buf_elems, cudaStream_t st) {
     const long long T = colpart ? (long long)plan.row_blocks * (plan.row_blocks + 1) / 2
@@ -394,12 +389,12 @@ int ntx_fwd_finalize_launch(const void* q, int dtype, const NtxDims& dm, const N
     if (dtype == NTX_F32)
         NTX_CUDA(ntx_launch_dep(fwd_finalize_kernel<float>, grid, threads, 0, st, (const float*)q, dm, lanes,
                                 plan.tile_rows, plan.key_tiles, T, G, rows_pad, partial, colpart, counter,
-                                block_sums, rowsum, pos_logit, row_loss, loss_sum, peers, rowsum_off, gate,
+                                rowsum, pos_logit, row_loss, loss_sum, peers, rowsum_off, gate,
                                 key_buf_elems));
     else
         NTX_CUDA(ntx_launch_dep(fwd_finalize_kernel<__nv_bfloat16>, grid, threads, 0, st,
                                 (const __nv_bfloat16*)q, dm, lanes, plan.tile_rows, plan.key_tiles, T, G, rows_pad,
-                                partial, colpart, counter, block_sums, rowsum, pos_logit, row_loss, loss_sum, peers,
+                                partial, colpart, counter, rowsum, pos_logit, row_loss, loss_sum, peers,
                                 rowsum_off, gate, key_buf_elems));
     return NTX_OK;
 }

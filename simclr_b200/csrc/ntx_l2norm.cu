@@ -68,7 +68,7 @@ template <typename TIn, typename TOut, bool kVector>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 l2norm_kernel(const TIn* __restrict__ view0, const TIn* __restrict__ view1, int n, int d,
               TOut* __restrict__ rows_local, NtxPeerOut peers, size_t keys_off, size_t key_buf_bytes,
-              uint32_t* __restrict__ step_out, int ld, float* __restrict__ inv_norm, int lanes) {
+              uint32_t* __restrict__ step_out, int ld, float* __restrict__ inv_norm, int lanes, float row_scale) {
     ntx_dep_trigger();
     ntx_dep_wait();
     const int sub = threadIdx.x % lanes;
@@ -118,7 +118,7 @@ l2norm_kernel(const TIn* __restrict__ view0, const TIn* __restrict__ view1, int 
                 if (c < d) {
                     Vec<TIn>::load(src + c, v);
 #pragma unroll
-                    for (int i = 0; i < V; ++i) v[i] = v[i] / denom;
+                    for (int i = 0; i < V; ++i) v[i] = v[i] / denom * row_scale;     // row_scale == 1: exact
                 } else {
 #pragma unroll
                     for (int i = 0; i < V; ++i) v[i] = 0.f;
@@ -141,7 +141,7 @@ l2norm_kernel(const TIn* __restrict__ view0, const TIn* __restrict__ view1, int 
             }
         } else {
             for (int c = sub; c < ld; c += lanes) {
-                const float x = c < d ? to_f32(src[c]) / denom : 0.f;
+                const float x = c < d ? to_f32(src[c]) / denom * row_scale : 0.f;
                 for (int p = 0; p < ndst; ++p) store1(dst_rows(p) + dst_off + c, x);
             }
         }
@@ -163,7 +163,7 @@ l2norm_kernel(const TIn* __restrict__ view0, const TIn* __restrict__ view1, int 
 
 template <typename TIn, typename TOut>
 int launch(const void* v0, const void* v1, int n, int d, void* rows, const NtxPeerOut& peers, size_t keys_off,
-           size_t key_buf_bytes, uint32_t* step_out, int ld, float* inv_norm, cudaStream_t st) {
+           size_t key_buf_bytes, uint32_t* step_out, int ld, float* inv_norm, float row_scale, cudaStream_t st) {
     constexpr int V = Vec<TIn>::N;
     const bool vec = (d % V == 0) && (ld % V == 0) &&
                      (reinterpret_cast<uintptr_t>(v0) % 16 == 0) &&
@@ -182,11 +182,11 @@ int launch(const void* v0, const void* v1, int n, int d, void* rows, const NtxPe
     if (vec)
         NTX_CUDA(ntx_launch_dep(l2norm_kernel<TIn, TOut, true>, grid, kWarpsPerBlock * 32, 0, st, (const TIn*)v0,
                                 (const TIn*)v1, n, d, (TOut*)rows, peers, keys_off, key_buf_bytes, step_out, ld,
-                                inv_norm, lanes));
+                                inv_norm, lanes, row_scale));
     else
         NTX_CUDA(ntx_launch_dep(l2norm_kernel<TIn, TOut, false>, grid, kWarpsPerBlock * 32, 0, st, (const TIn*)v0,
                                 (const TIn*)v1, n, d, (TOut*)rows, peers, keys_off, key_buf_bytes, step_out, ld,
-                                inv_norm, lanes));
+                                inv_norm, lanes, row_scale));
     return NTX_OK;
 }
 
@@ -232,15 +232,15 @@ int ntx_post_weights_launch(const void* w, int w_stride, int w_bf16, int q_rows,
 
 int ntx_l2norm_launch(const void* v0, const void* v1, int n, int d, int in_dtype, void* rows, const NtxPeerOut& peers,
                       size_t keys_off, size_t key_buf_bytes, uint32_t* step_out, int ld, int rows_dtype,
-                      float* inv_norm, cudaStream_t st) {
+                      float* inv_norm, float row_scale, cudaStream_t st) {
     if (in_dtype == NTX_F32 && rows_dtype == NTX_F32)
-        return launch<float, float>(v0, v1, n, d, rows, peers, keys_off, key_buf_bytes, step_out, ld, inv_norm, st);
+        return launch<float, float>(v0, v1, n, d, rows, peers, keys_off, key_buf_bytes, step_out, ld, inv_norm, row_scale, st);
     if (in_dtype == NTX_F32 && rows_dtype == NTX_BF16)
-        return launch<float, __nv_bfloat16>(v0, v1, n, d, rows, peers, keys_off, key_buf_bytes, step_out, ld, inv_norm, st);
+        return launch<float, __nv_bfloat16>(v0, v1, n, d, rows, peers, keys_off, key_buf_bytes, step_out, ld, inv_norm, row_scale, st);
     if (in_dtype == NTX_BF16 && rows_dtype == NTX_BF16)
-        return launch<__nv_bfloat16, __nv_bfloat16>(v0, v1, n, d, rows, peers, keys_off, key_buf_bytes, step_out, ld, inv_norm, st);
+        return launch<__nv_bfloat16, __nv_bfloat16>(v0, v1, n, d, rows, peers, keys_off, key_buf_bytes, step_out, ld, inv_norm, row_scale, st);
     if (in_dtype == NTX_BF16 && rows_dtype == NTX_F32)
-        return launch<__nv_bfloat16, float>(v0, v1, n, d, rows, peers, keys_off, key_buf_bytes, step_out, ld, inv_norm, st);
+        return launch<__nv_bfloat16, float>(v0, v1, n, d, rows, peers, keys_off, key_buf_bytes, step_out, ld, inv_norm, row_scale, st);
     ntx_set_error("ntx_l2norm: unsupported dtype pair (%d -> %d)", in_dtype, rows_dtype);
     return NTX_E_ARG;
 }

@@ -30,7 +30,7 @@ template <int NP>   // NP = padded output width (64, 128 or 256) = MMA N = TMEM 
 __global__ void __launch_bounds__(kThreads, 1)
 project_l2norm_kernel(const __grid_constant__ CUtensorMap tmap_h0, const __grid_constant__ CUtensorMap tmap_h1,
                       const __grid_constant__ CUtensorMap tmap_w, int n, int hdim, int d, int tiles_per_view,
-                      __nv_bfloat16* __restrict__ rows, int ld, float* __restrict__ inv_norm) {
+                      __nv_bfloat16* __restrict__ rows, int ld, float* __restrict__ inv_norm, float row_scale) {
     constexpr uint32_t kBBytes = NP * 128;    // [NP rows x 64 bf16]
     constexpr uint32_t kStageBytes = kABytes + kBBytes;
     constexpr int kStages = ProjStages<NP>::N;
@@ -128,8 +128,8 @@ project_l2norm_kernel(const __grid_constant__ CUtensorMap tmap_h0, const __grid_
 #pragma unroll
                     for (int h = 0; h < 4; ++h) {
                         const int j = j8 * 8 + h * 2;
-                        const float x0 = (c + j < d) ? __uint_as_float(v[j]) / denom : 0.f;
-                        const float x1 = (c + j + 1 < d) ? __uint_as_float(v[j + 1]) / denom : 0.f;
+                        const float x0 = (c + j < d) ? __uint_as_float(v[j]) / denom * row_scale : 0.f;
+                        const float x1 = (c + j + 1 < d) ? __uint_as_float(v[j + 1]) / denom * row_scale : 0.f;
                         __nv_bfloat162 hh = __floats2bfloat162_rn(x0, x1);
                         pk[h] = *reinterpret_cast<uint32_t*>(&hh);
                     }
@@ -145,28 +145,28 @@ project_l2norm_kernel(const __grid_constant__ CUtensorMap tmap_h0, const __grid_
 
 template <int NP>
 int launch(const CUtensorMap& m0, const CUtensorMap& m1, const CUtensorMap& mw, int n, int hdim, int d, void* rows,
-           int ld, float* inv_norm, cudaStream_t st) {
+           int ld, float* inv_norm, float row_scale, cudaStream_t st) {
     const size_t smem = (size_t)ProjStages<NP>::N * (kABytes + NP * 128) + sizeof(ProjCtl);
     NTX_SMEM_OPT_IN(project_l2norm_kernel<NP>, smem);
     const int tiles_per_view = (n + 127) / 128;
     NTX_CUDA(ntx_launch_dep(project_l2norm_kernel<NP>, 2 * tiles_per_view, kThreads, smem, st, m0, m1, mw, n, hdim, d,
-                            tiles_per_view, (__nv_bfloat16*)rows, ld, inv_norm));
+                            tiles_per_view, (__nv_bfloat16*)rows, ld, inv_norm, row_scale));
     return NTX_OK;
 }
 
 }  // namespace
 
 int ntx_project_launch(const void* h0, const void* h1, const void* weight, int n, int hdim, int d, void* rows, int ld,
-                       float* inv_norm, cudaStream_t st) {
+                       float* inv_norm, float row_scale, cudaStream_t st) {
     CUtensorMap m0, m1, mw;
     int rc;
     if ((rc = ntx_make_rows_tmap(&m0, h0, n, hdim, 128)) || (rc = ntx_make_rows_tmap(&m1, h1, n, hdim, 128)) ||
         (rc = ntx_make_rows_tmap(&mw, weight, d, hdim, ld)))
         return rc;
     switch (ld) {
-        case 64: return launch<64>(m0, m1, mw, n, hdim, d, rows, ld, inv_norm, st);
-        case 128: return launch<128>(m0, m1, mw, n, hdim, d, rows, ld, inv_norm, st);
-        case 256: return launch<256>(m0, m1, mw, n, hdim, d, rows, ld, inv_norm, st);
+        case 64: return launch<64>(m0, m1, mw, n, hdim, d, rows, ld, inv_norm, row_scale, st);
+        case 128: return launch<128>(m0, m1, mw, n, hdim, d, rows, ld, inv_norm, row_scale, st);
+        case 256: return launch<256>(m0, m1, mw, n, hdim, d, rows, ld, inv_norm, row_scale, st);
     }
     ntx_set_error("ntx_project_l2norm: row pitch %d not built (64, 128, 256)", ld);
     return NTX_E_UNSUPPORTED;

@@ -106,7 +106,8 @@ simt_fwd_kernel(const float* __restrict__ q, const float* __restrict__ k, NtxDim
     const int G = gridDim.x, cta = blockIdx.x;
     const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
     const long long t_begin = ntx_chunk_begin(T, G, cta), t_end = ntx_chunk_begin(T, G, cta + 1);
-    if (cta == 0 && threadIdx.x == 0) *done_counter = 0;    // ticket of the finalize kernel
+    if (cta == 0 && threadIdx.x == 0)                       // the finalize kernel's 64-bit arrival word
+        *reinterpret_cast<unsigned long long*>(done_counter) = 0ull;
 
     int cur_rb = -1;
     float rowsum[4] = {0.f, 0.f, 0.f, 0.f};

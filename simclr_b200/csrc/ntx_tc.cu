@@ -247,7 +247,9 @@ template <int NS> struct FwdCtl {
     alignas(16) double fin_sum[4];     // finish phase: per-warp loss sums of group 0
 };
 
-template <int NDB>
+// kScaled: the rows carry sqrt(log2e / tau) (NtxDims.scaled), so a similarity value IS the exponent: no FFMA2, and
+// the row sums are sums of e' = e * 2^c1 (NtxDims.rowsum_scale takes the factor out where they are finished)
+template <int NDB, bool kScaled>
 __global__ void __launch_bounds__(kFwdThreads, 1)
 tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
               const __grid_constant__ CUtensorMap tmap_q1, const __grid_constant__ CUtensorMap tmap_k1,
@@ -393,7 +395,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
 
         if (threadIdx.x == 0) {
             if (fold.enabled) ntx_fold_init(fold.tag, fold.done_total, fold.arrive, fold.row_blocks, cta);
-            else if (cta == 0) *fold.legacy_ticket = 0;          // ticket of the finalize kernel
+            else if (cta == 0) *reinterpret_cast<unsigned long long*>(fold.legacy_ticket) = 0ull;   // the finalize kernel's arrival word
         }
         int rb = (int)(t_begin / key_tiles), kt = (int)(t_begin % key_tiles);
         int own = 0, turn = 0;
@@ -428,8 +430,8 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
                         // polynomial for NTX_FWD_POLY of every 4 pairs, row sums by FADD2
 #pragma unroll
                         for (int j = 0; j < 16; ++j) {
-                            const f32x2 x = fma2(pack2(__uint_as_float(v[ch & 1][2 * j]),
-                                                       __uint_as_float(v[ch & 1][2 * j + 1])), c1x2, nc1x2);
+                            const f32x2 raw = pack2(__uint_as_float(v[ch & 1][2 * j]), __uint_as_float(v[ch & 1][2 * j + 1]));
+                            const f32x2 x = kScaled ? raw : fma2(raw, c1x2, nc1x2);
                             const bool poly = NTX_FWD_POLY > 0 && ((j * NTX_FWD_POLY) & 3) < NTX_FWD_POLY;
                             pacc[j & 1] = add2(pacc[j & 1], poly ? ex2_pair_poly(x) : ex2_pair_mufu(x));
                         }
@@ -437,14 +439,14 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
 #pragma unroll
                         for (int j = 0; j < 32; ++j) {
                             const int col = kt * 128 + ch * 32 + j;
-                            float e = ex2(fmaf(__uint_as_float(v[ch & 1][j]), c1, nc1));
+                            float e = ex2(kScaled ? __uint_as_float(v[ch & 1][j]) : fmaf(__uint_as_float(v[ch & 1][j]), c1, nc1));
                             if (col == self || col >= dm.k_rows) e = 0.f;   // mask of loss.py:38,46-47
                             if (col == my_pos) pos_val = __uint_as_float(v[ch & 1][j]);
                             acc[j & 3] += e;
                         }
                     }
                 }
-                if (has_pos && my_pos >= 0 && my_pos / 128 == kt) out.pos_logit[my_row] = pos_val * dm.inv_tau;
+                if (has_pos && my_pos >= 0 && my_pos / 128 == kt) out.pos_logit[my_row] = pos_val * dm.pos_scale;
             }
             if (last_of_seg) flush(rb);
             if (++kt == key_tiles) { kt = 0; ++rb; }
@@ -478,6 +480,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
 #pragma unroll
                         for (int u = 0; u < 8; ++u) R += t[u];
                     }
+                    R *= dm.rowsum_scale;
                     const float pos = __ldcg(out.pos_logit + row);
                     const float l = logf(R) + dm.inv_tau - pos;
                     out.rowsum[row] = R;
@@ -514,8 +517,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
                     named_bar_sync(3, 128);
                     if (tid == 0) {
                         const double v = (ctl->fin_sum[0] + ctl->fin_sum[1]) + (ctl->fin_sum[2] + ctl->fin_sum[3]);
-                        out.loss_sum[0] = (float)v;                              // reduction="sum"
-                        out.loss_sum[1] = (float)(v / (double)dm.q_rows);        // reduction="mean": sum / N * 0.5, rows = 2N
+                        ntx_store_loss(out.loss_sum, v, dm.q_rows, dm.loss_bf16);
                         *fold.done_total = 0u;
                         if (out.peers.world > 0)                                 // every rank's row sums are out
                             ntx_raise_flags(out.peers, NTX_CTL_RFLAG, gate.step ? *gate.step : 0u);
@@ -567,7 +569,7 @@ struct TriIter {
     }
 };
 
-template <int NDB>
+template <int NDB, bool kScaled>
 __global__ void __launch_bounds__(kSymThreads, 1)
 tc_fwd_sym_kernel(const __grid_constant__ CUtensorMap tmap, NtxDims dm, int key_tiles, long long T,
                   int rows_pad, float* __restrict__ partial, float* __restrict__ colpart,
@@ -619,7 +621,8 @@ tc_fwd_sym_kernel(const __grid_constant__ CUtensorMap tmap, NtxDims dm, int key_
     constexpr uint32_t tmem_base = 0;
     // everything above overlapped the tail of the previous kernel on the stream; from here on its results are read
     ntx_dep_wait();
-    if (threadIdx.x == 0 && cta == 0) *done_counter = 0;    // ticket of the finalize kernel
+    if (threadIdx.x == 0 && cta == 0)                        // the finalize kernel's 64-bit arrival word
+        *reinterpret_cast<unsigned long long*>(done_counter) = 0ull;
 
     if (warp == kProducerWarp) {
         if (elect_one()) {
@@ -802,8 +805,8 @@ tc_fwd_sym_kernel(const __grid_constant__ CUtensorMap tmap, NtxDims dm, int key_
 #pragma unroll
                             for (int h = 0; h < 4; ++h) {
                                 const int j = j8 * 8 + h * 2;
-                                const f32x2 x = fma2(pack2(__uint_as_float(v[ch & 1][j]),
-                                                           __uint_as_float(v[ch & 1][j + 1])), c1x2, nc1x2);
+                                const f32x2 raw = pack2(__uint_as_float(v[ch & 1][j]), __uint_as_float(v[ch & 1][j + 1]));
+                                const f32x2 x = kScaled ? raw : fma2(raw, c1x2, nc1x2);
                                 const bool poly = NTX_SYM_POLY > 0 && (((j8 * 4 + h) * NTX_SYM_POLY) & 3) < NTX_SYM_POLY;
                                 const f32x2 e = poly ? ex2_pair_poly(x) : ex2_pair_mufu(x);
                                 pacc[h & 1] = add2(pacc[h & 1], e);
@@ -825,8 +828,9 @@ tc_fwd_sym_kernel(const __grid_constant__ CUtensorMap tmap, NtxDims dm, int key_
                             for (int h = 0; h < 4; ++h) {
                                 const int j = j8 * 8 + h * 2;
                                 const int col = kt * 128 + ch * 32 + j;
-                                float e0 = ex2(fmaf(__uint_as_float(v[ch & 1][j]), c1, nc1));
-                                float e1 = ex2(fmaf(__uint_as_float(v[ch & 1][j + 1]), c1, nc1));
+                                float e0 = ex2(kScaled ? __uint_as_float(v[ch & 1][j]) : fmaf(__uint_as_float(v[ch & 1][j]), c1, nc1));
+                                float e1 = ex2(kScaled ? __uint_as_float(v[ch & 1][j + 1])
+                                                       : fmaf(__uint_as_float(v[ch & 1][j + 1]), c1, nc1));
                                 if (col == self || col >= dm.k_rows || !row_ok) e0 = 0.f;   // mask of loss.py:38,46-47
                                 if (col + 1 == self || col + 1 >= dm.k_rows || !row_ok) e1 = 0.f;
                                 acc[h] += e0 + e1;
@@ -895,6 +899,7 @@ struct BwdWeights {
     float w_scale;
     int w_chunk;        // > 0: one weight per rank, key c takes w_k[c / w_chunk]
     int w_bf16;         // weights are bf16 values
+    float coef_scale;   // scale of the weights in alpha / beta (w_scale, times 2^-c1 for scaled rows)
 };
 
 // The rows of a finished row block, turned into dview0 / dview1 inside the backward kernel (see ntx_common.cuh,
@@ -934,7 +939,7 @@ __device__ __forceinline__ void st4_any(void* base, size_t i, float4 v, int bf16
 }
 
 // 32 similarity values of one row -> 32 coefficients, packed bf16x2
-template <bool kEdge>
+template <bool kEdge, bool kScaled>
 __device__ __forceinline__ void coef_chunk(const uint32_t (&v)[32], uint32_t (&pk)[16], const float* bt,
                                            float alpha, float c1, float nc1, int col0, int self, int k_rows,
                                            bool row_ok) {
@@ -946,7 +951,8 @@ __device__ __forceinline__ void coef_chunk(const uint32_t (&v)[32], uint32_t (&p
 #pragma unroll
         for (int h = 0; h < 2; ++h) {        // two keys per instruction (FFMA2, FADD2, FMUL2)
             const int j = j4 * 4 + h * 2;
-            const f32x2 x = fma2(pack2(__uint_as_float(v[j]), __uint_as_float(v[j + 1])), c1x2, nc1x2);
+            const f32x2 raw = pack2(__uint_as_float(v[j]), __uint_as_float(v[j + 1]));
+            const f32x2 x = kScaled ? raw : fma2(raw, c1x2, nc1x2);
             const bool poly = !kEdge && NTX_BWD_POLY > 0 && (((j4 * 2 + h) * NTX_BWD_POLY) & 3) < NTX_BWD_POLY;
             const f32x2 e = poly ? ex2_pair_poly(x) : ex2_pair_mufu(x);
             float c0, c1v;
@@ -964,7 +970,7 @@ __device__ __forceinline__ void coef_chunk(const uint32_t (&v)[32], uint32_t (&p
 
 // kGate: peer exchange (the row sums and weights of other ranks' keys arrive during the kernel); a separate
 // instantiation so the single-GPU kernel keeps exactly its own instruction stream
-template <int NDB, bool kGate>
+template <int NDB, bool kGate, bool kScaled>
 __global__ void __launch_bounds__(BwdCfg<NDB>::kThreads, 1)
 tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
               const __grid_constant__ CUtensorMap tmap_q1, const __grid_constant__ CUtensorMap tmap_k1,
@@ -1187,14 +1193,14 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
             if (new_seg) {
                 const int row = rb * 128 + row_in_tile;
                 row_ok = row < dm.q_rows;
-                alpha = row_ok ? ntx_ld_weight(wt.w_q, (size_t)row * wt.w_stride, wt.w_bf16) * wt.w_scale / __ldg(wt.rowsum_q + row)
+                alpha = row_ok ? ntx_ld_weight(wt.w_q, (size_t)row * wt.w_stride, wt.w_bf16) * wt.coef_scale / __ldg(wt.rowsum_q + row)
                                : 0.f;
                 new_seg = false;
             }
             const bool last_of_seg = (i + 1 == n_tiles) || (kt + 1 == key_tiles);
             if (turn == g) {
                 float* bt = ctl->beta[g];
-                const float beta = w_next * wt.w_scale / r_next;
+                const float beta = w_next * wt.coef_scale / r_next;
                 named_bar_sync(2 + g, 128);          // everyone is done with the previous tile's values
                 bt[tid_g] = beta;
                 named_bar_sync(2 + g, 128);
@@ -1214,9 +1220,9 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
                     tmem_ld_32x32(taddr + ch * 32, v);
                     tmem_ld_wait_dep(v);
                     if (!edge)
-                        coef_chunk<false>(v, pk, bt + ch * 32, alpha, c1, nc1, 0, 0, 0, true);
+                        coef_chunk<false, kScaled>(v, pk, bt + ch * 32, alpha, c1, nc1, 0, 0, 0, true);
                     else
-                        coef_chunk<true>(v, pk, bt + ch * 32, alpha, c1, nc1, kt * 128 + ch * 32, self,
+                        coef_chunk<true, kScaled>(v, pk, bt + ch * 32, alpha, c1, nc1, kt * 128 + ch * 32, self,
                                          dm.k_rows, row_ok);
                     // bf16 pairs over fp32 columns already read: keys [32ch, 32ch+32) -> columns [16ch, +16)
                     tmem_st_32x16(taddr + ch * 16, pk);
@@ -1269,7 +1275,8 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
                     const void* zp_base = p < n ? fuse.view0 : fuse.view1;
                     const size_t zr_off = (size_t)(r < n ? r : r - n) * fuse.in_ld, zp_off = (size_t)(p < n ? p : p - n) * fuse.in_ld;
                     const float inr = __ldg(fuse.inv_norm + r), inp = __ldg(fuse.inv_norm + p);
-                    const float sr = fuse.normalised ? 1.f : inr, sp = fuse.normalised ? 1.f : inp;
+                    // rows -> unit rows: 1/||z|| for the caller's inputs, 1/sqrt(c1) for normalised rows that carry the scale
+                    const float sr = fuse.normalised ? dm.inv_rs : inr, sp = fuse.normalised ? dm.inv_rs : inp;
                     const float wpair = (ntx_ld_weight(wt.w_q, (size_t)r * wt.w_stride, wt.w_bf16) +
                                          ntx_ld_weight(wt.w_q, (size_t)p * wt.w_stride, wt.w_bf16)) * wt.w_scale;
                     const float* part = partial + (size_t)r * DP;
@@ -1291,9 +1298,9 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
                             }
                             const float4 zpv = ld4_any(zp_base, zp_off + c, fuse.in_bf16);
                             const float4 zrv = ld4_any(zr_base, zr_off + c, fuse.in_bf16);
-                            const float k = wpair * sp, it = dm.inv_tau;
-                            gq[v] = make_float4((acc.x - k * zpv.x) * it, (acc.y - k * zpv.y) * it, (acc.z - k * zpv.z) * it,
-                                                (acc.w - k * zpv.w) * it);
+                            const float k = wpair * sp, it = dm.inv_tau, ir = dm.inv_rs;     // dZ' = C . K' carries sqrt(c1)
+                            gq[v] = make_float4((acc.x * ir - k * zpv.x) * it, (acc.y * ir - k * zpv.y) * it,
+                                                (acc.z * ir - k * zpv.z) * it, (acc.w * ir - k * zpv.w) * it);
                             zh[v] = make_float4(zrv.x * sr, zrv.y * sr, zrv.z * sr, zrv.w * sr);
                             proj = fmaf(zh[v].x, gq[v].x, fmaf(zh[v].y, gq[v].y, fmaf(zh[v].z, gq[v].z, fmaf(zh[v].w, gq[v].w, proj))));
                         }
@@ -1413,24 +1420,30 @@ int make_row_maps(RowMaps* m, const __nv_bfloat16* q, const __nv_bfloat16* k, co
     return NTX_OK;
 }
 
+template <int NDB, bool kScaled>
+int launch_fwd_s(const RowMaps& m, const NtxDims& dm, const NtxPlan& plan, float* partial, const NtxFoldScratch& fold,
+                 const NtxFwdOut& out, const NtxGate& gate, cudaStream_t st) {
+    const size_t smem = fwd_smem_bytes<NDB>();
+    NTX_SMEM_OPT_IN((tc_fwd_kernel<NDB, kScaled>), smem);
+    const long long T = (long long)plan.row_blocks * plan.key_tiles;
+    NTX_CUDA(ntx_launch_dep(tc_fwd_kernel<NDB, kScaled>, plan.grid, kFwdThreads, smem, st, m.q[0], m.k[0], m.q[1], m.k[1],
+                            dm, plan.key_tiles, T, plan.row_blocks * plan.tile_rows, partial, fold, out, gate));
+    return NTX_OK;
+}
 template <int NDB>
 int launch_fwd(const RowMaps& m, const NtxDims& dm, const NtxPlan& plan, float* partial, const NtxFoldScratch& fold,
                const NtxFwdOut& out, const NtxGate& gate, cudaStream_t st) {
-    const size_t smem = fwd_smem_bytes<NDB>();
-    NTX_SMEM_OPT_IN(tc_fwd_kernel<NDB>, smem);
-    const long long T = (long long)plan.row_blocks * plan.key_tiles;
-    NTX_CUDA(ntx_launch_dep(tc_fwd_kernel<NDB>, plan.grid, kFwdThreads, smem, st, m.q[0], m.k[0], m.q[1], m.k[1], dm,
-                            plan.key_tiles, T, plan.row_blocks * plan.tile_rows, partial, fold, out, gate));
-    return NTX_OK;
+    return dm.scaled ? launch_fwd_s<NDB, true>(m, dm, plan, partial, fold, out, gate, st)
+                     : launch_fwd_s<NDB, false>(m, dm, plan, partial, fold, out, gate, st);
 }
 
-template <int NDB, bool kGate>
-int launch_bwd_g(const RowMaps& m, const NtxDims& dm, const NtxPlan& plan, const BwdWeights& wt, float* partial,
-                 const NtxGate& gate, const BwdFuse& fuse, cudaStream_t st) {
+template <int NDB, bool kGate, bool kScaled>
+int launch_bwd_gs(const RowMaps& m, const NtxDims& dm, const NtxPlan& plan, const BwdWeights& wt, float* partial,
+                  const NtxGate& gate, const BwdFuse& fuse, cudaStream_t st) {
     const size_t smem = bwd_smem_bytes<NDB>();
-    NTX_SMEM_OPT_IN((tc_bwd_kernel<NDB, kGate>), smem);
+    NTX_SMEM_OPT_IN((tc_bwd_kernel<NDB, kGate, kScaled>), smem);
     const long long T = (long long)plan.row_blocks * plan.key_tiles;
-    NTX_CUDA(ntx_launch_dep(tc_bwd_kernel<NDB, kGate>, plan.grid, BwdCfg<NDB>::kThreads, smem, st, m.q[0], m.k[0],
+    NTX_CUDA(ntx_launch_dep(tc_bwd_kernel<NDB, kGate, kScaled>, plan.grid, BwdCfg<NDB>::kThreads, smem, st, m.q[0], m.k[0],
                             m.q[1], m.k[1], dm, plan.key_tiles, T, plan.row_blocks * plan.tile_rows, wt, partial, gate,
                             fuse));
     return NTX_OK;
@@ -1438,8 +1451,11 @@ int launch_bwd_g(const RowMaps& m, const NtxDims& dm, const NtxPlan& plan, const
 template <int NDB>
 int launch_bwd(const RowMaps& m, const NtxDims& dm, const NtxPlan& plan, const BwdWeights& wt, float* partial,
                const NtxGate& gate, const BwdFuse& fuse, cudaStream_t st) {
-    return gate.step ? launch_bwd_g<NDB, true>(m, dm, plan, wt, partial, gate, fuse, st)
-                     : launch_bwd_g<NDB, false>(m, dm, plan, wt, partial, gate, fuse, st);
+    if (dm.scaled)
+        return gate.step ? launch_bwd_gs<NDB, true, true>(m, dm, plan, wt, partial, gate, fuse, st)
+                         : launch_bwd_gs<NDB, false, true>(m, dm, plan, wt, partial, gate, fuse, st);
+    return gate.step ? launch_bwd_gs<NDB, true, false>(m, dm, plan, wt, partial, gate, fuse, st)
+                     : launch_bwd_gs<NDB, false, false>(m, dm, plan, wt, partial, gate, fuse, st);
 }
 
 }  // namespace
@@ -1470,29 +1486,33 @@ int ntx_tc_fwd_launch(const __nv_bfloat16* q, const __nv_bfloat16* k, const NtxD
     return NTX_E_UNSUPPORTED;
 }
 
+namespace {
+template <int NDB, bool kScaled>
+int launch_sym(const CUtensorMap& m, const NtxDims& dm, const NtxPlan& plan, float* partial, float* colpart,
+               unsigned int* counter, cudaStream_t st) {
+    const long long T = (long long)plan.row_blocks * (plan.row_blocks + 1) / 2;
+    const int rows_pad = plan.row_blocks * plan.tile_rows;
+    const size_t smem = (size_t)(1 + kSymNS) * NDB * kBlkBytes + kSymWG * 2 * kBlkBytes + 2048 + sizeof(SymCtl);
+    NTX_SMEM_OPT_IN((tc_fwd_sym_kernel<NDB, kScaled>), smem);
+    NTX_CUDA(ntx_launch_dep(tc_fwd_sym_kernel<NDB, kScaled>, plan.fwd_grid, kSymThreads, smem, st, m, dm, plan.row_blocks, T,
+                            rows_pad, partial, colpart, counter));
+    return NTX_OK;
+}
+}  // namespace
+
 int ntx_tc_fwd_sym_launch(const __nv_bfloat16* rows, const NtxDims& dm, const NtxPlan& plan, float* partial,
                           float* colpart, unsigned int* counter, cudaStream_t st) {
     CUtensorMap m;
     int rc = make_rows_tmap(&m, rows, dm.q_rows, dm.ld);
     if (rc) return rc;
-    const long long T = (long long)plan.row_blocks * (plan.row_blocks + 1) / 2;
-    const int rows_pad = plan.row_blocks * plan.tile_rows;
-    if (plan.d_pad == 64) {
-        const size_t smem = (size_t)(1 + kSymNS) * 1 * kBlkBytes + kSymWG * 2 * kBlkBytes + 2048 + sizeof(SymCtl);
-        NTX_SMEM_OPT_IN(tc_fwd_sym_kernel<1>, smem);
-        NTX_CUDA(ntx_launch_dep(tc_fwd_sym_kernel<1>, plan.fwd_grid, kSymThreads, smem, st, m, dm, plan.row_blocks, T,
-                                rows_pad, partial, colpart, counter));
-    } else if (plan.d_pad == 128) {
-        const size_t smem = (size_t)(1 + kSymNS) * 2 * kBlkBytes + kSymWG * 2 * kBlkBytes + 2048 + sizeof(SymCtl);
-        NTX_SMEM_OPT_IN(tc_fwd_sym_kernel<2>, smem);
-        NTX_CUDA(ntx_launch_dep(tc_fwd_sym_kernel<2>, plan.fwd_grid, kSymThreads, smem, st, m, dm, plan.row_blocks, T,
-                                rows_pad, partial, colpart, counter));
-    } else {
-        ntx_set_error("symmetric forward: padded feature dim %d not built", plan.d_pad);
-        return NTX_E_UNSUPPORTED;
-    }
-    NTX_CUDA(cudaGetLastError());
-    return NTX_OK;
+    if (plan.d_pad == 64)
+        return dm.scaled ? launch_sym<1, true>(m, dm, plan, partial, colpart, counter, st)
+                         : launch_sym<1, false>(m, dm, plan, partial, colpart, counter, st);
+    if (plan.d_pad == 128)
+        return dm.scaled ? launch_sym<2, true>(m, dm, plan, partial, colpart, counter, st)
+                         : launch_sym<2, false>(m, dm, plan, partial, colpart, counter, st);
+    ntx_set_error("symmetric forward: padded feature dim %d not built", plan.d_pad);
+    return NTX_E_UNSUPPORTED;
 }
 
 int ntx_tc_bwd_launch(const __nv_bfloat16* q, const __nv_bfloat16* k, const NtxDims& dm,
@@ -1501,7 +1521,7 @@ int ntx_tc_bwd_launch(const __nv_bfloat16* q, const __nv_bfloat16* k, const NtxD
     RowMaps m;
     int rc = make_row_maps(&m, q, k, dm, gate, key_buf_elems);
     if (rc) return rc;
-    BwdWeights wt{w.rowsum_q, w.rowsum_k, w.w_q, w.w_k, w.w_stride, w.w_scale, w.w_chunk, w.w_bf16};
+    BwdWeights wt{w.rowsum_q, w.rowsum_k, w.w_q, w.w_k, w.w_stride, w.w_scale, w.w_chunk, w.w_bf16, w.coef_scale};
     const BwdFuse fuse{o.view0, o.view1, o.dview0, o.dview1, o.inv_norm, o.tag, o.done_total, o.arrive, o.row_blocks,
                        o.in_ld, o.normalised, o.in_bf16, dm.d, o.enabled};
     switch (plan.d_pad) {

@@ -82,45 +82,44 @@ class NTXentFunction(torch.autograd.Function):
         q_rows = 2 * n
         ld, ws_bytes = _shape_info(be, q_rows, world * q_rows, d, rows_dtype, dev)
         stats = torch.empty((4, q_rows), dtype=torch.float32, device=dev)   # inv_norm, rowsum, pos, row loss
-        loss_sum = torch.empty(2, dtype=torch.float32, device=dev)
+        loss_sum = torch.empty(2, dtype=view0.dtype, device=dev)            # [sum, mean] in the dtype the loss is returned in
         inv_norm, rowsum, pos_logit, row_loss = stats[0], stats[1], stats[2], stats[3]
         exchange = None
         ws = _workspace(dev, ws_bytes)
+        # bf16 rows are stored times sqrt(log2 e / temperature): a similarity then is its logit's exponent and the
+        # tensor-core epilogues skip one packed FMA per pair of logits (1 for fp32 rows)
+        rs = be.row_scale(temperature, rows_dtype)
         if world > 1 and peer:
             # kernels store rows, row sums and weights straight into every rank's exchange block (NVLink peer
             # memory) and order them with flag words: no collective call, no barrier kernel
             exchange = peer_exchange.exchange_for(be, group, q_rows, ld, rows_dtype, dev)
             exchange.begin_forward(any(ctx.needs_input_grad[:2]))
             keys = torch.empty(1, dtype=torch.int32, device=dev)           # the step number, set on the device
-            be.peer_l2norm(view0, view1, exchange.blocks, ld, rows_dtype, inv_norm, keys)
+            be.peer_l2norm(view0, view1, exchange.blocks, ld, rows_dtype, inv_norm, keys, row_scale=rs)
             be.peer_fwd(exchange.blocks, n, d, ld, rows_dtype, temperature, keys, rowsum, pos_logit, row_loss,
-                        loss_sum, ws)
+                        loss_sum, ws, row_scale=rs)
         else:
             rows = torch.empty((q_rows, ld), dtype=rows_dtype, device=dev)
-            be.l2norm(view0, view1, rows, inv_norm)
+            be.l2norm(view0, view1, rows, inv_norm, row_scale=rs)
             if world > 1:
                 keys = torch.empty((world * q_rows, ld), dtype=rows_dtype, device=dev)
                 dist.all_gather_into_tensor(keys, rows, group=group)      # rank-major key buffer
                 q = keys[rank * q_rows:(rank + 1) * q_rows]
             else:
                 keys = q = rows
-            be.fwd(q, keys, d, (n, world, rank), temperature, rowsum, pos_logit, row_loss, loss_sum, ws)
+            be.fwd(q, keys, d, (n, world, rank, rs), temperature, rowsum, pos_logit, row_loss, loss_sum, ws)
 
         ctx.save_for_backward(view0, view1, keys, stats)
-        ctx.meta = (temperature, reduction, group, world, rank, d, exchange, rows_dtype, cat)
+        ctx.meta = (temperature, reduction, group, world, rank, d, exchange, rows_dtype, cat, rs)
         if reduction == "none":
-            out = row_loss.view(2, n).clone()                              # loss.py:55-58
-        elif reduction == "sum":
-            out = loss_sum[0]                                              # loss.py:60-63
-        else:
-            out = loss_sum[1]                                              # loss.py:65
-        return out.to(view0.dtype)
+            return row_loss.view(2, n).to(view0.dtype, copy=True)          # loss.py:55-58
+        return loss_sum[0] if reduction == "sum" else loss_sum[1]          # loss.py:60-65
 
     @staticmethod
     def backward(ctx, grad_out):
         be = _backend
         view0, view1, keys, stats = ctx.saved_tensors
-        temperature, reduction, group, world, rank, d, exchange, rows_dtype, cat = ctx.meta
+        temperature, reduction, group, world, rank, d, exchange, rows_dtype, cat, rs = ctx.meta
         n = view0.shape[0]
         q_rows = 2 * n
         dev = view0.device
@@ -146,7 +145,7 @@ class NTXentFunction(torch.autograd.Function):
             # every key's row sum and weight from its own exchange block
             be.peer_post_weights(exchange.blocks, n, ld, rows_dtype, keys, w_q, w_stride)
             be.peer_bwd(exchange.blocks, n, d, ld, rows_dtype, temperature, keys, rowsum, w_stride, w_scale, view0,
-                        view1, inv_norm, dview0, dview1, ws)
+                        view1, inv_norm, dview0, dview1, ws, row_scale=rs)
             exchange.end_backward()
             return grads + (None,) * 8
         if world > 1:
@@ -161,7 +160,7 @@ class NTXentFunction(torch.autograd.Function):
             q = keys[rank * q_rows:(rank + 1) * q_rows]
         else:
             rowsum_k, w_k, q = rowsum, w_q, keys
-        be.bwd(q, keys, d, (n, world, rank), temperature, rowsum, rowsum_k, w_q, w_k, w_stride, w_scale,
+        be.bwd(q, keys, d, (n, world, rank, rs), temperature, rowsum, rowsum_k, w_q, w_k, w_stride, w_scale,
                view0, view1, inv_norm, dview0, dview1, ws)
         return grads + (None,) * 8
 
@@ -185,25 +184,22 @@ class NTXentHiddenFunction(torch.autograd.Function):
         ld, ws_bytes = _shape_info(be, q_rows, q_rows, d, torch.bfloat16, dev)
         rows = torch.empty((q_rows, ld), dtype=torch.bfloat16, device=dev)
         stats = torch.empty((4, q_rows), dtype=torch.float32, device=dev)   # inv_norm, rowsum, pos, row loss
-        loss_sum = torch.empty(2, dtype=torch.float32, device=dev)
-        be.project_l2norm(h0, h1, weight, rows, stats[0])
-        be.fwd(rows, rows, d, (n, 1, 0), temperature, stats[1], stats[2], stats[3], loss_sum,
+        loss_sum = torch.empty(2, dtype=h0.dtype, device=dev)
+        rs = be.row_scale(temperature, torch.bfloat16)
+        be.project_l2norm(h0, h1, weight, rows, stats[0], row_scale=rs)
+        be.fwd(rows, rows, d, (n, 1, 0, rs), temperature, stats[1], stats[2], stats[3], loss_sum,
                _workspace(dev, ws_bytes))
         ctx.save_for_backward(h0, h1, weight, rows, stats)
-        ctx.meta = (temperature, reduction, d, ws_bytes, cat)
+        ctx.meta = (temperature, reduction, d, ws_bytes, cat, rs)
         if reduction == "none":
-            out = stats[3].view(2, n).clone()
-        elif reduction == "sum":
-            out = loss_sum[0]
-        else:
-            out = loss_sum[1]
-        return out.to(h0.dtype)
+            return stats[3].view(2, n).to(h0.dtype, copy=True)
+        return loss_sum[0] if reduction == "sum" else loss_sum[1]
 
     @staticmethod
     def backward(ctx, grad_out):
         be = _backend
         h0, h1, weight, rows, stats = ctx.saved_tensors
-        temperature, reduction, d, ws_bytes, cat = ctx.meta
+        temperature, reduction, d, ws_bytes, cat, rs = ctx.meta
         n = h0.shape[0]
         q_rows = 2 * n
         g = grad_out.detach().contiguous().view(-1)
@@ -212,7 +208,7 @@ class NTXentHiddenFunction(torch.autograd.Function):
         w_stride = 1 if reduction == "none" else 0
         w_scale = 1.0 / q_rows if reduction == "mean" else 1.0
         dz = torch.empty((q_rows, d), dtype=torch.bfloat16, device=h0.device)
-        be.bwd_rows(rows, rows, d, (n, 1, 0), temperature, stats[1], stats[1], g, g, w_stride, w_scale, stats[0],
+        be.bwd_rows(rows, rows, d, (n, 1, 0, rs), temperature, stats[1], stats[1], g, g, w_stride, w_scale, stats[0],
                     dz, _workspace(h0.device, ws_bytes))
         hdim = h0.shape[1]
         dh = torch.empty((q_rows, hdim), dtype=torch.bfloat16, device=h0.device)

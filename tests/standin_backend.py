@@ -20,7 +20,11 @@ class StandInBackend:
     def plan(self, q_rows, k_rows, d, dtype, sm_count=0):
         return types.SimpleNamespace(fwd_ws_bytes=16, bwd_ws_bytes=16)
 
-    def l2norm(self, view0, view1, rows, inv_norm):
+    def row_scale(self, temperature, dtype):
+        return 1.0              # unit rows: the scale only matters to the tensor-core kernels
+
+    def l2norm(self, view0, view1, rows, inv_norm, row_scale=1.0):
+        assert row_scale == 1.0
         z = torch.cat([view0, view1]).double()
         denom = z.norm(dim=1).clamp_min(1e-12)
         rows.zero_()
@@ -29,7 +33,7 @@ class StandInBackend:
 
     @staticmethod
     def _cols(layout, q_rows):
-        n, world, rank = layout
+        n, world, rank = layout[:3]
         r = torch.arange(q_rows)
         off = rank * q_rows
         return off + r, off + (r + n) % q_rows

@@ -103,16 +103,16 @@ def test_newer_entry_points_validate_before_touching_the_device():
     assert be.peer_block_bytes(2048, 128, torch.bfloat16, 8) >= 256 + 2 * 8 * 2048 * 4 + 2 * 8 * 2048 * 128 * 2
     assert be.peer_block_bytes(2048, 128, torch.bfloat16, 9) == 0
     bad_rank = be.peer_blocks([4096, 8192], 2)
-    assert lib.ntx_peer_l2norm(4096, 4096, 4, 8, 0, ctypes.byref(bad_rank), 8, 0, 4096, 4096, None) == -1
+    assert lib.ntx_peer_l2norm(4096, 4096, 4, 8, 0, ctypes.byref(bad_rank), 8, 0, 4096, 1.0, 4096, None) == -1
     assert b"rank=2" in lib.ntx_last_error()
     holed = be.peer_blocks([4096, 0], 0)
-    assert lib.ntx_peer_fwd(ctypes.byref(holed), 4, 8, 8, 0, 0.5, 4096, 4096, 4096, 4096, 4096, 4096, 1 << 20, None) == -1
+    assert lib.ntx_peer_fwd(ctypes.byref(holed), 4, 8, 8, 0, 0.5, 1.0, 0, 4096, 4096, 4096, 4096, 4096, 4096, 1 << 20, None) == -1
     assert b"rank 1" in lib.ntx_last_error()
     skew = be.peer_blocks([4096, 8192 + 16], 0)
-    assert lib.ntx_peer_fwd(ctypes.byref(skew), 4, 8, 8, 0, 0.5, 4096, 4096, 4096, 4096, 4096, 4096, 1 << 20, None) == -1
+    assert lib.ntx_peer_fwd(ctypes.byref(skew), 4, 8, 8, 0, 0.5, 1.0, 0, 4096, 4096, 4096, 4096, 4096, 4096, 1 << 20, None) == -1
     assert b"aligned" in lib.ntx_last_error()
     good = be.peer_blocks([4096, 8192], 0)
-    assert lib.ntx_peer_fwd(ctypes.byref(good), 4, 8, 8, 0, 0.5, None, 4096, 4096, 4096, 4096, 4096, 1 << 20, None) == -1
+    assert lib.ntx_peer_fwd(ctypes.byref(good), 4, 8, 8, 0, 0.5, 1.0, 0, None, 4096, 4096, 4096, 4096, 4096, 1 << 20, None) == -1
     assert b"step" in lib.ntx_last_error()
     assert lib.ntx_peer_post_weights(ctypes.byref(good), 4, 8, 0, 4096, 4096, 2, 0, None) == -1
     assert b"w_stride" in lib.ntx_last_error()
@@ -122,14 +122,31 @@ def test_newer_entry_points_validate_before_touching_the_device():
     assert lib.ntx_simclr_augment(4096, 4, 32, 32, 0.0, 0, 0, 32, 4096, 4096, None, None) == -1
     assert lib.ntx_simclr_augment(4096, 4, 32, 32, 0.5, 0, 0, 100, 4096, 4096, None, None) == -1
     # projection: hidden size in whole TMA blocks, row pitch of bf16 rows, d <= 256
-    assert lib.ntx_project_l2norm(4096, 4096, 4096, 4, 100, 64, 4096, 64, 4096, None) == -1
+    assert lib.ntx_project_l2norm(4096, 4096, 4096, 4, 100, 64, 4096, 64, 4096, 1.0, None) == -1
     assert b"multiple of 64" in lib.ntx_last_error()
-    assert lib.ntx_project_l2norm(4096, 4096, 4096, 4, 128, 96, 4096, 96, 4096, None) == -1
+    assert lib.ntx_project_l2norm(4096, 4096, 4096, 4, 128, 96, 4096, 96, 4096, 1.0, None) == -1
     assert b"ntx_row_pitch" in lib.ntx_last_error()
-    assert lib.ntx_project_l2norm(4096, 4096, 4096, 4, 128, 300, 4096, 320, 4096, None) == -1
-    assert lib.ntx_project_l2norm(4096, None, 4096, 4, 128, 64, 4096, 64, 4096, None) == -1
+    assert lib.ntx_project_l2norm(4096, 4096, 4096, 4, 128, 300, 4096, 320, 4096, 1.0, None) == -1
+    assert lib.ntx_project_l2norm(4096, None, 4096, 4, 128, 64, 4096, 64, 4096, 1.0, None) == -1
     # rows-backward: output required (odd sizes go to the unaligned finalize: no size restriction)
     lay = _cabi.NtxLayout(4, 1, 0)
     rc = lib.ntx_bwd_rows(4096, 4096, 8, 8, 8, 64, 1, ctypes.byref(lay), 0.5, 4096, 4096, 4096, 4096, 0, 0, 1.0, 4096,
                           None, 4096, 64, None)
     assert rc == -1 and b"NULL" in lib.ntx_last_error()
+
+
+def test_row_scale_is_accepted_only_as_handed_out():
+    """bf16 rows may carry ntx_row_scale(temperature); any other factor, or a factor on fp32 rows, is an argument
+    error (the kernels would silently compute another loss)."""
+    import math
+    lib = _cabi.load()
+    be = _cabi.Backend()
+    assert be.row_scale(0.5, torch.float32) == 1.0
+    assert abs(be.row_scale(0.5, torch.bfloat16) - math.sqrt(math.log2(math.e) / 0.5)) < 1e-6
+    assert be.row_scale(0.01, torch.bfloat16) == 1.0                 # below the tensor-core kernels' temperature range
+    lay = _cabi.NtxLayout(4, 1, 0, 1.5)
+    rc = lib.ntx_fwd(4096, 4096, 8, 8, 8, 64, 1, ctypes.byref(lay), 0.5, 4096, 4096, 4096, 4096, 4096, 1 << 20, None)
+    assert rc == -1 and b"row_scale" in lib.ntx_last_error()
+    lay = _cabi.NtxLayout(4, 1, 0, be.row_scale(0.5, torch.bfloat16))
+    rc = lib.ntx_fwd(4096, 4096, 8, 8, 8, 8, 0, ctypes.byref(lay), 0.5, 4096, 4096, 4096, 4096, 4096, 1 << 20, None)
+    assert rc == -1 and b"row_scale" in lib.ntx_last_error()          # fp32 rows

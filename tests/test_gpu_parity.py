@@ -638,7 +638,10 @@ def test_reference_model_training_steps(dev):
     sys.path.insert(0, os.path.join(root, "tools"))
     import resnet_step
     out = resnet_step.run(steps=3, batch=512)
-    assert out["max_rel_loss_diff"] < 1e-5, out["losses_ours_vs_reference"]
+    first = out["losses_ours_vs_reference"][0]
+    assert abs(first[0] - first[1]) < 1e-5 * abs(first[1]), out["losses_ours_vs_reference"]      # identical weights
+    # later steps: the two models have been updated with gradients that differ in the last fp32 bits
+    assert out["max_rel_loss_diff"] < 2e-4, out["losses_ours_vs_reference"]
     assert all(np.isfinite(a) for a, _ in out["losses_ours_vs_reference"])
 
 
@@ -790,3 +793,57 @@ def test_small_temperature_sharded_one_gpu(dev):
         scale = np.abs(ref["dview0"]).max()
         assert np.abs(d0.cpu().numpy() - ref["dview0"][sl]).max() / scale < FP32_TOL
         assert np.abs(d1.cpu().numpy() - ref["dview1"][sl]).max() / scale < FP32_TOL
+
+
+@pytest.mark.parametrize("n,d,world,tau", [(700, 128, 1, 0.5), (300, 64, 1, 0.1), (512, 128, 4, 0.5), (260, 256, 1, 0.2)])
+def test_scaled_rows_match_unit_rows(n, d, world, tau, dev):
+    """bf16 rows stored times ntx_row_scale(tau) (what the module does: the similarity MMA then yields the exponent
+    and the epilogues skip the per-logit scaling) against unit rows through the same entry points: row sums,
+    positive logits, losses and gradients agree to bf16 rounding, and both match the oracle.  Shapes: symmetric
+    forward, D = 64, one of four ranks (full-tile forward against all keys), D = 256."""
+    from simclr_b200 import _cabi
+    be = _cabi.Backend()
+    g = torch.Generator().manual_seed(n + d)
+    v0, v1 = torch.randn(n, d, generator=g).bfloat16(), torch.randn(n, d, generator=g).bfloat16()
+    ref = orc.ntxent_rows_fp64(v0.float().numpy(), v1.float().numpy(), tau, weights=orc.weights_for("mean", n))
+    nl = n // world
+    q_rows = 2 * nl
+    ld = be.row_pitch(d, torch.bfloat16)
+    plan = be.plan(q_rows, world * q_rows, d, torch.bfloat16)
+    ws = torch.empty(max(plan.fwd_ws_bytes, plan.bwd_ws_bytes), dtype=torch.uint8, device=dev)
+    one = torch.ones(1, device=dev)
+    res = {}
+    for rs in (1.0, be.row_scale(tau, torch.bfloat16)):
+        assert rs == 1.0 or abs(rs * rs - math.log2(math.e) / tau) < 1e-4
+        keys = torch.empty(world * q_rows, ld, dtype=torch.bfloat16, device=dev)
+        inv = torch.empty(world, q_rows, device=dev)
+        views = []
+        for k in range(world):
+            a, b = v0[k * nl:(k + 1) * nl].to(dev), v1[k * nl:(k + 1) * nl].to(dev)
+            views.append((a, b))
+            be.l2norm(a, b, keys[k * q_rows:(k + 1) * q_rows], inv[k], row_scale=rs)
+        st = torch.empty(world, 3, q_rows, device=dev)
+        ls = torch.empty(world, 2, device=dev)
+        for k in range(world):
+            be.fwd(keys[k * q_rows:(k + 1) * q_rows], keys, d, (nl, world, k, rs), tau, st[k, 0], st[k, 1], st[k, 2], ls[k], ws)
+        rowsum_k = st[:, 0, :].reshape(-1).contiguous()
+        grads = []
+        for k in range(world):
+            a, b = views[k]
+            d0, d1 = torch.empty_like(a), torch.empty_like(b)
+            be.bwd(keys[k * q_rows:(k + 1) * q_rows], keys, d, (nl, world, k, rs), tau, st[k, 0], rowsum_k, one, one, 0,
+                   0.5 / n, a, b, inv[k], d0, d1, ws)
+            grads.append((d0.float().cpu().numpy(), d1.float().cpu().numpy()))
+        res[rs == 1.0] = (st.cpu().numpy(), ls.cpu().numpy(), grads)
+    (st_u, ls_u, g_u), (st_s, ls_s, g_s) = res[True], res[False]
+    assert rel_err(st_s[:, 0], st_u[:, 0]) < 6e-3 and rel_err(st_s[:, 1], st_u[:, 1]) < 6e-3       # row sums, positives
+    assert rel_err(st_s[:, 2], st_u[:, 2]) < 6e-3
+    loss_rows = np.concatenate([st_s[k, 2].reshape(2, nl) for k in range(world)], axis=1)
+    assert rel_err(loss_rows, ref["loss"]) < BF16_TOL
+    assert abs(ls_s[:, 1].mean() - ref["loss"].mean()) < BF16_TOL * ref["loss"].mean()
+    scale = max(np.abs(ref["dview0"]).max(), np.abs(ref["dview1"]).max())
+    for k in range(world):
+        sl = slice(k * nl, (k + 1) * nl)
+        assert np.abs(g_s[k][0] - ref["dview0"][sl]).max() / scale < BF16_TOL
+        assert np.abs(g_s[k][1] - ref["dview1"][sl]).max() / scale < BF16_TOL
+        assert np.abs(g_s[k][0] - g_u[k][0]).max() / scale < BF16_TOL

@@ -35,6 +35,7 @@ plan = be.plan(ql, q_rows, d, torch.bfloat16)
 ws = torch.empty(max(plan.fwd_ws_bytes, plan.bwd_ws_bytes), dtype=torch.uint8, device=dev)
 g0, g1 = torch.empty_like(v0), torch.empty_like(v1)
 one = torch.ones(1, device=dev)
+rs = be.row_scale(0.5, torch.bfloat16) if os.environ.get("NTX_UNIT_ROWS") is None else 1.0
 rsk = torch.full((q_rows,), 5000.0, device=dev)          # stand-in row sums of every key (world > 1 timing only)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 tf, tb, tt = [], [], []
@@ -44,17 +45,17 @@ for it in range(iters + 5):
         e.record()
     flush.zero_()
     ev[4].record()
-    be.l2norm(v0, v1, rows, stats[0])
+    be.l2norm(v0, v1, rows, stats[0], row_scale=rs)
     be.profile_next(0, ev[0], ev[1])
     if world == 1:
-        be.fwd(rows, rows, d, (n, 1, 0), 0.5, stats[1], stats[2], stats[3], loss_sum, ws)
+        be.fwd(rows, rows, d, (n, 1, 0, rs), 0.5, stats[1], stats[2], stats[3], loss_sum, ws)
         be.profile_next(1, ev[2], ev[3])
-        be.bwd(rows, rows, d, (n, 1, 0), 0.5, stats[1], stats[1], one, one, 0, 1.0 / q_rows, v0, v1, stats[0], g0, g1, ws)
+        be.bwd(rows, rows, d, (n, 1, 0, rs), 0.5, stats[1], stats[1], one, one, 0, 1.0 / q_rows, v0, v1, stats[0], g0, g1, ws)
     else:
         # rows laid out rank-major would interleave the views; for timing the first ql rows stand in for rank 0's
-        be.fwd(rows[:ql], rows, d, (nl, world, 0), 0.5, stats[1][:ql], stats[2][:ql], stats[3][:ql], loss_sum, ws)
+        be.fwd(rows[:ql], rows, d, (nl, world, 0, rs), 0.5, stats[1][:ql], stats[2][:ql], stats[3][:ql], loss_sum, ws)
         be.profile_next(1, ev[2], ev[3])
-        be.bwd(rows[:ql], rows, d, (nl, world, 0), 0.5, stats[1][:ql], rsk, one, one, 0, 1.0 / q_rows, v0[:nl], v1[:nl],
+        be.bwd(rows[:ql], rows, d, (nl, world, 0, rs), 0.5, stats[1][:ql], rsk, one, one, 0, 1.0 / q_rows, v0[:nl], v1[:nl],
                stats[0][:ql], g0[:nl], g1[:nl], ws)
     ev[5].record()
     torch.cuda.synchronize()

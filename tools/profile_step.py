@@ -33,25 +33,26 @@ loss_sum = torch.empty(2, device=dev)
 plan = be.plan(q_rows, world * q_rows, d, torch.bfloat16)
 ws = torch.empty(max(plan.fwd_ws_bytes, plan.bwd_ws_bytes), dtype=torch.uint8, device=dev)
 one = torch.ones(1, device=dev)
+rs = be.row_scale(0.5, torch.bfloat16)              # the module's bf16 rows carry sqrt(log2 e / tau)
 views = [(v0[k * nl:(k + 1) * nl], v1[k * nl:(k + 1) * nl]) for k in range(world)]
 g0, g1 = torch.empty_like(views[0][0]), torch.empty_like(views[0][1])
 
 
 def forward(k):
     q = keys[k * q_rows:(k + 1) * q_rows]
-    be.l2norm(views[k][0], views[k][1], q, stats[k, 0])
-    be.fwd(q, keys, d, (nl, world, k), 0.5, stats[k, 1], stats[k, 2], stats[k, 3], loss_sum, ws)
+    be.l2norm(views[k][0], views[k][1], q, stats[k, 0], row_scale=rs)
+    be.fwd(q, keys, d, (nl, world, k, rs), 0.5, stats[k, 1], stats[k, 2], stats[k, 3], loss_sum, ws)
 
 
 for k in range(world - 1, 0, -1):                 # every rank's rows first, then their forward passes
-    be.l2norm(views[k][0], views[k][1], keys[k * q_rows:(k + 1) * q_rows], stats[k, 0])
-be.l2norm(views[0][0], views[0][1], keys[:q_rows], stats[0, 0])
+    be.l2norm(views[k][0], views[k][1], keys[k * q_rows:(k + 1) * q_rows], stats[k, 0], row_scale=rs)
+be.l2norm(views[0][0], views[0][1], keys[:q_rows], stats[0, 0], row_scale=rs)
 for k in range(world - 1, 0, -1):
     forward(k)
 for _ in range(steps):
     forward(0)
     rowsum_k = stats[:, 1, :].reshape(-1).contiguous() if world > 1 else stats[0, 1]
-    be.bwd(keys[:q_rows], keys, d, (nl, world, 0), 0.5, stats[0, 1], rowsum_k, one, one, 0, 1.0 / q_rows,
+    be.bwd(keys[:q_rows], keys, d, (nl, world, 0, rs), 0.5, stats[0, 1], rowsum_k, one, one, 0, 1.0 / q_rows,
            views[0][0], views[0][1], stats[0, 0], g0, g1, ws)
 torch.cuda.synchronize()
 print("loss", float(loss_sum[1]))
