@@ -44,6 +44,8 @@ def _workspace(device: torch.device, nbytes: int) -> torch.Tensor:
     key = (device, _cabi.current_stream_handle(device) if device.type == "cuda" else 0)
     buf = _workspaces.get(key)
     if buf is None or buf.numel() < nbytes:
+        if len(_workspaces) >= 16:          # streams come and go (their handles are reused): do not grow without bound
+            _workspaces.clear()
         buf = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
         _workspaces[key] = buf
     return buf
