@@ -14,8 +14,11 @@
 
 namespace {
 
-constexpr int kThreads = 512;        // backward finalize / generic kernels
-constexpr int kFwdThreads = 1024;    // forward finalize: few blocks -> few serialized tickets (256 when that leaves SMs idle)
+// block sizes measured on B200 at the benchmark size (one box, alternating runs): backward finalize 512 -> 256
+// threads -0.9 us per step, forward finalize 1024 -> 256 -0.3 us (more, smaller blocks hide the load latency better;
+// the forward's arrival word takes any number of blocks)
+constexpr int kThreads = 256;        // backward finalize / generic kernels
+constexpr int kFwdThreads = 256;     // forward finalize
 
 __device__ __forceinline__ float ldf(const float* p, size_t i) { return __ldg(p + i); }
 __device__ __forceinline__ float ldf(const __nv_bfloat16* p, size_t i) { return __bfloat162float(p[i]); }
@@ -70,7 +73,7 @@ fwd_finalize_kernel(const T* __restrict__ q, NtxDims dm, int lanes, int tile_row
     }
     __syncthreads();
     double my_loss = 0.0;
-    const int nthreads = (int)blockDim.x;                    // kFwdThreads or 256
+    const int nthreads = (int)blockDim.x;                    // kFwdThreads
     const int rows_per_block = nthreads / lanes;
     // The positive logit's operands first: their loads are in flight while the partial sums below are gathered
     // (these kernels are chains of dependent memory round trips; every one that overlaps another is ~0.5 us).
@@ -320,6 +323,7 @@ __global__ void debug_indices_kernel(int n_local, int rank, int32_t* __restrict_
 // (16 or more, so that the rows of one block, <= 1024 / 16, never straddle a 64-row tile: one slot count per block)
 // threads per row: 16 up to 256 features (64 four-element groups), so that a block covers enough rows for the
 // whole grid to be resident at once (these kernels are latency-bound: one wave, not two), 32 beyond
+// (8 and 32 lanes at 128 features measured on one box: +4.6 / +5 us per step)
 int lanes_for(int groups4) { return groups4 <= 64 ? 16 : 32; }
 
 template <typename TIn>
@@ -364,12 +368,7 @@ int ntx_debug_indices_launch(int n_local, int rank, int32_t* self_col, int32_t* 
     return NTX_OK;
 }
 
-// threads per block of the forward finalize: kFwdThreads, or 256 when that would leave most SMs without a block
-// (one of several ranks: 2048 rows are 32 blocks of 1024 threads)
-static int fwd_finalize_threads(int q_rows, int lanes) {
-    const int blocks = (q_rows + kFwdThreads / lanes - 1) / (kFwdThreads / lanes);
-    return blocks < 148 ? 256 : kFwdThreads;
-}
+static int fwd_finalize_threads(int, int) { return kFwdThreads; }
 
 int ntx_fwd_finalize_blocks(int q_rows, int ld) {
     const int lanes = lanes_for(ld / 4);

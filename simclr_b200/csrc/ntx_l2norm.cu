@@ -9,7 +9,7 @@
 
 namespace {
 
-constexpr int kWarpsPerBlock = 8;
+constexpr int kWarpsPerBlock = 8;      // (4 and 16 measured: +0.2 / +0.5 us per step)
 
 template <typename T> struct Vec;   // 16-byte vector of T
 template <> struct Vec<float> {
