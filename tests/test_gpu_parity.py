@@ -847,3 +847,27 @@ def test_scaled_rows_match_unit_rows(n, d, world, tau, dev):
         assert np.abs(g_s[k][0] - ref["dview0"][sl]).max() / scale < BF16_TOL
         assert np.abs(g_s[k][1] - ref["dview1"][sl]).max() / scale < BF16_TOL
         assert np.abs(g_s[k][0] - g_u[k][0]).max() / scale < BF16_TOL
+
+
+def test_integration_md_ctypes_stub_runs(dev):
+    """The ctypes binding printed in INTEGRATION.md section 2 is executed as written (only the library path is made
+    absolute) and its nt_xent_mean must match the oracle: the document cannot drift from include/ntxent_b200.h."""
+    import os
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    text = open(os.path.join(root, "INTEGRATION.md")).read()
+    block = re.search(r"```python\nimport ctypes, torch\n(.*?)```", text, re.S)
+    assert block, "INTEGRATION.md lost its ctypes example"
+    code = "import ctypes, torch\n" + block.group(1)
+    code = code.replace('"simclr_b200/libntxent_b200.so"', repr(os.path.join(root, "simclr_b200", "libntxent_b200.so")))
+    ns = {}
+    exec(compile(code, "INTEGRATION.md", "exec"), ns)
+    ns["lib"].ntx_last_error.restype = __import__("ctypes").c_char_p
+    g = torch.Generator().manual_seed(5)
+    a, b = torch.randn(300, 40, generator=g), torch.randn(300, 40, generator=g)
+    with torch.cuda.device(dev):
+        loss, keep = ns["nt_xent_mean"](a.to(dev), b.to(dev), 0.5)
+        torch.cuda.synchronize()
+    ref = orc.ntxent_rows_fp64(a.numpy(), b.numpy(), 0.5)
+    assert rel_err(loss.cpu().numpy(), orc.reduce_rows(ref["loss"], "mean")) < FP32_TOL
+    del keep
