@@ -38,6 +38,16 @@ extern "C" {
 /* element types of caller buffers */
 #define NTX_F32 0
 #define NTX_BF16 1
+/* Normalised ROWS only (rows_dtype of ntx_l2norm, dtype of ntx_plan / ntx_fwd / ntx_bwd): fp32 rows held as two bf16
+ * terms, x = hi + lo with hi = bf16(x), lo = bf16(x - hi) (x to 2^-17 relative).  A row is [hi (pitch/2) | lo
+ * (pitch/2)] bf16 values, pitch = ntx_row_pitch(d, NTX_BF16X2) = 2 * (d rounded up to 64); d <= 128.  The tcgen05
+ * kernels then form q.k = hi.lo + lo.hi + hi.hi with fp32 accumulation and split the backward's coefficient
+ * tile the same way (C_hi.K_hi + C_hi.K_lo + C_lo.K_hi): fp32-grade results at tensor-core speed for callers whose
+ * fp32 batches are large enough for the CUDA-core kernels to matter.  Error against the fp64 oracle, relative to
+ * the largest gradient entry: 2e-7 at temperature 0.5, 1e-6 at 0.1, 1e-5 at 0.05 (it grows like 1/temperature; the
+ * module uses this layout from temperature 0.1 upwards and the NTX_F32 kernels below).
+ * One rank or an all-gathered key buffer; the peer-exchange entry points take NTX_F32 / NTX_BF16 rows only. */
+#define NTX_BF16X2 2
 
 /* error codes */
 #define NTX_OK 0
@@ -80,8 +90,9 @@ typedef struct NtxPlan {
     int32_t key_tiles;     /* ceil(k_rows / tile_keys) */
     int32_t grid;          /* CTAs of the main kernel; CTA i owns tiles [i*T/grid, (i+1)*T/grid) */
     int32_t max_slots;     /* most CTAs that share one row block (partials per row) */
-    int32_t d_pad;         /* feature dim padded to the kernel's granule */
-    int32_t tensor_cores;  /* 1 = tcgen05 path (bf16 rows), 0 = fp32 CUDA-core path */
+    int32_t d_pad;         /* feature dim padded to the kernel's granule (NTX_BF16X2: of one term, half the row pitch) */
+    int32_t tensor_cores;  /* 1 = tcgen05 path (bf16 rows), 2 = tcgen05 path on two-term rows (NTX_BF16X2),
+                            * 0 = fp32 CUDA-core path */
     uint64_t fwd_ws_bytes; /* scratch ntx_fwd wants (enables the symmetric forward when it applies) */
     uint64_t bwd_ws_bytes; /* scratch ntx_bwd needs */
     uint64_t fwd_ws_bytes_min; /* least scratch ntx_fwd accepts (full-tile forward) */
@@ -98,11 +109,12 @@ const char* ntx_last_error(void);
 long long ntx_launch_count(void);
 
 /* The factor NT_Xent's module stores into bf16 rows (see NtxLayout.row_scale): sqrt(log2(e) / temperature) for
- * NTX_BF16 rows at temperature >= NTX_MIN_TEMPERATURE, 1 otherwise. */
+ * NTX_BF16 / NTX_BF16X2 rows at temperature >= NTX_MIN_TEMPERATURE, 1 otherwise. */
 float ntx_row_scale(float temperature, int dtype);
 
 /* Leading dimension (elements per row) the library wants for normalised rows of
- * feature size d in dtype NTX_F32 / NTX_BF16: d rounded up to 4 (fp32) or 64 (bf16). */
+ * feature size d in dtype NTX_F32 / NTX_BF16 / NTX_BF16X2: d rounded up to 4 (fp32) or 64 (bf16), twice that for
+ * two-term rows (bf16 elements). */
 int ntx_row_pitch(int d, int dtype);
 
 /* Integer planning shared by ntx_fwd/ntx_bwd and their finalize kernels.

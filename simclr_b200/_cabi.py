@@ -14,8 +14,29 @@ import torch
 _PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("NTXENT_B200_LIB") or os.path.join(_PKG, "libntxent_b200.so")
 
-NTX_F32, NTX_BF16 = 0, 1
-DTYPES = {torch.float32: NTX_F32, torch.bfloat16: NTX_BF16}
+NTX_F32, NTX_BF16, NTX_BF16X2 = 0, 1, 2
+
+
+class _RowsKind:
+    """A rows layout that is not a torch dtype: stands where a ``rows_dtype`` is expected."""
+
+    def __init__(self, name: str, storage: torch.dtype):
+        self.name, self.storage = name, storage
+
+    def __repr__(self):
+        return f"rows:{self.name}"
+
+
+# fp32 rows held as two bf16 terms [hi | lo] (NTX_BF16X2 of include/ntxent_b200.h): stored in a bf16 tensor of
+# ntx_row_pitch(d, NTX_BF16X2) columns, computed on the tensor cores to fp32-grade accuracy
+BF16X2 = _RowsKind("bf16x2", torch.bfloat16)
+DTYPES = {torch.float32: NTX_F32, torch.bfloat16: NTX_BF16, BF16X2: NTX_BF16X2}
+
+
+def storage_dtype(rows_dtype) -> torch.dtype:
+    """torch dtype of the tensor that holds rows of `rows_dtype`."""
+    return rows_dtype.storage if isinstance(rows_dtype, _RowsKind) else rows_dtype
+
 
 EXPORTS = (
     "ntx_version", "ntx_last_error", "ntx_row_pitch", "ntx_row_scale", "ntx_plan", "ntx_l2norm", "ntx_fwd",
@@ -162,10 +183,11 @@ class Backend:
         _check(load().ntx_plan(q_rows, k_rows, d, DTYPES[dtype], sm_count, ctypes.byref(p)))
         return p
 
-    def l2norm(self, view0, view1, rows, inv_norm, row_scale: float = 1.0):
+    def l2norm(self, view0, view1, rows, inv_norm, row_scale: float = 1.0, rows_dtype=None):
+        """``rows_dtype``: what the rows tensor holds when that is not its torch dtype (``BF16X2``)."""
         n, d = view0.shape
         _check(load().ntx_l2norm(view0.data_ptr(), view1.data_ptr(), n, d, DTYPES[view0.dtype],
-                                 rows.data_ptr(), rows.shape[1], DTYPES[rows.dtype],
+                                 rows.data_ptr(), rows.shape[1], DTYPES[rows_dtype or rows.dtype],
                                  inv_norm.data_ptr(), float(row_scale), _stream(rows)))
 
     def project_l2norm(self, h0, h1, weight, rows, inv_norm, row_scale: float = 1.0):
@@ -218,11 +240,11 @@ class Backend:
                                    dview0.data_ptr(), dview1.data_ptr(), workspace.data_ptr(),
                                    workspace.numel() * workspace.element_size(), _stream(view0)))
 
-    def fwd(self, q, k, d, layout, temperature, rowsum, pos_logit, row_loss, loss_sum, workspace):
+    def fwd(self, q, k, d, layout, temperature, rowsum, pos_logit, row_loss, loss_sum, workspace, rows_dtype=None):
         lay = NtxLayout(*layout)
         lay.loss_dtype = DTYPES[loss_sum.dtype]               # two floats, or two bf16 values written ready to return
         _check(load().ntx_fwd(q.data_ptr(), k.data_ptr(), q.shape[0], k.shape[0], d, q.shape[1],
-                              DTYPES[q.dtype], ctypes.byref(lay), float(temperature), rowsum.data_ptr(),
+                              DTYPES[rows_dtype or q.dtype], ctypes.byref(lay), float(temperature), rowsum.data_ptr(),
                               pos_logit.data_ptr(), row_loss.data_ptr(), loss_sum.data_ptr(),
                               workspace.data_ptr(), workspace.numel() * workspace.element_size(),
                               _stream(q)))
@@ -245,10 +267,10 @@ class Backend:
         return DTYPES[w_q.dtype]
 
     def bwd(self, q, k, d, layout, temperature, rowsum_q, rowsum_k, w_q, w_k, w_stride, w_scale, view0,
-            view1, inv_norm, dview0, dview1, workspace):
+            view1, inv_norm, dview0, dview1, workspace, rows_dtype=None):
         lay = NtxLayout(*layout)
         _check(load().ntx_bwd(q.data_ptr(), k.data_ptr(), q.shape[0], k.shape[0], d, q.shape[1],
-                              DTYPES[q.dtype], ctypes.byref(lay), float(temperature), rowsum_q.data_ptr(),
+                              DTYPES[rows_dtype or q.dtype], ctypes.byref(lay), float(temperature), rowsum_q.data_ptr(),
                               rowsum_k.data_ptr(), w_q.data_ptr(), w_k.data_ptr(), int(w_stride),
                               self._weight_dtype(w_q, w_k), float(w_scale), view0.data_ptr(), view1.data_ptr(),
                               DTYPES[view0.dtype],

@@ -79,12 +79,16 @@ int check_layout(const NtxLayout* L, int q_rows, int k_rows) {
 
 int make_dims(int q_rows, int k_rows, int d, int ld, int dtype, const NtxLayout* L, float temperature,
               NtxDims* dm) {
-    NTX_CHECK_ARG(dtype == NTX_F32 || dtype == NTX_BF16, "rows dtype %d not supported", dtype);
+    NTX_CHECK_ARG(dtype == NTX_F32 || dtype == NTX_BF16 || dtype == NTX_BF16X2, "rows dtype %d not supported", dtype);
     NTX_CHECK_ARG(d >= 1, "feature dim d=%d must be positive", d);
+    if (dtype == NTX_BF16X2 && d > 128) {
+        ntx_set_error("two-term rows (NTX_BF16X2) support d <= 128 (got %d)", d);
+        return NTX_E_UNSUPPORTED;
+    }
     NTX_CHECK_ARG(ld == ntx_row_pitch(d, dtype), "ld=%d must be ntx_row_pitch(d=%d)=%d", ld, d,
                   ntx_row_pitch(d, dtype));
     NTX_CHECK_ARG(temperature > 0.f, "temperature must be positive (loss.py:16)");
-    if (temperature < NTX_MIN_TEMPERATURE && dtype == NTX_BF16) {
+    if (temperature < NTX_MIN_TEMPERATURE && dtype != NTX_F32) {
         ntx_set_error("temperature %g is below %g: the tensor-core kernels' fixed-shift logsumexp would leave fp32 "
                       "range; use fp32 rows, whose kernels switch to a max-shifted form",
                       (double)temperature, (double)NTX_MIN_TEMPERATURE);
@@ -99,6 +103,8 @@ int make_dims(int q_rows, int k_rows, int d, int ld, int dtype, const NtxLayout*
     dm->stable = temperature < NTX_MIN_TEMPERATURE ? 1 : 0;
     NTX_CHECK_ARG(L->loss_dtype == NTX_F32 || L->loss_dtype == NTX_BF16, "layout.loss_dtype %d not supported", L->loss_dtype);
     dm->loss_bf16 = L->loss_dtype == NTX_BF16 ? 1 : 0;
+    dm->split = dtype == NTX_BF16X2 ? 1 : 0;
+    dm->dh = dm->split ? ld / 2 : ld;
     // rows that carry sqrt(log2e / tau): only the value ntx_row_scale() hands out, and only bf16 rows
     const float rs = L->row_scale > 0.f ? L->row_scale : 1.0f;
     dm->scaled = 0;
@@ -107,7 +113,7 @@ int make_dims(int q_rows, int k_rows, int d, int ld, int dtype, const NtxLayout*
     dm->inv_rs = 1.0f;
     if (rs != 1.0f) {
         const float want = ntx_row_scale(temperature, dtype);
-        NTX_CHECK_ARG(dtype == NTX_BF16 && want != 1.0f && fabsf(rs - want) <= 1e-6f * want,
+        NTX_CHECK_ARG(dtype != NTX_F32 && want != 1.0f && fabsf(rs - want) <= 1e-6f * want,
                       "layout.row_scale=%g: rows must be unit rows (1) or, for bf16 rows, scaled by ntx_row_scale(%g)=%g",
                       (double)rs, (double)temperature, (double)want);
         dm->scaled = 1;
@@ -145,28 +151,32 @@ long long ntx_launch_count(void) { return g_launches.load(std::memory_order_rela
 const char* ntx_last_error(void) { return g_err; }
 
 float ntx_row_scale(float temperature, int dtype) {
-    if (dtype != NTX_BF16 || !(temperature >= NTX_MIN_TEMPERATURE)) return 1.0f;
+    if ((dtype != NTX_BF16 && dtype != NTX_BF16X2) || !(temperature >= NTX_MIN_TEMPERATURE)) return 1.0f;
     return sqrtf(NTX_LOG2E / temperature);
 }
 
 int ntx_row_pitch(int d, int dtype) {
     if (d < 1) return 0;
-    const int g = dtype == NTX_BF16 ? 64 : 4;
-    return (d + g - 1) / g * g;
+    const int g = dtype == NTX_F32 ? 4 : 64;
+    return (d + g - 1) / g * g * (dtype == NTX_BF16X2 ? 2 : 1);
 }
 
 int ntx_plan(int q_rows, int k_rows, int d, int dtype, int sm_count, NtxPlan* plan) {
     NTX_CHECK_ARG(plan != nullptr, "plan is NULL");
     NTX_CHECK_ARG(q_rows >= 1 && k_rows >= q_rows && d >= 1, "bad sizes q_rows=%d k_rows=%d d=%d",
                   q_rows, k_rows, d);
-    NTX_CHECK_ARG(dtype == NTX_F32 || dtype == NTX_BF16, "rows dtype %d not supported", dtype);
+    NTX_CHECK_ARG(dtype == NTX_F32 || dtype == NTX_BF16 || dtype == NTX_BF16X2, "rows dtype %d not supported", dtype);
     if (sm_count <= 0) {
         int rc = cached_sm_count(&sm_count);
         if (rc) return rc;
     }
     memset(plan, 0, sizeof(*plan));
-    plan->d_pad = ntx_row_pitch(d, dtype);
-    plan->tensor_cores = dtype == NTX_BF16 ? 1 : 0;
+    plan->d_pad = ntx_row_pitch(d, dtype == NTX_BF16X2 ? NTX_BF16 : dtype);
+    plan->tensor_cores = dtype == NTX_BF16 ? 1 : dtype == NTX_BF16X2 ? 2 : 0;
+    if (dtype == NTX_BF16X2 && plan->d_pad > 128) {
+        ntx_set_error("two-term rows (NTX_BF16X2) support d <= 128 (got %d)", d);
+        return NTX_E_UNSUPPORTED;
+    }
     if (plan->tensor_cores) {
         if (plan->d_pad > kTcMaxD) {
             ntx_set_error("bf16 rows: d=%d pads to %d > %d features per tile", d, plan->d_pad, kTcMaxD);
@@ -216,7 +226,7 @@ int ntx_plan(int q_rows, int k_rows, int d, int dtype, int sm_count, NtxPlan* pl
     // (rb, kt >= rb) need computing.  Needs one column partial per (row block, key) besides the slots.
     plan->fwd_grid = plan->grid;
     plan->fwd_max_slots = max_slots;
-    if (plan->tensor_cores && q_rows == k_rows && plan->d_pad <= 128 && plan->row_blocks >= 2 &&
+    if (plan->tensor_cores == 1 && q_rows == k_rows && plan->d_pad <= 128 && plan->row_blocks >= 2 &&
         getenv("NTXENT_NO_SYMMETRIC_FWD") == nullptr) {
         const int RB = plan->row_blocks;
         const long long Tt = (long long)RB * (RB + 1) / 2;
@@ -240,11 +250,20 @@ int ntx_l2norm(const void* view0, const void* view1, int n, int d, int in_dtype,
     NTX_CHECK_ARG(n >= 1 && d >= 1, "bad sizes n=%d d=%d", n, d);
     NTX_CHECK_ARG(view0 && view1 && rows && inv_norm, "NULL buffer");
     NTX_CHECK_ARG(in_dtype == NTX_F32 || in_dtype == NTX_BF16, "view dtype %d not supported", in_dtype);
-    NTX_CHECK_ARG(rows_dtype == NTX_F32 || rows_dtype == NTX_BF16, "rows dtype %d not supported",
-                  rows_dtype);
+    NTX_CHECK_ARG(rows_dtype == NTX_F32 || rows_dtype == NTX_BF16 || rows_dtype == NTX_BF16X2,
+                  "rows dtype %d not supported", rows_dtype);
+    NTX_CHECK_ARG(row_scale >= 0.f, "row_scale must not be negative");
+    if (rows_dtype == NTX_BF16X2) {
+        // two-term rows: [hi | lo], each half ld / 2 = d rounded up to 64 wide
+        NTX_CHECK_ARG(d <= 128 && ld == ntx_row_pitch(d, NTX_BF16X2),
+                      "two-term rows: d=%d must be <= 128 and ld=%d equal to ntx_row_pitch(d, NTX_BF16X2)=%d", d, ld,
+                      ntx_row_pitch(d, NTX_BF16X2));
+        NTX_CHECK_ARG(reinterpret_cast<uintptr_t>(rows) % 16 == 0, "rows must be 16-byte aligned");
+        return ntx_l2norm_split_launch(view0, view1, n, d, in_dtype, rows, ld, inv_norm, row_scale > 0.f ? row_scale : 1.0f,
+                                       (cudaStream_t)stream);
+    }
     NTX_CHECK_ARG(ld >= ntx_row_pitch(d, rows_dtype) && ld % (rows_dtype == NTX_BF16 ? 64 : 4) == 0,
                   "ld=%d too small or misaligned for d=%d", ld, d);
-    NTX_CHECK_ARG(row_scale >= 0.f, "row_scale must not be negative");
     return ntx_l2norm_launch(view0, view1, n, d, in_dtype, rows, NtxPeerOut{}, 0, 0, nullptr, ld, rows_dtype, inv_norm,
                              row_scale > 0.f ? row_scale : 1.0f, (cudaStream_t)stream);
 }
@@ -306,7 +325,7 @@ int fwd_impl(const void* q, const void* k, int q_rows, int k_rows, int d, int ld
         // shares), equal for 1 of 4, 168 against 164 us for 1 of 2 and 226 against 220 us on one GPU, where the
         // shares are large and the separate, fully occupied finalize kernel is faster; 83.3 against 85.0 us per
         // step in the 8-GPU bench.  Default: the separate finalize kernel.
-        const bool no_fold = !fold_wanted(plan);
+        const bool no_fold = !fold_wanted(plan) || dm.split;
         char* ws = (char*)workspace;
         const uint64_t head = ntx_fold_ctl_bytes(plan.row_blocks) + ntx_fold_seg_bytes(plan.row_blocks, plan.grid);
         const uint64_t partial_bytes = (uint64_t)plan.max_slots * rows_pad * sizeof(float);
@@ -395,7 +414,7 @@ static int bwd_impl(const void* q, const void* k, int q_rows, int k_rows, int d,
         // the tensor-core kernel also finishes the rows (fold counters at the head of the scratch) whenever the
         // vectorised finalize applies; odd shapes keep the separate, unaligned finalize kernel
         auto al16 = [](const void* p) { return reinterpret_cast<uintptr_t>(p) % 16 == 0; };
-        const bool no_fold = !fold_wanted(plan);
+        const bool no_fold = !fold_wanted(plan) || dm.split;
         const bool fused = !no_fold && d % 4 == 0 && row_pitch_in % 4 == 0 && al16(view0) && al16(view1) && al16(dview0) &&
                            al16(dview1);
         char* ws = (char*)workspace;

@@ -143,6 +143,8 @@ struct NtxDims {
     float pos_scale;     // <row, partner row> -> positive logit s: ln 2                     (1/tau when not scaled)
     float inv_rs;        // 1 / sqrt(c1) : dZ' = C . K' and the rows themselves -> unit rows (1 when not scaled)
     int loss_bf16;       // loss_sum receives two bf16 values instead of two floats (NtxLayout.loss_dtype)
+    int split;           // NTX_BF16X2 rows: [hi | lo] bf16 terms, each dh = ld / 2 elements wide
+    int dh;
 };
 #ifdef __CUDACC__
 // loss.py:60-65: the reduced loss, sum and mean (= sum / N * 0.5 over the 2N rows), in the dtype the caller asked for
@@ -362,6 +364,9 @@ __device__ __forceinline__ void ntx_fold_init(unsigned int* tag, unsigned int* d
 int ntx_l2norm_launch(const void* v0, const void* v1, int n, int d, int in_dtype, void* rows, const NtxPeerOut& peers,
                       size_t keys_off, size_t key_buf_bytes, uint32_t* step_out, int ld, int rows_dtype,
                       float* inv_norm, float row_scale, cudaStream_t st);
+// NTX_BF16X2 rows: [hi | lo] bf16 terms of the fp32 normalised row (ntx_l2norm.cu)
+int ntx_l2norm_split_launch(const void* v0, const void* v1, int n, int d, int in_dtype, void* rows, int ld,
+                            float* inv_norm, float row_scale, cudaStream_t st);
 int ntx_post_weights_launch(const void* w, int w_stride, int w_bf16, int q_rows, const NtxPeerOut& peers, size_t weight_off,
                             const uint32_t* step, cudaStream_t st);
 int ntx_make_rows_tmap(void* map, const void* base, int rows, int ld, int box_rows);      // map = CUtensorMap*

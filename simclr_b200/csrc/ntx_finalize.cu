@@ -86,9 +86,18 @@ fwd_finalize_kernel(const T* __restrict__ q, NtxDims dm, int lanes, int tile_row
         const int p = ntx_pos_row(r, dm.n_local);
         const T* a = q + (size_t)r * dm.ld;
         const T* b = q + (size_t)p * dm.ld;
-        for (int c = sub * 4; c < dm.ld; c += lanes * 4) {      // ld is a multiple of 4
-            const float4 x = ld4(a + c), y = ld4(b + c);
-            dot = fmaf(x.x, y.x, fmaf(x.y, y.y, fmaf(x.z, y.z, fmaf(x.w, y.w, dot))));
+        if (dm.split) {                                          // two-term rows: x = hi + lo, exact in fp32
+            for (int c = sub * 4; c < dm.dh; c += lanes * 4) {
+                const float4 xh = ld4(a + c), xl = ld4(a + dm.dh + c), yh = ld4(b + c), yl = ld4(b + dm.dh + c);
+                const float4 x = make_float4(xh.x + xl.x, xh.y + xl.y, xh.z + xl.z, xh.w + xl.w);
+                const float4 y = make_float4(yh.x + yl.x, yh.y + yl.y, yh.z + yl.z, yh.w + yl.w);
+                dot = fmaf(x.x, y.x, fmaf(x.y, y.y, fmaf(x.z, y.z, fmaf(x.w, y.w, dot))));
+            }
+        } else {
+            for (int c = sub * 4; c < dm.ld; c += lanes * 4) {  // ld is a multiple of 4
+                const float4 x = ld4(a + c), y = ld4(b + c);
+                dot = fmaf(x.x, y.x, fmaf(x.y, y.y, fmaf(x.z, y.z, fmaf(x.w, y.w, dot))));
+            }
         }
     }
     // Row sums first, with the block laid out rows-fastest so that a warp reads 32 consecutive rows of one

@@ -219,7 +219,54 @@ post_weights_kernel(const float* __restrict__ w, int w_stride, int w_bf16, int q
     }
 }
 
+
+// NTX_BF16X2 rows: the fp32 normalised (and scaled) row x as two bf16 terms, hi = bf16(x) in columns [0, dh) and
+// lo = bf16(x - hi) in [dh, 2 dh), zero padded from d to dh.  One warp per row, two columns per lane and pass.
+template <typename TIn>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+l2norm_split_kernel(const TIn* __restrict__ view0, const TIn* __restrict__ view1, int n, int d,
+                    __nv_bfloat16* __restrict__ rows, int dh, float* __restrict__ inv_norm, float row_scale) {
+    ntx_dep_trigger();
+    ntx_dep_wait();
+    const int lane = threadIdx.x & 31;
+    const int r = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
+    if (r >= 2 * n) return;                                   // whole warps leave together
+    const TIn* src = (r < n) ? view0 + (size_t)r * d : view1 + (size_t)(r - n) * d;
+    float ss = 0.f;
+    for (int c = lane; c < d; c += 32) {
+        const float v = to_f32(src[c]);
+        ss = fmaf(v, v, ss);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    const float denom = fmaxf(sqrtf(ss), 1e-12f);             // clamp_min(eps) of F.normalize
+    if (lane == 0) inv_norm[r] = 1.0f / denom;
+    __nv_bfloat16* dst = rows + (size_t)r * 2 * dh;
+    for (int c = 2 * lane; c < dh; c += 64) {
+        const float x0 = c < d ? to_f32(src[c]) / denom * row_scale : 0.f;
+        const float x1 = c + 1 < d ? to_f32(src[c + 1]) / denom * row_scale : 0.f;
+        const __nv_bfloat162 hi = __floats2bfloat162_rn(x0, x1);
+        const float2 hf = __bfloat1622float2(hi);
+        const __nv_bfloat162 lo = __floats2bfloat162_rn(x0 - hf.x, x1 - hf.y);     // the differences are exact in fp32
+        *reinterpret_cast<__nv_bfloat162*>(dst + c) = hi;
+        *reinterpret_cast<__nv_bfloat162*>(dst + dh + c) = lo;
+    }
+}
+
 }  // namespace
+
+int ntx_l2norm_split_launch(const void* v0, const void* v1, int n, int d, int in_dtype, void* rows, int ld,
+                            float* inv_norm, float row_scale, cudaStream_t st) {
+    const int grid = (2 * n + kWarpsPerBlock - 1) / kWarpsPerBlock;
+    if (in_dtype == NTX_F32)
+        NTX_CUDA(ntx_launch_dep(l2norm_split_kernel<float>, grid, kWarpsPerBlock * 32, 0, st, (const float*)v0,
+                                (const float*)v1, n, d, (__nv_bfloat16*)rows, ld / 2, inv_norm, row_scale));
+    else
+        NTX_CUDA(ntx_launch_dep(l2norm_split_kernel<__nv_bfloat16>, grid, kWarpsPerBlock * 32, 0, st,
+                                (const __nv_bfloat16*)v0, (const __nv_bfloat16*)v1, n, d, (__nv_bfloat16*)rows, ld / 2,
+                                inv_norm, row_scale));
+    return NTX_OK;
+}
 
 int ntx_post_weights_launch(const void* w, int w_stride, int w_bf16, int q_rows, const NtxPeerOut& peers,
                             size_t weight_off, const uint32_t* step, cudaStream_t st) {

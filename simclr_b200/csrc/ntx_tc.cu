@@ -162,18 +162,36 @@ __device__ __forceinline__ bool positive_tile(int rb, int kt, const NtxDims& dm)
     return hit(r0, r1);
 }
 
-// S = Q . K^T for one key tile: NDB blocks of 64 features, 4 MMAs (K = 16) per block
-template <int NDB>
+// S = Q . K^T for one key tile: NDB blocks of 64 features, 4 MMAs (K = 16) per block.
+// kSplit (NTX_BF16X2 rows): the tile holds NDB / 2 blocks of hi terms followed by NDB / 2 blocks of lo terms and
+// S = hi.lo + lo.hi + hi.hi, accumulated in fp32 in TMEM.  The lo.lo products (2^-18 of a term, below the 2^-17 to
+// which two bf16 terms hold a value anyway) are left out: with them the error against the fp64 oracle was the same.
+template <int NDB, bool kSplit = false>
 __device__ __forceinline__ void issue_gemm1(uint32_t d_tmem, const uint8_t* q_smem, const uint8_t* k_tile) {
     constexpr uint32_t idesc = instr_desc_bf16(128, 128, 0);
+    if constexpr (kSplit) {
+        constexpr int NH = NDB / 2;
 #pragma unroll
-    for (int b = 0; b < NDB; ++b)
+        for (int t = 0; t < 3; ++t)                // (q term, k term): (hi, lo), (lo, hi), (hi, hi)
 #pragma unroll
-        for (int k4 = 0; k4 < 4; ++k4) {
-            const uint64_t a = smem_desc_sw128(smem_u32(q_smem + b * kBlkBytes + k4 * 32), 16, 1024);
-            const uint64_t bd = smem_desc_sw128(smem_u32(k_tile + b * kBlkBytes + k4 * 32), 16, 1024);
-            mma_bf16_ss(d_tmem, a, bd, idesc, (b | k4) ? 1u : 0u);
-        }
+            for (int b = 0; b < NH; ++b)
+#pragma unroll
+                for (int k4 = 0; k4 < 4; ++k4) {
+                    const int qb = t == 1 ? NH + b : b, kb = t == 0 ? NH + b : b;
+                    const uint64_t a = smem_desc_sw128(smem_u32(q_smem + qb * kBlkBytes + k4 * 32), 16, 1024);
+                    const uint64_t bd = smem_desc_sw128(smem_u32(k_tile + kb * kBlkBytes + k4 * 32), 16, 1024);
+                    mma_bf16_ss(d_tmem, a, bd, idesc, (t | b | k4) ? 1u : 0u);
+                }
+    } else {
+#pragma unroll
+        for (int b = 0; b < NDB; ++b)
+#pragma unroll
+            for (int k4 = 0; k4 < 4; ++k4) {
+                const uint64_t a = smem_desc_sw128(smem_u32(q_smem + b * kBlkBytes + k4 * 32), 16, 1024);
+                const uint64_t bd = smem_desc_sw128(smem_u32(k_tile + b * kBlkBytes + k4 * 32), 16, 1024);
+                mma_bf16_ss(d_tmem, a, bd, idesc, (b | k4) ? 1u : 0u);
+            }
+    }
 }
 
 __device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
@@ -249,7 +267,8 @@ template <int NS> struct FwdCtl {
 
 // kScaled: the rows carry sqrt(log2e / tau) (NtxDims.scaled), so a similarity value IS the exponent: no FFMA2, and
 // the row sums are sums of e' = e * 2^c1 (NtxDims.rowsum_scale takes the factor out where they are finished)
-template <int NDB, bool kScaled>
+// kSplit: NTX_BF16X2 rows (issue_gemm1 above); every exponential on MUFU, the polynomial's 7.5e-5 is too coarse here
+template <int NDB, bool kScaled, bool kSplit = false>
 __global__ void __launch_bounds__(kFwdThreads, 1)
 tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
               const __grid_constant__ CUtensorMap tmap_q1, const __grid_constant__ CUtensorMap tmap_k1,
@@ -331,7 +350,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
                     tc_fence_after();
                     NTX_TIC(tm_issue);
                     if (elect_one()) {
-                        issue_gemm1<NDB>(tmem_base + buf * 128, q_smem, k_smem + s * kTileBytes);
+                        issue_gemm1<NDB, kSplit>(tmem_base + buf * 128, q_smem, k_smem + s * kTileBytes);
                         mma_commit(&ctl->k_empty[s]);
                         mma_commit(&ctl->s_full[buf]);
                     }
@@ -432,7 +451,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
                         for (int j = 0; j < 16; ++j) {
                             const f32x2 raw = pack2(__uint_as_float(v[ch & 1][2 * j]), __uint_as_float(v[ch & 1][2 * j + 1]));
                             const f32x2 x = kScaled ? raw : fma2(raw, c1x2, nc1x2);
-                            const bool poly = NTX_FWD_POLY > 0 && ((j * NTX_FWD_POLY) & 3) < NTX_FWD_POLY;
+                            const bool poly = !kSplit && NTX_FWD_POLY > 0 && ((j * NTX_FWD_POLY) & 3) < NTX_FWD_POLY;
                             pacc[j & 1] = add2(pacc[j & 1], poly ? ex2_pair_poly(x) : ex2_pair_mufu(x));
                         }
                     } else {
@@ -876,12 +895,16 @@ tc_fwd_sym_kernel(const __grid_constant__ CUtensorMap tmap, NtxDims dm, int key_
 // ============================================================================ backward
 // NDB = 1, 2 (d_pad 64, 128): dZ in TMEM columns [0, 128), three S/C buffers, three groups.
 // NDB = 4       (d_pad 256) : dZ in TMEM columns [0, 256), two S/C buffers, two groups.
-template <int NDB> struct BwdCfg {
-    static constexpr int NWG = NDB == 4 ? 2 : 3;           // epilogue groups = S/C buffers
-    static constexpr int NS = NDB == 4 ? 2 : 6;            // multiple of NWG: the MMA loop unrolls by NS
-    static constexpr int DP = NDB * 64;                    // dZ columns
-    static constexpr uint32_t kSCol = NDB == 4 ? 256 : 128;
-    static constexpr int kThreads = NWG * 128 + 96;        // + producer warp + GEMM1 warp + GEMM2 warp
+// kSplit (NTX_BF16X2 rows, NDB = 2 or 4 blocks of [hi | lo] terms, d_pad = NDB * 32): dZ in columns [0, 128), two
+//   buffers of 192 columns: S (128 fp32 columns), over which the hi term of the coefficient tile is written in place
+//   (64 columns), then 64 columns for its lo term; two groups.
+template <int NDB, bool kSplit = false> struct BwdCfg {
+    static constexpr int NWG = (NDB == 4 || kSplit) ? 2 : 3;   // epilogue groups = S/C buffers
+    static constexpr int NS = NDB == 4 ? 2 : (kSplit ? 4 : 6); // multiple of NWG: the MMA loop unrolls by NS
+    static constexpr int DP = kSplit ? NDB * 32 : NDB * 64;    // dZ columns
+    static constexpr uint32_t kSCol = (NDB == 4 && !kSplit) ? 256 : 128;
+    static constexpr uint32_t kBufCols = kSplit ? 192 : 128;   // TMEM columns per S/C buffer
+    static constexpr int kThreads = NWG * 128 + 96;            // + producer warp + GEMM1 warp + GEMM2 warp
 };
 template <int NS, int NWG> struct BwdCtl {
     uint64_t q_full, q_empty, k_full[NS], k_empty[NS], s_full[NWG], c_full[NWG], buf_free[NWG], dz_full,
@@ -938,11 +961,12 @@ __device__ __forceinline__ void st4_any(void* base, size_t i, float4 v, int bf16
     }
 }
 
-// 32 similarity values of one row -> 32 coefficients, packed bf16x2
-template <bool kEdge, bool kScaled>
-__device__ __forceinline__ void coef_chunk(const uint32_t (&v)[32], uint32_t (&pk)[16], const float* bt,
-                                           float alpha, float c1, float nc1, int col0, int self, int k_rows,
-                                           bool row_ok) {
+// 32 similarity values of one row -> 32 coefficients, packed bf16x2.  kSplit: the coefficients as two bf16 terms,
+// pk = bf16(c), pk_lo = bf16(c - pk), and every exponential on MUFU.
+template <bool kEdge, bool kScaled, bool kSplit = false>
+__device__ __forceinline__ void coef_chunk(const uint32_t (&v)[32], uint32_t (&pk)[16], uint32_t (&pk_lo)[16],
+                                           const float* bt, float alpha, float c1, float nc1, int col0, int self,
+                                           int k_rows, bool row_ok) {
     const f32x2 c1x2 = pack2(c1, c1), nc1x2 = pack2(nc1, nc1), alpha2 = pack2(alpha, alpha);
 #pragma unroll
     for (int j4 = 0; j4 < 8; ++j4) {
@@ -953,7 +977,7 @@ __device__ __forceinline__ void coef_chunk(const uint32_t (&v)[32], uint32_t (&p
             const int j = j4 * 4 + h * 2;
             const f32x2 raw = pack2(__uint_as_float(v[j]), __uint_as_float(v[j + 1]));
             const f32x2 x = kScaled ? raw : fma2(raw, c1x2, nc1x2);
-            const bool poly = !kEdge && NTX_BWD_POLY > 0 && (((j4 * 2 + h) * NTX_BWD_POLY) & 3) < NTX_BWD_POLY;
+            const bool poly = !kEdge && !kSplit && NTX_BWD_POLY > 0 && (((j4 * 2 + h) * NTX_BWD_POLY) & 3) < NTX_BWD_POLY;
             const f32x2 e = poly ? ex2_pair_poly(x) : ex2_pair_mufu(x);
             float c0, c1v;
             unpack2(mul2(e, add2(alpha2, beta2[h])), c0, c1v);
@@ -964,24 +988,29 @@ __device__ __forceinline__ void coef_chunk(const uint32_t (&v)[32], uint32_t (&p
             }
             __nv_bfloat162 hh = __floats2bfloat162_rn(c0, c1v);
             pk[j4 * 2 + h] = *reinterpret_cast<uint32_t*>(&hh);
+            if constexpr (kSplit) {
+                const float2 hf = __bfloat1622float2(hh);
+                __nv_bfloat162 ll = __floats2bfloat162_rn(c0 - hf.x, c1v - hf.y);
+                pk_lo[j4 * 2 + h] = *reinterpret_cast<uint32_t*>(&ll);
+            }
         }
     }
 }
 
 // kGate: peer exchange (the row sums and weights of other ranks' keys arrive during the kernel); a separate
 // instantiation so the single-GPU kernel keeps exactly its own instruction stream
-template <int NDB, bool kGate, bool kScaled>
-__global__ void __launch_bounds__(BwdCfg<NDB>::kThreads, 1)
+template <int NDB, bool kGate, bool kScaled, bool kSplit = false>
+__global__ void __launch_bounds__(BwdCfg<NDB, kSplit>::kThreads, 1)
 tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
               const __grid_constant__ CUtensorMap tmap_q1, const __grid_constant__ CUtensorMap tmap_k1,
               NtxDims dm, int key_tiles, long long T, int rows_pad, BwdWeights wt,
               float* __restrict__ partial, NtxGate gate, BwdFuse fuse) {
-    using Cfg = BwdCfg<NDB>;
+    using Cfg = BwdCfg<NDB, kSplit>;
 #ifdef NTX_TIMELINE
     const long long t_entry = clock64();
 #endif
     constexpr int NS = Cfg::NS, NWG = Cfg::NWG, DP = Cfg::DP;
-    constexpr uint32_t kSCol = Cfg::kSCol;
+    constexpr uint32_t kSCol = Cfg::kSCol, kBufCols = Cfg::kBufCols;
     constexpr uint32_t kTileBytes = NDB * kBlkBytes;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = checked_1024(smem_raw);
@@ -1058,7 +1087,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
                 tc_fence_after();
                 NTX_TIC(tm_issue);
                 if (elect_one()) {
-                    issue_gemm1<NDB>(tmem_base + kSCol + sb * 128, q_smem, k_smem + s * kTileBytes);
+                    issue_gemm1<NDB, kSplit>(tmem_base + kSCol + sb * kBufCols, q_smem, k_smem + s * kTileBytes);
                     mma_commit(&ctl->s_full[sb]);
                     if (last_of_seg) mma_commit(&ctl->q_empty);
                 }
@@ -1090,13 +1119,22 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
                 tc_fence_after();
                 NTX_TIC(tm_issue);
                 if (elect_one()) {
-                    const uint32_t c_tmem = tmem_base + kSCol + cb * 128;
+                    const uint32_t c_tmem = tmem_base + kSCol + cb * kBufCols;
                     const uint8_t* k_tile = k_smem + sj * kTileBytes;
 #pragma unroll
                     for (int kk = 0; kk < 8; ++kk) {
                         // MN-major key tile: next 64 features one 16 KB block away, 8-key groups 1 KB apart
                         const uint64_t bd = smem_desc_sw128(smem_u32(k_tile + kk * 2048), kBlkBytes, 1024);
-                        mma_bf16_ts(tmem_base, c_tmem + kk * 8, bd, idesc2, (first_of_seg && kk == 0) ? 0u : 1u);
+                        if constexpr (kSplit) {
+                            // dZ += C_lo . K_hi + C_hi . K_lo + C_hi . K_hi; the lo blocks of the tile follow its hi blocks
+                            const uint64_t bd_lo =
+                                smem_desc_sw128(smem_u32(k_tile + (NDB / 2) * kBlkBytes + kk * 2048), kBlkBytes, 1024);
+                            mma_bf16_ts(tmem_base, c_tmem + 128 + kk * 8, bd, idesc2, (first_of_seg && kk == 0) ? 0u : 1u);
+                            mma_bf16_ts(tmem_base, c_tmem + kk * 8, bd_lo, idesc2, 1u);
+                            mma_bf16_ts(tmem_base, c_tmem + kk * 8, bd, idesc2, 1u);
+                        } else {
+                            mma_bf16_ts(tmem_base, c_tmem + kk * 8, bd, idesc2, (first_of_seg && kk == 0) ? 0u : 1u);
+                        }
                     }
                     mma_commit(&ctl->k_empty[sj]);
                     mma_commit(&ctl->buf_free[cb]);
@@ -1116,7 +1154,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         const int tid_g = threadIdx.x & 127;
         const int row_in_tile = (warp & 3) * 32 + lane;
         const uint32_t t_lane = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
-        const uint32_t taddr = t_lane + kSCol + g * 128;
+        const uint32_t taddr = t_lane + kSCol + g * kBufCols;
         const float c1 = dm.c1, nc1 = -dm.c1;
         float alpha = 0.f;
         bool row_ok = false;
@@ -1216,14 +1254,15 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
                 const int self = ntx_self_col(rb * 128 + row_in_tile, dm.n_local, dm.rank);
 #pragma unroll 1
                 for (int ch = 0; ch < 4; ++ch) {
-                    uint32_t v[32], pk[16];
+                    uint32_t v[32], pk[16], pk_lo[16];                    // pk_lo: two-term rows only
                     tmem_ld_32x32(taddr + ch * 32, v);
                     tmem_ld_wait_dep(v);
                     if (!edge)
-                        coef_chunk<false, kScaled>(v, pk, bt + ch * 32, alpha, c1, nc1, 0, 0, 0, true);
+                        coef_chunk<false, kScaled, kSplit>(v, pk, pk_lo, bt + ch * 32, alpha, c1, nc1, 0, 0, 0, true);
                     else
-                        coef_chunk<true, kScaled>(v, pk, bt + ch * 32, alpha, c1, nc1, kt * 128 + ch * 32, self,
-                                         dm.k_rows, row_ok);
+                        coef_chunk<true, kScaled, kSplit>(v, pk, pk_lo, bt + ch * 32, alpha, c1, nc1, kt * 128 + ch * 32,
+                                                          self, dm.k_rows, row_ok);
+                    if constexpr (kSplit) tmem_st_32x16(taddr + 128 + ch * 16, pk_lo);   // lo terms behind the S columns
                     // bf16 pairs over fp32 columns already read: keys [32ch, 32ch+32) -> columns [16ch, +16)
                     tmem_st_32x16(taddr + ch * 16, pk);
                 }
@@ -1396,8 +1435,9 @@ int make_rows_tmap(CUtensorMap* m, const __nv_bfloat16* base, int rows, int ld, 
 template <int NDB> size_t fwd_smem_bytes() {
     return (size_t)(1 + FwdCfg<NDB>::NS) * NDB * kBlkBytes + sizeof(FwdCtl<FwdCfg<NDB>::NS>);
 }
-template <int NDB> size_t bwd_smem_bytes() {
-    return (size_t)(1 + BwdCfg<NDB>::NS) * NDB * kBlkBytes + sizeof(BwdCtl<BwdCfg<NDB>::NS, BwdCfg<NDB>::NWG>);
+template <int NDB, bool kSplit = false> size_t bwd_smem_bytes() {
+    using Cfg = BwdCfg<NDB, kSplit>;
+    return (size_t)(1 + Cfg::NS) * NDB * kBlkBytes + sizeof(BwdCtl<Cfg::NS, Cfg::NWG>);
 }
 
 // the maps of a launch: rows and keys in key buffer 0 and, with a peer exchange, in key buffer 1
@@ -1420,32 +1460,32 @@ int make_row_maps(RowMaps* m, const __nv_bfloat16* q, const __nv_bfloat16* k, co
     return NTX_OK;
 }
 
-template <int NDB, bool kScaled>
+template <int NDB, bool kScaled, bool kSplit = false>
 int launch_fwd_s(const RowMaps& m, const NtxDims& dm, const NtxPlan& plan, float* partial, const NtxFoldScratch& fold,
                  const NtxFwdOut& out, const NtxGate& gate, cudaStream_t st) {
     const size_t smem = fwd_smem_bytes<NDB>();
-    NTX_SMEM_OPT_IN((tc_fwd_kernel<NDB, kScaled>), smem);
+    NTX_SMEM_OPT_IN((tc_fwd_kernel<NDB, kScaled, kSplit>), smem);
     const long long T = (long long)plan.row_blocks * plan.key_tiles;
-    NTX_CUDA(ntx_launch_dep(tc_fwd_kernel<NDB, kScaled>, plan.grid, kFwdThreads, smem, st, m.q[0], m.k[0], m.q[1], m.k[1],
-                            dm, plan.key_tiles, T, plan.row_blocks * plan.tile_rows, partial, fold, out, gate));
+    NTX_CUDA(ntx_launch_dep(tc_fwd_kernel<NDB, kScaled, kSplit>, plan.grid, kFwdThreads, smem, st, m.q[0], m.k[0], m.q[1],
+                            m.k[1], dm, plan.key_tiles, T, plan.row_blocks * plan.tile_rows, partial, fold, out, gate));
     return NTX_OK;
 }
-template <int NDB>
+template <int NDB, bool kSplit = false>
 int launch_fwd(const RowMaps& m, const NtxDims& dm, const NtxPlan& plan, float* partial, const NtxFoldScratch& fold,
                const NtxFwdOut& out, const NtxGate& gate, cudaStream_t st) {
-    return dm.scaled ? launch_fwd_s<NDB, true>(m, dm, plan, partial, fold, out, gate, st)
-                     : launch_fwd_s<NDB, false>(m, dm, plan, partial, fold, out, gate, st);
+    return dm.scaled ? launch_fwd_s<NDB, true, kSplit>(m, dm, plan, partial, fold, out, gate, st)
+                     : launch_fwd_s<NDB, false, kSplit>(m, dm, plan, partial, fold, out, gate, st);
 }
 
-template <int NDB, bool kGate, bool kScaled>
+template <int NDB, bool kGate, bool kScaled, bool kSplit = false>
 int launch_bwd_gs(const RowMaps& m, const NtxDims& dm, const NtxPlan& plan, const BwdWeights& wt, float* partial,
                   const NtxGate& gate, const BwdFuse& fuse, cudaStream_t st) {
-    const size_t smem = bwd_smem_bytes<NDB>();
-    NTX_SMEM_OPT_IN((tc_bwd_kernel<NDB, kGate, kScaled>), smem);
+    const size_t smem = bwd_smem_bytes<NDB, kSplit>();
+    NTX_SMEM_OPT_IN((tc_bwd_kernel<NDB, kGate, kScaled, kSplit>), smem);
     const long long T = (long long)plan.row_blocks * plan.key_tiles;
-    NTX_CUDA(ntx_launch_dep(tc_bwd_kernel<NDB, kGate, kScaled>, plan.grid, BwdCfg<NDB>::kThreads, smem, st, m.q[0], m.k[0],
-                            m.q[1], m.k[1], dm, plan.key_tiles, T, plan.row_blocks * plan.tile_rows, wt, partial, gate,
-                            fuse));
+    NTX_CUDA(ntx_launch_dep(tc_bwd_kernel<NDB, kGate, kScaled, kSplit>, plan.grid, BwdCfg<NDB, kSplit>::kThreads, smem, st,
+                            m.q[0], m.k[0], m.q[1], m.k[1], dm, plan.key_tiles, T, plan.row_blocks * plan.tile_rows, wt,
+                            partial, gate, fuse));
     return NTX_OK;
 }
 template <int NDB>
@@ -1456,6 +1496,13 @@ int launch_bwd(const RowMaps& m, const NtxDims& dm, const NtxPlan& plan, const B
                          : launch_bwd_gs<NDB, false, true>(m, dm, plan, wt, partial, gate, fuse, st);
     return gate.step ? launch_bwd_gs<NDB, true, false>(m, dm, plan, wt, partial, gate, fuse, st)
                      : launch_bwd_gs<NDB, false, false>(m, dm, plan, wt, partial, gate, fuse, st);
+}
+// two-term rows (NTX_BF16X2): one rank or an all-gathered key buffer, no peer gate
+template <int NDB>
+int launch_bwd_split(const RowMaps& m, const NtxDims& dm, const NtxPlan& plan, const BwdWeights& wt, float* partial,
+                     const NtxGate& gate, const BwdFuse& fuse, cudaStream_t st) {
+    return dm.scaled ? launch_bwd_gs<NDB, false, true, true>(m, dm, plan, wt, partial, gate, fuse, st)
+                     : launch_bwd_gs<NDB, false, false, true>(m, dm, plan, wt, partial, gate, fuse, st);
 }
 
 }  // namespace
@@ -1477,6 +1524,16 @@ int ntx_tc_fwd_launch(const __nv_bfloat16* q, const __nv_bfloat16* k, const NtxD
     RowMaps m;
     int rc = make_row_maps(&m, q, k, dm, gate, key_buf_elems);
     if (rc) return rc;
+    if (dm.split) {                     // tiles of [hi | lo] terms: plan.d_pad is the width of one term
+        if (gate.step) {
+            ntx_set_error("two-term rows are not built for the peer exchange");
+            return NTX_E_UNSUPPORTED;
+        }
+        if (plan.d_pad == 64) return launch_fwd<2, true>(m, dm, plan, partial, fold, out, gate, st);
+        if (plan.d_pad == 128) return launch_fwd<4, true>(m, dm, plan, partial, fold, out, gate, st);
+        ntx_set_error("tensor-core forward on two-term rows: padded feature dim %d not built", plan.d_pad);
+        return NTX_E_UNSUPPORTED;
+    }
     switch (plan.d_pad) {
         case 64: return launch_fwd<1>(m, dm, plan, partial, fold, out, gate, st);
         case 128: return launch_fwd<2>(m, dm, plan, partial, fold, out, gate, st);
@@ -1524,6 +1581,16 @@ int ntx_tc_bwd_launch(const __nv_bfloat16* q, const __nv_bfloat16* k, const NtxD
     BwdWeights wt{w.rowsum_q, w.rowsum_k, w.w_q, w.w_k, w.w_stride, w.w_scale, w.w_chunk, w.w_bf16, w.coef_scale};
     const BwdFuse fuse{o.view0, o.view1, o.dview0, o.dview1, o.inv_norm, o.tag, o.done_total, o.arrive, o.row_blocks,
                        o.in_ld, o.normalised, o.in_bf16, dm.d, o.enabled};
+    if (dm.split) {
+        if (gate.step) {
+            ntx_set_error("two-term rows are not built for the peer exchange");
+            return NTX_E_UNSUPPORTED;
+        }
+        if (plan.d_pad == 64) return launch_bwd_split<2>(m, dm, plan, wt, partial, gate, fuse, st);
+        if (plan.d_pad == 128) return launch_bwd_split<4>(m, dm, plan, wt, partial, gate, fuse, st);
+        ntx_set_error("tensor-core backward on two-term rows: padded feature dim %d not built", plan.d_pad);
+        return NTX_E_UNSUPPORTED;
+    }
     switch (plan.d_pad) {
         case 64: return launch_bwd<1>(m, dm, plan, wt, partial, gate, fuse, st);
         case 128: return launch_bwd<2>(m, dm, plan, wt, partial, gate, fuse, st);

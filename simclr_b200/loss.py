@@ -23,6 +23,9 @@ import torch.distributed as dist
 from . import _cabi, peer_exchange
 
 MIN_TC_TEMPERATURE = 0.0235         # NTX_MIN_TEMPERATURE of the library: below it only fp32 rows are served
+FP32_TC_MIN_KEYS = 2048             # fp32 inputs with at least this many keys use the two-term tensor-core path,
+FP32_TC_MIN_TEMPERATURE = 0.1       # from this temperature upwards (its 2^-17 rounding grows like 1/temperature:
+                                    # gradient error 2e-7 at 0.5, 1e-6 at 0.1, 1e-5 at 0.05 against the fp64 oracle)
 _backend = _cabi.Backend()          # tests may swap in a stand-in with the same methods
 _workspaces: dict = {}
 _shapes: dict = {}
@@ -60,6 +63,10 @@ def _device_of(t: torch.Tensor):
     """Context that makes the tensor's GPU current: the library plans, opts kernels in and launches on the
     current device, while the stream is taken from the tensor's device."""
     return torch.cuda.device(t.device) if t.device.type == "cuda" else contextlib.nullcontext()
+
+
+def _fp32_tc_enabled() -> bool:
+    return os.environ.get("NTXENT_FP32_TC", "1").lower() not in ("0", "false", "no", "off")
 
 
 def _env_flag(name: str) -> bool:
@@ -101,15 +108,18 @@ class NTXentFunction(torch.autograd.Function):
             be.peer_fwd(exchange.blocks, n, d, ld, rows_dtype, temperature, keys, rowsum, pos_logit, row_loss,
                         loss_sum, ws, row_scale=rs)
         else:
-            rows = torch.empty((q_rows, ld), dtype=rows_dtype, device=dev)
-            be.l2norm(view0, view1, rows, inv_norm, row_scale=rs)
+            # two-term rows (fp32 values as [hi | lo] bf16 terms) live in a bf16 tensor: name the layout to the library
+            store = _cabi.storage_dtype(rows_dtype)
+            kind = {} if store is rows_dtype else {"rows_dtype": rows_dtype}
+            rows = torch.empty((q_rows, ld), dtype=store, device=dev)
+            be.l2norm(view0, view1, rows, inv_norm, row_scale=rs, **kind)
             if world > 1:
-                keys = torch.empty((world * q_rows, ld), dtype=rows_dtype, device=dev)
+                keys = torch.empty((world * q_rows, ld), dtype=store, device=dev)
                 dist.all_gather_into_tensor(keys, rows, group=group)      # rank-major key buffer
                 q = keys[rank * q_rows:(rank + 1) * q_rows]
             else:
                 keys = q = rows
-            be.fwd(q, keys, d, (n, world, rank, rs), temperature, rowsum, pos_logit, row_loss, loss_sum, ws)
+            be.fwd(q, keys, d, (n, world, rank, rs), temperature, rowsum, pos_logit, row_loss, loss_sum, ws, **kind)
 
         ctx.save_for_backward(view0, view1, keys, stats)
         ctx.meta = (temperature, reduction, group, world, rank, d, exchange, rows_dtype, cat, rs)
@@ -162,8 +172,9 @@ class NTXentFunction(torch.autograd.Function):
             q = keys[rank * q_rows:(rank + 1) * q_rows]
         else:
             rowsum_k, w_k, q = rowsum, w_q, keys
+        kind = {} if _cabi.storage_dtype(rows_dtype) is rows_dtype else {"rows_dtype": rows_dtype}
         be.bwd(q, keys, d, (n, world, rank, rs), temperature, rowsum, rowsum_k, w_q, w_k, w_stride, w_scale,
-               view0, view1, inv_norm, dview0, dview1, ws)
+               view0, view1, inv_norm, dview0, dview1, ws, **kind)
         return grads + (None,) * 8
 
 
@@ -302,20 +313,28 @@ class NT_Xent(torch.nn.Module):
         if self.gather and dist.is_available() and dist.is_initialized():
             group = self.process_group
             world, rank = dist.get_world_size(group), dist.get_rank(group)
-        rows_dtype = self._rows_dtype(view0)
+        peer = world > 1 and self.gather_backend == "peer"
+        rows_dtype = self._rows_dtype(view0, 2 * view0.shape[0] * world, peer)
         with _device_of(view0):
             return NTXentFunction.apply(view0.contiguous(), view1.contiguous(), float(self.temperature),
                                         self.reduction, rows_dtype, group, world, rank,
                                         world > 1 and self.gather_backend == "peer")
 
-    def _rows_dtype(self, x: torch.Tensor) -> torch.dtype:
-        """dtype of the normalised rows: ``compute_dtype``, else the input dtype -- except that bf16 rows wider than
-        the tensor-core kernels' 256 features per tile, or at a temperature below their fixed-shift range, fall back
-        to fp32 rows on the CUDA-core kernels (any D, any temperature > 0), so the module accepts every feature size
-        and temperature the reference does."""
+    def _rows_dtype(self, x: torch.Tensor, keys: int = 0, peer: bool = False):
+        """Layout of the normalised rows: ``compute_dtype``, else the input dtype -- except that
+        * bf16 rows wider than the tensor-core kernels' 256 features per tile, or at a temperature below their
+          fixed-shift range, fall back to fp32 rows on the CUDA-core kernels (any D, any temperature > 0), so the
+          module accepts every feature size and temperature the reference does;
+        * fp32 rows of a large batch (``keys`` >= FP32_TC_MIN_KEYS gathered rows, D <= 128, temperature >=
+          FP32_TC_MIN_TEMPERATURE, no peer exchange) are held as two bf16 terms and go through the tcgen05 kernels
+          (``_cabi.BF16X2``): fp32-grade results, an order of magnitude faster than the CUDA-core kernels at
+          N = 8192.  ``NTXENT_FP32_TC=0`` keeps fp32 on the CUDA cores."""
         dt = self.compute_dtype or x.dtype
         if dt == torch.bfloat16 and (x.shape[1] > 256 or self.temperature < MIN_TC_TEMPERATURE):
             return torch.float32
+        if (dt == torch.float32 and keys >= FP32_TC_MIN_KEYS and x.shape[1] <= 128 and not peer
+                and self.temperature >= FP32_TC_MIN_TEMPERATURE and _fp32_tc_enabled()):
+            return _cabi.BF16X2
         return dt
 
     def forward_cat(self, z: torch.Tensor) -> torch.Tensor:
@@ -339,7 +358,7 @@ class NT_Xent(torch.nn.Module):
         if self.gather and dist.is_available() and dist.is_initialized():
             group = self.process_group
             world, rank = dist.get_world_size(group), dist.get_rank(group)
-        rows_dtype = self._rows_dtype(z)
+        rows_dtype = self._rows_dtype(z, z.shape[0] * world, world > 1 and self.gather_backend == "peer")
         with _device_of(z):
             return NTXentFunction.apply(z.contiguous(), None, float(self.temperature), self.reduction, rows_dtype,
                                         group, world, rank, world > 1 and self.gather_backend == "peer", True)

@@ -37,6 +37,9 @@ def test_row_pitch():
     assert be.row_pitch(128, torch.bfloat16) == 128
     assert be.row_pitch(96, torch.bfloat16) == 128
     assert be.row_pitch(1, torch.bfloat16) == 64
+    # two-term rows (fp32 values as [hi | lo] bf16 terms): twice the bf16 pitch
+    assert be.row_pitch(128, _cabi.BF16X2) == 256
+    assert be.row_pitch(33, _cabi.BF16X2) == 128
 
 
 def owner(T, G, t):
@@ -52,6 +55,8 @@ def owner(T, G, t):
     (66, 66, 20, torch.float32, 148),
     (2, 2, 8, torch.float32, 148),
     (600, 1200, 100, torch.bfloat16, 7),
+    (16384, 16384, 128, _cabi.BF16X2, 148),       # config 4 with fp32 inputs on the tensor cores
+    (300, 600, 40, _cabi.BF16X2, 148),
 ])
 def test_plan_partition_is_exact(q_rows, k_rows, d, dtype, sms):
     p = _cabi.Backend().plan(q_rows, k_rows, d, dtype, sms)
@@ -73,7 +78,9 @@ def test_plan_partition_is_exact(q_rows, k_rows, d, dtype, sms):
     rows_pad = p.row_blocks * p.tile_rows
     assert p.fwd_ws_bytes >= slots * rows_pad * 4 + 16      # + the finalize kernel's ticket and block sums
     assert p.bwd_ws_bytes >= slots * rows_pad * p.d_pad * 4       # + the fold counters of the tensor-core kernel
-    assert p.tensor_cores == (1 if dtype == torch.bfloat16 else 0)
+    assert p.tensor_cores == {torch.bfloat16: 1, _cabi.BF16X2: 2}.get(dtype, 0)
+    if dtype is _cabi.BF16X2:                     # d_pad is the width of one term = of the dZ slots; never symmetric
+        assert p.d_pad == _cabi.Backend().row_pitch(d, dtype) // 2 and p.fwd_symmetric == 0
 
 
 def test_argument_errors_are_reported_without_a_device():
