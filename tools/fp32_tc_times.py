@@ -69,7 +69,7 @@ def run(label, dtype, env):
     got = torch.cat([a.grad, b.grad]).float().cpu().numpy()[sample]
     gerr = np.abs(got - ref["dz"]).max() / np.abs(ref["dz"]).max()
     print(f"{label:46s} {statistics.median(times):9.1f} us/step   gradient error (sampled rows) {gerr:.2e}   "
-          f"loss {float(loss):.6f}")
+          f"loss {float(loss.detach()):.6f}")
 
 
 if __name__ == "__main__":
