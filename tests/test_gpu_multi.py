@@ -63,3 +63,51 @@ def test_sharded_loss_over_nccl(dtype_name, tol, backend, steps):
         sl = slice(k * nl, (k + 1) * nl)
         assert np.abs(out[k]["g0"] / world - c.dview0[sl]).max() < tol * scale
         assert np.abs(out[k]["g1"] / world - c.dview1[sl]).max() < tol * scale
+
+
+def _worker_fp32_tc(rank, world, port, n, d, tau, out):
+    import torch.distributed as dist
+    from simclr_b200 import NT_Xent, _cabi, distributed_utils as du
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    du.init_ddp({"distributed": {"local_rank": rank, "world_size": world, "dist_url": f"tcp://127.0.0.1:{port}"}})
+    dev = torch.device("cuda", rank)
+    g = torch.Generator().manual_seed(21)
+    v0 = torch.randn(n, d, generator=g)
+    v1 = torch.randn(n, d, generator=g) + 0.5 * v0
+    nl = n // world
+    a = v0[rank * nl:(rank + 1) * nl].to(dev).requires_grad_(True)
+    b = v1[rank * nl:(rank + 1) * nl].to(dev).requires_grad_(True)
+    crit = NT_Xent(temperature=tau, reduction="mean", device=rank, gather=True, gather_backend="nccl")
+    picked = crit._rows_dtype(a, 2 * nl * world, False) is _cabi.BF16X2
+    loss = crit(a, b)
+    loss.backward()
+    torch.cuda.synchronize()
+    out[rank] = {"loss": float(loss.detach()), "g0": a.grad.cpu().numpy(), "g1": b.grad.cpu().numpy(), "picked": picked}
+    dist.barrier()
+    du.cleanup()
+
+
+def test_sharded_fp32_inputs_on_tensor_cores_over_nccl():
+    """fp32 inputs, 2048 gathered keys on two ranks: the module holds the rows as two bf16 terms (NTX_BF16X2), the
+    all-gather moves them like any row buffer, and loss and gradients match the fp64 oracle at the fp32 tolerance."""
+    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
+        pytest.skip("needs at least 2 GPUs")
+    from oracle import ntxent_oracle as orc
+    world, n, d, tau = 2, 1024, 96, 0.5
+    g = torch.Generator().manual_seed(21)
+    v0 = torch.randn(n, d, generator=g)
+    v1 = torch.randn(n, d, generator=g) + 0.5 * v0
+    ref = orc.ntxent_rows_fp64(v0.numpy(), v1.numpy(), tau, weights=orc.weights_for("mean", n))
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_worker_fp32_tc, args=(world, _free_port(), n, d, tau, out), nprocs=world, join=True)
+    nl = n // world
+    want = float(ref["loss"].mean())
+    scale = max(np.abs(ref["dview0"]).max(), np.abs(ref["dview1"]).max())
+    for k in range(world):
+        assert out[k]["picked"]
+        sl = slice(k * nl, (k + 1) * nl)
+        # each rank's loss is the mean over ITS rows; its gradient that of the sum over ranks of those means
+        assert abs(out[k]["loss"] - float(ref["loss"][:, sl].mean())) < 1e-5 * want
+        assert np.abs(out[k]["g0"] / world - ref["dview0"][sl]).max() < 1e-5 * scale
+        assert np.abs(out[k]["g1"] / world - ref["dview1"][sl]).max() < 1e-5 * scale
