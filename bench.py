@@ -42,8 +42,8 @@ FALLBACK_TFLOPS = 1590.0          # B200_PROFILING.md fallback when MEASURED_PEA
 PARITY_TOL = 1e-2                 # bf16 mode: 1e-2 relative (BASELINE.json north_star)
 PARITY_GRAD_PAIRS = 256           # sampled pairs per rank: both views' rows -> 512 gradient rows
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE tc_bwd_kernel<2> launch at config 4 on one GPU, from the
-# committed `ncu --set full` capture (profiles/r01b_all_kernels_ncu_full_summary.csv): the keys once, nothing else
-BWD_TRAFFIC_BYTES_C4_1GPU = 4328192
+# committed `ncu --set full` capture (profiles/r02_all_kernels_ncu_full_summary.csv, end of round 2: 4.347 MB read + 2.6 KB written): the keys once, nothing else
+BWD_TRAFFIC_BYTES_C4_1GPU = 4349952
 
 
 def parse():
@@ -639,7 +639,7 @@ def run_ours(args):
                          "achieved": achieved, "peak": peak,
                          "unit": "TFLOP/s", "frac": achieved / peak,
                          "traffic": BWD_TRAFFIC_BYTES_C4_1GPU if (world == 1 and N_GLOBAL == 8192 and DIM == 128) else None,
-                         "traffic_source": "ncu --set full, profiles/r01b_all_kernels_ncu_full_summary.csv (bytes per launch)",
+                         "traffic_source": "ncu --set full, profiles/r02_all_kernels_ncu_full_summary.csv (dram bytes read + written per launch of this kernel, captured once; not measured by this run)",
                          "peak_source": peak_src, "algorithmic_flops_per_launch": bwd_flops,
                          "kernel_ms": bwd_ms,
                          "executed_flops_per_launch": bwd_executed,
