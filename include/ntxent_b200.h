@@ -46,7 +46,7 @@ extern "C" {
  * fp32 batches are large enough for the CUDA-core kernels to matter.  Error against the fp64 oracle, relative to
  * the largest gradient entry: 2e-7 at temperature 0.5, 1e-6 at 0.1, 1e-5 at 0.05 (it grows like 1/temperature; the
  * module uses this layout from temperature 0.1 upwards and the NTX_F32 kernels below).
- * One rank or an all-gathered key buffer; the peer-exchange entry points take NTX_F32 / NTX_BF16 rows only. */
+ * Every entry point that takes a rows dtype accepts it (ntx_bwd_rows excepted), the peer exchange included. */
 #define NTX_BF16X2 2
 
 /* error codes */

@@ -50,6 +50,10 @@ struct ProfScope {
 
 constexpr int kTcMaxD = 256;   // widest padded feature dim the tcgen05 kernels hold in smem
 
+// bytes per stored element of a rows layout (NTX_BF16X2 rows are bf16 elements, twice as many)
+inline size_t esz_of(int dtype) { return dtype == NTX_F32 ? 4 : 2; }
+inline bool rows_dtype_ok(int dtype) { return dtype == NTX_F32 || dtype == NTX_BF16 || dtype == NTX_BF16X2; }
+
 int cached_sm_count(int* out) {
     static int counts[64];
     static bool have[64];
@@ -259,8 +263,8 @@ int ntx_l2norm(const void* view0, const void* view1, int n, int d, int in_dtype,
                       "two-term rows: d=%d must be <= 128 and ld=%d equal to ntx_row_pitch(d, NTX_BF16X2)=%d", d, ld,
                       ntx_row_pitch(d, NTX_BF16X2));
         NTX_CHECK_ARG(reinterpret_cast<uintptr_t>(rows) % 16 == 0, "rows must be 16-byte aligned");
-        return ntx_l2norm_split_launch(view0, view1, n, d, in_dtype, rows, ld, inv_norm, row_scale > 0.f ? row_scale : 1.0f,
-                                       (cudaStream_t)stream);
+        return ntx_l2norm_split_launch(view0, view1, n, d, in_dtype, rows, NtxPeerOut{}, 0, 0, nullptr, ld, inv_norm,
+                                       row_scale > 0.f ? row_scale : 1.0f, (cudaStream_t)stream);
     }
     NTX_CHECK_ARG(ld >= ntx_row_pitch(d, rows_dtype) && ld % (rows_dtype == NTX_BF16 ? 64 : 4) == 0,
                   "ld=%d too small or misaligned for d=%d", ld, d);
@@ -469,7 +473,7 @@ int make_exchange(const NtxPeerBlocks* pb, int q_rows, int ld, int dtype, const 
     }
     ex->out.mc = static_cast<uint8_t*>(pb->multicast);
     if (!step) { ntx_set_error("%s: NULL step word", who); return NTX_E_ARG; }
-    const int esz = dtype == NTX_BF16 ? 2 : 4;
+    const int esz = (int)esz_of(dtype);
     ex->out.world = pb->world;
     ex->out.rank = pb->rank;
     ex->geom = ntx_peer_geom(q_rows, ld, esz, pb->world);
@@ -487,7 +491,7 @@ extern "C" {
 
 size_t ntx_peer_block_bytes(int q_rows, int ld, int rows_dtype, int world) {
     if (q_rows < 1 || ld < 1 || world < 1 || world > NTX_MAX_PEERS) return 0;
-    return ntx_peer_geom(q_rows, ld, rows_dtype == NTX_BF16 ? 2 : 4, world).total;
+    return ntx_peer_geom(q_rows, ld, (int)esz_of(rows_dtype), world).total;
 }
 
 int ntx_peer_l2norm(const void* view0, const void* view1, int n, int d, int in_dtype, const NtxPeerBlocks* blocks,
@@ -495,13 +499,18 @@ int ntx_peer_l2norm(const void* view0, const void* view1, int n, int d, int in_d
     NTX_CHECK_ARG(n >= 1 && d >= 1, "bad sizes n=%d d=%d", n, d);
     NTX_CHECK_ARG(view0 && view1 && inv_norm, "NULL buffer");
     NTX_CHECK_ARG(in_dtype == NTX_F32 || in_dtype == NTX_BF16, "view dtype %d not supported", in_dtype);
-    NTX_CHECK_ARG(rows_dtype == NTX_F32 || rows_dtype == NTX_BF16, "rows dtype %d not supported", rows_dtype);
+    NTX_CHECK_ARG(rows_dtype_ok(rows_dtype), "rows dtype %d not supported", rows_dtype);
+    NTX_CHECK_ARG(rows_dtype != NTX_BF16X2 || d <= 128, "two-term rows support d <= 128 (got %d)", d);
     NTX_CHECK_ARG(ld == ntx_row_pitch(d, rows_dtype), "ld=%d must be ntx_row_pitch(d=%d)=%d", ld, d,
                   ntx_row_pitch(d, rows_dtype));
     Exchange ex;
     int rc = make_exchange(blocks, 2 * n, ld, rows_dtype, step, &ex, "ntx_peer_l2norm");
     if (rc) return rc;
     NTX_CHECK_ARG(row_scale >= 0.f, "row_scale must not be negative");
+    if (rows_dtype == NTX_BF16X2)
+        return ntx_l2norm_split_launch(view0, view1, n, d, in_dtype, nullptr, ex.out, ex.geom.keys_off,
+                                       ex.geom.key_buf_bytes, step, ld, inv_norm, row_scale > 0.f ? row_scale : 1.0f,
+                                       (cudaStream_t)stream);
     return ntx_l2norm_launch(view0, view1, n, d, in_dtype, nullptr, ex.out, ex.geom.keys_off, ex.geom.key_buf_bytes,
                              step, ld, rows_dtype, inv_norm, row_scale > 0.f ? row_scale : 1.0f, (cudaStream_t)stream);
 }
@@ -510,13 +519,13 @@ int ntx_peer_fwd(const NtxPeerBlocks* blocks, int n_local, int d, int ld, int dt
                  float row_scale, int loss_dtype, const uint32_t* step, float* rowsum, float* pos_logit, float* row_loss, float* loss_sum,
                  void* workspace, size_t workspace_bytes, void* stream) {
     NTX_CHECK_ARG(n_local >= 1 && d >= 1, "bad sizes n_local=%d d=%d", n_local, d);
-    NTX_CHECK_ARG(dtype == NTX_F32 || dtype == NTX_BF16, "rows dtype %d not supported", dtype);
+    NTX_CHECK_ARG(rows_dtype_ok(dtype), "rows dtype %d not supported", dtype);
     const int q_rows = 2 * n_local;
     Exchange ex;
     int rc = make_exchange(blocks, q_rows, ld, dtype, step, &ex, "ntx_peer_fwd");
     if (rc) return rc;
     const NtxLayout lay{n_local, blocks->world, blocks->rank, row_scale, loss_dtype};
-    const size_t esz = dtype == NTX_BF16 ? 2 : 4;
+    const size_t esz = esz_of(dtype);
     const uint8_t* keys = ex.out.base[blocks->rank] + ex.geom.keys_off;            // key buffer 0 of this rank's block
     const uint8_t* q = keys + (size_t)blocks->rank * q_rows * ld * esz;
     return fwd_impl(q, keys, q_rows, q_rows * blocks->world, d, ld, dtype, &lay, temperature, rowsum, pos_logit, row_loss,
@@ -526,7 +535,7 @@ int ntx_peer_fwd(const NtxPeerBlocks* blocks, int n_local, int d, int ld, int dt
 int ntx_peer_post_weights(const NtxPeerBlocks* blocks, int n_local, int ld, int dtype, const uint32_t* step,
                           const void* w, int w_stride, int w_dtype, void* stream) {
     NTX_CHECK_ARG(n_local >= 1, "bad size n_local=%d", n_local);
-    NTX_CHECK_ARG(dtype == NTX_F32 || dtype == NTX_BF16, "rows dtype %d not supported", dtype);
+    NTX_CHECK_ARG(rows_dtype_ok(dtype), "rows dtype %d not supported", dtype);
     NTX_CHECK_ARG(w != nullptr, "NULL row weights");
     NTX_CHECK_ARG(w_stride == 0 || w_stride == 1, "w_stride must be 0 (one weight) or 1 (one per row)");
     NTX_CHECK_ARG(w_dtype == NTX_F32 || w_dtype == NTX_BF16, "weight dtype %d not supported", w_dtype);
@@ -543,13 +552,13 @@ int ntx_peer_bwd(const NtxPeerBlocks* blocks, int n_local, int d, int ld, int dt
                  size_t workspace_bytes, void* stream) {
     NTX_CHECK_ARG(n_local >= 1 && d >= 1, "bad sizes n_local=%d d=%d", n_local, d);
     NTX_CHECK_ARG(w_stride == 0 || w_stride == 1, "w_stride must be 0 (one weight) or 1 (one per row)");
-    NTX_CHECK_ARG(dtype == NTX_F32 || dtype == NTX_BF16, "rows dtype %d not supported", dtype);
+    NTX_CHECK_ARG(rows_dtype_ok(dtype), "rows dtype %d not supported", dtype);
     const int q_rows = 2 * n_local;
     Exchange ex;
     int rc = make_exchange(blocks, q_rows, ld, dtype, step, &ex, "ntx_peer_bwd");
     if (rc) return rc;
     const NtxLayout lay{n_local, blocks->world, blocks->rank, row_scale, NTX_F32};
-    const size_t esz = dtype == NTX_BF16 ? 2 : 4;
+    const size_t esz = esz_of(dtype);
     const uint8_t* own = ex.out.base[blocks->rank];
     const uint8_t* keys = own + ex.geom.keys_off;
     const uint8_t* q = keys + (size_t)blocks->rank * q_rows * ld * esz;
@@ -579,7 +588,7 @@ int ntx_bwd_rows(const void* q, const void* k, int q_rows, int k_rows, int d, in
                  void* dz, void* workspace, size_t workspace_bytes, void* stream) {
     NTX_CHECK_ARG(q != nullptr && dz != nullptr && layout != nullptr, "NULL buffer");
     NTX_CHECK_ARG(dtype == NTX_F32 || dtype == NTX_BF16, "rows dtype %d not supported", dtype);
-    const size_t esz = dtype == NTX_BF16 ? 2 : 4;
+    const size_t esz = esz_of(dtype);
     const int n = layout->n_local;
     // the normalised rows of this rank stand in for the views: rows [0, n) and [n, 2n), pitch ld
     const char* qb = static_cast<const char*>(q);

@@ -365,7 +365,8 @@ int ntx_l2norm_launch(const void* v0, const void* v1, int n, int d, int in_dtype
                       size_t keys_off, size_t key_buf_bytes, uint32_t* step_out, int ld, int rows_dtype,
                       float* inv_norm, float row_scale, cudaStream_t st);
 // NTX_BF16X2 rows: [hi | lo] bf16 terms of the fp32 normalised row (ntx_l2norm.cu)
-int ntx_l2norm_split_launch(const void* v0, const void* v1, int n, int d, int in_dtype, void* rows, int ld,
+int ntx_l2norm_split_launch(const void* v0, const void* v1, int n, int d, int in_dtype, void* rows,
+                            const NtxPeerOut& peers, size_t keys_off, size_t key_buf_bytes, uint32_t* step_out, int ld,
                             float* inv_norm, float row_scale, cudaStream_t st);
 int ntx_post_weights_launch(const void* w, int w_stride, int w_bf16, int q_rows, const NtxPeerOut& peers, size_t weight_off,
                             const uint32_t* step, cudaStream_t st);

@@ -221,50 +221,94 @@ post_weights_kernel(const float* __restrict__ w, int w_stride, int w_bf16, int q
 
 
 // NTX_BF16X2 rows: the fp32 normalised (and scaled) row x as two bf16 terms, hi = bf16(x) in columns [0, dh) and
-// lo = bf16(x - hi) in [dh, 2 dh), zero padded from d to dh.  One warp per row, two columns per lane and pass.
+// lo = bf16(x - hi) in [dh, 2 dh), zero padded from d to dh.  One warp per row, four columns (8 bytes of each term)
+// per lane and pass.  Peer mode as in l2norm_kernel: the row goes into the step's key buffer of every rank's block.
 template <typename TIn>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 l2norm_split_kernel(const TIn* __restrict__ view0, const TIn* __restrict__ view1, int n, int d,
-                    __nv_bfloat16* __restrict__ rows, int dh, float* __restrict__ inv_norm, float row_scale) {
+                    __nv_bfloat16* __restrict__ rows_local, NtxPeerOut peers, size_t keys_off, size_t key_buf_bytes,
+                    uint32_t* __restrict__ step_out, int dh, float* __restrict__ inv_norm, float row_scale) {
     ntx_dep_trigger();
     ntx_dep_wait();
     const int lane = threadIdx.x & 31;
     const int r = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
-    if (r >= 2 * n) return;                                   // whole warps leave together
-    const TIn* src = (r < n) ? view0 + (size_t)r * d : view1 + (size_t)(r - n) * d;
-    float ss = 0.f;
-    for (int c = lane; c < d; c += 32) {
-        const float v = to_f32(src[c]);
-        ss = fmaf(v, v, ss);
+    const int ndst = peers.world > 0 ? peers.world : 1;
+    uint32_t* ctl = nullptr;
+    uint32_t step = 0;
+    size_t dst_off = (size_t)r * 2 * dh;                      // elements, same place in every destination
+    size_t dst_bytes = 0;
+    if (peers.world > 0) {
+        ctl = reinterpret_cast<uint32_t*>(peers.base[peers.rank]);
+        step = ctl[NTX_CTL_STEP] + 1;                         // see l2norm_kernel
+        dst_off += (size_t)peers.rank * 2 * n * 2 * dh;
+        dst_bytes = keys_off + (step & 1u) * key_buf_bytes;
     }
+    if (r < 2 * n) {                                          // whole warps share a row
+        const TIn* src = (r < n) ? view0 + (size_t)r * d : view1 + (size_t)(r - n) * d;
+        float ss = 0.f;
+        for (int c = lane; c < d; c += 32) {
+            const float v = to_f32(src[c]);
+            ss = fmaf(v, v, ss);
+        }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
-    const float denom = fmaxf(sqrtf(ss), 1e-12f);             // clamp_min(eps) of F.normalize
-    if (lane == 0) inv_norm[r] = 1.0f / denom;
-    __nv_bfloat16* dst = rows + (size_t)r * 2 * dh;
-    for (int c = 2 * lane; c < dh; c += 64) {
-        const float x0 = c < d ? to_f32(src[c]) / denom * row_scale : 0.f;
-        const float x1 = c + 1 < d ? to_f32(src[c + 1]) / denom * row_scale : 0.f;
-        const __nv_bfloat162 hi = __floats2bfloat162_rn(x0, x1);
-        const float2 hf = __bfloat1622float2(hi);
-        const __nv_bfloat162 lo = __floats2bfloat162_rn(x0 - hf.x, x1 - hf.y);     // the differences are exact in fp32
-        *reinterpret_cast<__nv_bfloat162*>(dst + c) = hi;
-        *reinterpret_cast<__nv_bfloat162*>(dst + dh + c) = lo;
+        for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+        const float denom = fmaxf(sqrtf(ss), 1e-12f);         // clamp_min(eps) of F.normalize
+        if (lane == 0) inv_norm[r] = 1.0f / denom;
+        for (int c = 4 * lane; c < dh; c += 128) {
+            float x[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) x[j] = c + j < d ? to_f32(src[c + j]) / denom * row_scale : 0.f;
+            __nv_bfloat162 hi[2], lo[2];
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                hi[j] = __floats2bfloat162_rn(x[2 * j], x[2 * j + 1]);
+                const float2 hf = __bfloat1622float2(hi[j]);
+                lo[j] = __floats2bfloat162_rn(x[2 * j] - hf.x, x[2 * j + 1] - hf.y);   // the differences are exact in fp32
+            }
+            const uint2 hv = *reinterpret_cast<const uint2*>(hi), lv = *reinterpret_cast<const uint2*>(lo);
+            if (peers.world > 0 && peers.mc) {                // one multicast store per 8 bytes instead of one per rank
+                const size_t at = dst_bytes + (dst_off + c) * sizeof(__nv_bfloat16);
+                ntx_mc_st_8B(peers.mc, at, hv);
+                ntx_mc_st_8B(peers.mc, at + (size_t)dh * sizeof(__nv_bfloat16), lv);
+            } else {
+                for (int p = 0; p < ndst; ++p) {
+                    __nv_bfloat16* dst = (peers.world > 0 ? reinterpret_cast<__nv_bfloat16*>(peers.base[p] + dst_bytes)
+                                                          : rows_local) + dst_off;
+                    *reinterpret_cast<uint2*>(dst + c) = hv;
+                    *reinterpret_cast<uint2*>(dst + dh + c) = lv;
+                }
+            }
+        }
+    }
+    if (peers.world > 0) {
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();                                  // the CTA's stores (barrier above) before its ticket
+            if (atomicAdd(ctl + NTX_CTL_TICKET, 1u) == gridDim.x - 1) {
+                __threadfence();
+                ctl[NTX_CTL_TICKET] = 0;
+                ctl[NTX_CTL_STEP] = step;
+                *step_out = step;
+                ntx_raise_flags(peers, NTX_CTL_KFLAG, step);
+            }
+        }
     }
 }
 
 }  // namespace
 
-int ntx_l2norm_split_launch(const void* v0, const void* v1, int n, int d, int in_dtype, void* rows, int ld,
+int ntx_l2norm_split_launch(const void* v0, const void* v1, int n, int d, int in_dtype, void* rows,
+                            const NtxPeerOut& peers, size_t keys_off, size_t key_buf_bytes, uint32_t* step_out, int ld,
                             float* inv_norm, float row_scale, cudaStream_t st) {
     const int grid = (2 * n + kWarpsPerBlock - 1) / kWarpsPerBlock;
     if (in_dtype == NTX_F32)
         NTX_CUDA(ntx_launch_dep(l2norm_split_kernel<float>, grid, kWarpsPerBlock * 32, 0, st, (const float*)v0,
-                                (const float*)v1, n, d, (__nv_bfloat16*)rows, ld / 2, inv_norm, row_scale));
+                                (const float*)v1, n, d, (__nv_bfloat16*)rows, peers, keys_off, key_buf_bytes, step_out,
+                                ld / 2, inv_norm, row_scale));
     else
         NTX_CUDA(ntx_launch_dep(l2norm_split_kernel<__nv_bfloat16>, grid, kWarpsPerBlock * 32, 0, st,
-                                (const __nv_bfloat16*)v0, (const __nv_bfloat16*)v1, n, d, (__nv_bfloat16*)rows, ld / 2,
-                                inv_norm, row_scale));
+                                (const __nv_bfloat16*)v0, (const __nv_bfloat16*)v1, n, d, (__nv_bfloat16*)rows, peers,
+                                keys_off, key_buf_bytes, step_out, ld / 2, inv_norm, row_scale));
     return NTX_OK;
 }
 

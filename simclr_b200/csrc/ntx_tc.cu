@@ -1497,11 +1497,14 @@ int launch_bwd(const RowMaps& m, const NtxDims& dm, const NtxPlan& plan, const B
     return gate.step ? launch_bwd_gs<NDB, true, false>(m, dm, plan, wt, partial, gate, fuse, st)
                      : launch_bwd_gs<NDB, false, false>(m, dm, plan, wt, partial, gate, fuse, st);
 }
-// two-term rows (NTX_BF16X2): one rank or an all-gathered key buffer, no peer gate
+// two-term rows (NTX_BF16X2)
 template <int NDB>
 int launch_bwd_split(const RowMaps& m, const NtxDims& dm, const NtxPlan& plan, const BwdWeights& wt, float* partial,
                      const NtxGate& gate, const BwdFuse& fuse, cudaStream_t st) {
-    return dm.scaled ? launch_bwd_gs<NDB, false, true, true>(m, dm, plan, wt, partial, gate, fuse, st)
+    if (dm.scaled)
+        return gate.step ? launch_bwd_gs<NDB, true, true, true>(m, dm, plan, wt, partial, gate, fuse, st)
+                         : launch_bwd_gs<NDB, false, true, true>(m, dm, plan, wt, partial, gate, fuse, st);
+    return gate.step ? launch_bwd_gs<NDB, true, false, true>(m, dm, plan, wt, partial, gate, fuse, st)
                      : launch_bwd_gs<NDB, false, false, true>(m, dm, plan, wt, partial, gate, fuse, st);
 }
 
@@ -1525,10 +1528,6 @@ int ntx_tc_fwd_launch(const __nv_bfloat16* q, const __nv_bfloat16* k, const NtxD
     int rc = make_row_maps(&m, q, k, dm, gate, key_buf_elems);
     if (rc) return rc;
     if (dm.split) {                     // tiles of [hi | lo] terms: plan.d_pad is the width of one term
-        if (gate.step) {
-            ntx_set_error("two-term rows are not built for the peer exchange");
-            return NTX_E_UNSUPPORTED;
-        }
         if (plan.d_pad == 64) return launch_fwd<2, true>(m, dm, plan, partial, fold, out, gate, st);
         if (plan.d_pad == 128) return launch_fwd<4, true>(m, dm, plan, partial, fold, out, gate, st);
         ntx_set_error("tensor-core forward on two-term rows: padded feature dim %d not built", plan.d_pad);
@@ -1582,10 +1581,6 @@ int ntx_tc_bwd_launch(const __nv_bfloat16* q, const __nv_bfloat16* k, const NtxD
     const BwdFuse fuse{o.view0, o.view1, o.dview0, o.dview1, o.inv_norm, o.tag, o.done_total, o.arrive, o.row_blocks,
                        o.in_ld, o.normalised, o.in_bf16, dm.d, o.enabled};
     if (dm.split) {
-        if (gate.step) {
-            ntx_set_error("two-term rows are not built for the peer exchange");
-            return NTX_E_UNSUPPORTED;
-        }
         if (plan.d_pad == 64) return launch_bwd_split<2>(m, dm, plan, wt, partial, gate, fuse, st);
         if (plan.d_pad == 128) return launch_bwd_split<4>(m, dm, plan, wt, partial, gate, fuse, st);
         ntx_set_error("tensor-core backward on two-term rows: padded feature dim %d not built", plan.d_pad);

@@ -313,26 +313,25 @@ class NT_Xent(torch.nn.Module):
         if self.gather and dist.is_available() and dist.is_initialized():
             group = self.process_group
             world, rank = dist.get_world_size(group), dist.get_rank(group)
-        peer = world > 1 and self.gather_backend == "peer"
-        rows_dtype = self._rows_dtype(view0, 2 * view0.shape[0] * world, peer)
+        rows_dtype = self._rows_dtype(view0, 2 * view0.shape[0] * world)
         with _device_of(view0):
             return NTXentFunction.apply(view0.contiguous(), view1.contiguous(), float(self.temperature),
                                         self.reduction, rows_dtype, group, world, rank,
                                         world > 1 and self.gather_backend == "peer")
 
-    def _rows_dtype(self, x: torch.Tensor, keys: int = 0, peer: bool = False):
+    def _rows_dtype(self, x: torch.Tensor, keys: int = 0):
         """Layout of the normalised rows: ``compute_dtype``, else the input dtype -- except that
         * bf16 rows wider than the tensor-core kernels' 256 features per tile, or at a temperature below their
           fixed-shift range, fall back to fp32 rows on the CUDA-core kernels (any D, any temperature > 0), so the
           module accepts every feature size and temperature the reference does;
         * fp32 rows of a large batch (``keys`` >= FP32_TC_MIN_KEYS gathered rows, D <= 128, temperature >=
-          FP32_TC_MIN_TEMPERATURE, no peer exchange) are held as two bf16 terms and go through the tcgen05 kernels
+          FP32_TC_MIN_TEMPERATURE; either gather back end) are held as two bf16 terms and go through the tcgen05 kernels
           (``_cabi.BF16X2``): fp32-grade results, an order of magnitude faster than the CUDA-core kernels at
           N = 8192.  ``NTXENT_FP32_TC=0`` keeps fp32 on the CUDA cores."""
         dt = self.compute_dtype or x.dtype
         if dt == torch.bfloat16 and (x.shape[1] > 256 or self.temperature < MIN_TC_TEMPERATURE):
             return torch.float32
-        if (dt == torch.float32 and keys >= FP32_TC_MIN_KEYS and x.shape[1] <= 128 and not peer
+        if (dt == torch.float32 and keys >= FP32_TC_MIN_KEYS and x.shape[1] <= 128
                 and self.temperature >= FP32_TC_MIN_TEMPERATURE and _fp32_tc_enabled()):
             return _cabi.BF16X2
         return dt
@@ -358,7 +357,7 @@ class NT_Xent(torch.nn.Module):
         if self.gather and dist.is_available() and dist.is_initialized():
             group = self.process_group
             world, rank = dist.get_world_size(group), dist.get_rank(group)
-        rows_dtype = self._rows_dtype(z, z.shape[0] * world, world > 1 and self.gather_backend == "peer")
+        rows_dtype = self._rows_dtype(z, z.shape[0] * world)
         with _device_of(z):
             return NTXentFunction.apply(z.contiguous(), None, float(self.temperature), self.reduction, rows_dtype,
                                         group, world, rank, world > 1 and self.gather_backend == "peer", True)

@@ -118,7 +118,6 @@ def test_module_uses_two_term_rows_for_large_fp32_batches(dev, monkeypatch):
     crit = NT_Xent(tau)
     assert crit._rows_dtype(a, 2 * n) is _cabi.BF16X2
     assert crit._rows_dtype(a[:100], 200) is torch.float32
-    assert crit._rows_dtype(a, 2 * n, peer=True) is torch.float32
     assert NT_Xent(0.05)._rows_dtype(a, 2 * n) is torch.float32
     assert NT_Xent(tau, compute_dtype=torch.bfloat16)._rows_dtype(a, 2 * n) is torch.bfloat16
     out = {}
@@ -149,7 +148,7 @@ def test_module_uses_two_term_rows_for_large_fp32_batches(dev, monkeypatch):
 
 
 def test_two_term_rows_refusals(dev):
-    """D > 128, the peer entry points and temperatures below the tensor-core floor are refused with a message."""
+    """D > 128 and temperatures below the tensor-core floor are refused with a message."""
     from simclr_b200 import _cabi
     be = _cabi.Backend()
     with pytest.raises(RuntimeError, match="128"):
@@ -164,3 +163,35 @@ def test_two_term_rows_refusals(dev):
     with pytest.raises(RuntimeError, match="temperature"):
         be.fwd(rows, rows, 32, (64, 1, 0, 1.0), 0.01, st[1], st[2], st[3], torch.empty(2, device=dev), ws,
                rows_dtype=_cabi.BF16X2)
+
+
+def test_fp32_inputs_at_config4_size_against_sampled_oracle(dev):
+    """BASELINE configs[3] size (N = 8192 pairs, D = 128) with fp32 inputs: the module takes the two-term tensor-core
+    path; every row's loss and the gradient of 1024 sampled rows under non-uniform row weights against the fp64
+    oracle at the fp32 tolerance, plus size-independent properties: swapping the views swaps the halves of the
+    result, and the gradient is orthogonal to its input row (the loss does not depend on the rows' norms)."""
+    from simclr_b200 import NT_Xent, _cabi
+    n, d, tau = 8192, 128, 0.5
+    g = torch.Generator().manual_seed(17)
+    a = torch.randn(n, d, generator=g)
+    b = torch.randn(n, d, generator=g) + 0.25 * a
+    i = torch.arange(2 * n, dtype=torch.float64).reshape(2, n)
+    w = (0.5 + ((i * 7919) % 1000) / 1000.0).float()                        # non-uniform upstream gradient
+    rng = np.random.default_rng(5)
+    pairs = np.sort(rng.choice(n, size=512, replace=False))
+    rows = np.concatenate([pairs, n + pairs])
+    ref = orc.ntxent_sampled_fp64(a.numpy(), b.numpy(), tau, w.double().numpy(), rows)
+    crit = NT_Xent(tau, "none")
+    assert crit._rows_dtype(a, 2 * n) is _cabi.BF16X2
+    ta, tb = a.to(dev).requires_grad_(True), b.to(dev).requires_grad_(True)
+    out = crit(ta, tb)
+    out.backward(w.to(dev))
+    assert rel_err(out.detach().cpu().numpy(), ref["loss"]) < FP32_TOL
+    got = np.concatenate([ta.grad[pairs].cpu().numpy(), tb.grad[pairs].cpu().numpy()])
+    assert np.abs(got - ref["dz"]).max() / np.abs(ref["dz"]).max() < FP32_TOL
+    # views swapped: the (2, N) losses swap their halves (the tiles and slots every row goes through change)
+    swapped = crit(tb.detach(), ta.detach())
+    assert torch.allclose(swapped[0], out[1].detach(), rtol=0, atol=2e-5) and torch.allclose(swapped[1], out[0].detach(), rtol=0, atol=2e-5)
+    # d loss / d z_r is orthogonal to z_r
+    dots = (ta.grad * ta.detach()).sum(1).abs().max() / (ta.grad.norm(dim=1) * ta.detach().norm(dim=1)).max()
+    assert float(dots) < 1e-4

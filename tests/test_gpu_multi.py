@@ -65,7 +65,7 @@ def test_sharded_loss_over_nccl(dtype_name, tol, backend, steps):
         assert np.abs(out[k]["g1"] / world - c.dview1[sl]).max() < tol * scale
 
 
-def _worker_fp32_tc(rank, world, port, n, d, tau, out):
+def _worker_fp32_tc(rank, world, port, n, d, tau, out, backend="nccl", steps=1):
     import torch.distributed as dist
     from simclr_b200 import NT_Xent, _cabi, distributed_utils as du
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
@@ -77,19 +77,23 @@ def _worker_fp32_tc(rank, world, port, n, d, tau, out):
     nl = n // world
     a = v0[rank * nl:(rank + 1) * nl].to(dev).requires_grad_(True)
     b = v1[rank * nl:(rank + 1) * nl].to(dev).requires_grad_(True)
-    crit = NT_Xent(temperature=tau, reduction="mean", device=rank, gather=True, gather_backend="nccl")
-    picked = crit._rows_dtype(a, 2 * nl * world, False) is _cabi.BF16X2
-    loss = crit(a, b)
-    loss.backward()
+    crit = NT_Xent(temperature=tau, reduction="mean", device=rank, gather=True, gather_backend=backend)
+    picked = crit._rows_dtype(a, 2 * nl * world) is _cabi.BF16X2
+    for _ in range(steps):
+        a.grad = b.grad = None
+        loss = crit(a, b)
+        loss.backward()
     torch.cuda.synchronize()
     out[rank] = {"loss": float(loss.detach()), "g0": a.grad.cpu().numpy(), "g1": b.grad.cpu().numpy(), "picked": picked}
     dist.barrier()
     du.cleanup()
 
 
-def test_sharded_fp32_inputs_on_tensor_cores_over_nccl():
+@pytest.mark.parametrize("backend,steps", [("nccl", 1), ("peer", 3)])
+def test_sharded_fp32_inputs_on_tensor_cores(backend, steps):
     """fp32 inputs, 2048 gathered keys on two ranks: the module holds the rows as two bf16 terms (NTX_BF16X2), the
-    all-gather moves them like any row buffer, and loss and gradients match the fp64 oracle at the fp32 tolerance."""
+    all-gather or the kernels' peer-memory stores move them like any row buffer, and loss and gradients match the
+    fp64 oracle at the fp32 tolerance."""
     if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
         pytest.skip("needs at least 2 GPUs")
     from oracle import ntxent_oracle as orc
@@ -100,7 +104,7 @@ def test_sharded_fp32_inputs_on_tensor_cores_over_nccl():
     ref = orc.ntxent_rows_fp64(v0.numpy(), v1.numpy(), tau, weights=orc.weights_for("mean", n))
     mgr = mp.Manager()
     out = mgr.dict()
-    mp.spawn(_worker_fp32_tc, args=(world, _free_port(), n, d, tau, out), nprocs=world, join=True)
+    mp.spawn(_worker_fp32_tc, args=(world, _free_port(), n, d, tau, out, backend, steps), nprocs=world, join=True)
     nl = n // world
     want = float(ref["loss"].mean())
     scale = max(np.abs(ref["dview0"]).max(), np.abs(ref["dview1"]).max())

@@ -474,7 +474,7 @@ def test_symmetric_forward_matches_full_tile_forward_and_oracle(n, d, tau, dev):
     assert abs(sym_sum[1] - ref["loss"].mean()) < BF16_TOL * abs(ref["loss"].mean())
 
 
-@pytest.mark.parametrize("dtype,tol", [(torch.float32, FP32_TOL), (torch.bfloat16, BF16_TOL)])
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, FP32_TOL), (torch.bfloat16, BF16_TOL), ("bf16x2", FP32_TOL)])
 @pytest.mark.parametrize("world", [2, 4])
 def test_peer_exchange_entry_points_on_one_gpu(world, dtype, tol, dev):
     """ntx_peer_l2norm / ntx_peer_fwd / ntx_peer_bwd through the C ABI with `world` exchange blocks of this one GPU
@@ -484,6 +484,8 @@ def test_peer_exchange_entry_points_on_one_gpu(world, dtype, tol, dev):
     from conftest import GOLDEN
     from simclr_b200 import _cabi
     be = _cabi.Backend()
+    if dtype == "bf16x2":                 # fp32 inputs, rows exchanged as two bf16 terms (tensor cores, fp32 tolerance)
+        dtype = _cabi.BF16X2
     c = next(g for g in GOLDEN if g.name == f"shard_w{world}")
     nl, d = c.n // world, c.d
     q_rows = 2 * nl
