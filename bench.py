@@ -635,7 +635,7 @@ def run_ours(args):
             "gpu_launches_how": f"{kernels_per_step} kernels of libntxent_b200.so per step (counted by the library while "
                                 "the step was captured / launched: ntx_launch_count) x timed steps",
             "parity": parity,
-            "roofline": {"bound": "tensor", "kernel": f"tc_bwd_kernel<{DIM // 64}, false, true>",
+            "roofline": {"bound": "tensor", "kernel": f"tc_bwd_kernel<{DIM // 64}, {'true' if world > 1 and GATHER_BACKEND == 'peer' else 'false'}, true, false>",
                          "achieved": achieved, "peak": peak,
                          "unit": "TFLOP/s", "frac": achieved / peak,
                          "traffic": BWD_TRAFFIC_BYTES_C4_1GPU if (world == 1 and N_GLOBAL == 8192 and DIM == 128) else None,
@@ -647,7 +647,8 @@ def run_ours(args):
                          "peak_sustained": peak_sustained,
                          "executed_frac_of_sustained": (bwd_executed / (bwd_ms * 1e-3) / 1e12 / peak_sustained
                                                         if peak_sustained else None),
-                         "fwd_kernel": {"kernel": ("tc_fwd_sym_kernel" if world == 1 and DIM <= 128 else "tc_fwd_kernel") + f"<{DIM // 64}, true>", "kernel_ms": fwd_ms,
+                         "fwd_kernel": {"kernel": (f"tc_fwd_sym_kernel<{DIM // 64}, true>" if world == 1 and DIM <= 128
+                                                   else f"tc_fwd_kernel<{DIM // 64}, true, false>"), "kernel_ms": fwd_ms,
                                         "achieved": fwd_flops / (fwd_ms * 1e-3) / 1e12},
                          "whole_step_frac": 18.0 * N_GLOBAL * N_GLOBAL * DIM / world / (ms_per_step * 1e-3) / 1e12 / peak},
             "clocks": clocks.summary(),
