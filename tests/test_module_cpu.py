@@ -52,3 +52,27 @@ def test_shape_and_dtype_errors():
 def test_no_cpu_fallback():
     with pytest.raises(RuntimeError, match="no CPU path"):
         NT_Xent(0.5)(torch.randn(4, 8), torch.randn(4, 8))
+
+
+def test_rows_layout_choice(monkeypatch):
+    """Which rows the module asks the library for (pure host logic): the input dtype, except bf16 outside the
+    tensor-core kernels' range -> fp32 rows, and large fp32 batches at temperature >= 0.1 -> two-term rows."""
+    import torch
+    from simclr_b200 import NT_Xent, _cabi
+    from simclr_b200 import loss as loss_mod
+    monkeypatch.delenv("NTXENT_FP32_TC", raising=False)
+    monkeypatch.delenv("NTXENT_COMPUTE_DTYPE", raising=False)
+    f32, bf16 = torch.empty(4, 128), torch.empty(4, 128, dtype=torch.bfloat16)
+    big = loss_mod.FP32_TC_MIN_KEYS
+    assert NT_Xent(0.5)._rows_dtype(f32, big) is _cabi.BF16X2
+    assert NT_Xent(0.5)._rows_dtype(f32, big - 2) is torch.float32            # small batch: CUDA-core kernels
+    assert NT_Xent(0.09)._rows_dtype(f32, big) is torch.float32               # rounding grows like 1 / temperature
+    assert NT_Xent(0.5)._rows_dtype(torch.empty(4, 129), big) is torch.float32    # one term must fit a 128-wide tile
+    assert NT_Xent(0.5)._rows_dtype(bf16, big) is torch.bfloat16
+    assert NT_Xent(0.5, compute_dtype=torch.bfloat16)._rows_dtype(f32, big) is torch.bfloat16
+    assert NT_Xent(0.5, compute_dtype=torch.float32)._rows_dtype(bf16, big) is _cabi.BF16X2
+    assert NT_Xent(0.5)._rows_dtype(torch.empty(4, 300, dtype=torch.bfloat16), big) is torch.float32
+    assert NT_Xent(0.02)._rows_dtype(bf16, big) is torch.float32
+    monkeypatch.setenv("NTXENT_FP32_TC", "0")
+    assert NT_Xent(0.5)._rows_dtype(f32, big) is torch.float32
+    assert _cabi.storage_dtype(_cabi.BF16X2) is torch.bfloat16 and _cabi.storage_dtype(torch.float32) is torch.float32
