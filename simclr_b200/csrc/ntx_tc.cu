@@ -23,7 +23,7 @@
 
 #ifdef NTX_TIMING
 // bring-up only: per-CTA cycle counters (fwd: slots 0-7, bwd: slots 8-15), read by ntx_debug_timers()
-__device__ long long g_ntx_timers[148][16];
+__device__ long long g_ntx_timers[148][24];   // 16..23: NTX_TIMELINE points (cycles from kernel entry)
 #define NTX_T(var) long long var = 0
 #define NTX_TIC(var) const long long var##_t0 = clock64()
 #define NTX_TOC(var) var += clock64() - var##_t0
@@ -274,6 +274,9 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
               const __grid_constant__ CUtensorMap tmap_q1, const __grid_constant__ CUtensorMap tmap_k1,
               NtxDims dm, int key_tiles, long long T, int rows_pad, float* __restrict__ partial,
               NtxFoldScratch fold, NtxFwdOut out, NtxGate gate) {
+#ifdef NTX_TIMELINE
+    const long long t_entry = clock64();
+#endif
     constexpr int NS = FwdCfg<NDB>::NS;
     constexpr uint32_t kTileBytes = NDB * kBlkBytes;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -314,6 +317,9 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     constexpr uint32_t tmem_base = 0;
     // everything above overlapped the tail of the previous kernel on the stream; from here on its results are read
     ntx_dep_wait();
+#ifdef NTX_TIMELINE
+    if (threadIdx.x == 0) g_ntx_timers[blockIdx.x % 148][20] = clock64() - t_entry;
+#endif
 
     if (warp == kProducerWarp) {
         if (elect_one()) {
@@ -422,11 +428,16 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
             const bool last_of_seg = (i + 1 == n_tiles) || (kt + 1 == key_tiles);
             if (turn == g) {
                 { NTX_TIC(te_wait); mbar_wait(&ctl->s_full[g], own & 1); NTX_TOC(te_wait); }
+#ifdef NTX_TIMELINE
+                if (own == 0 && threadIdx.x == 0) g_ntx_timers[blockIdx.x % 148][21] = clock64() - t_entry;
+#endif
                 ++own;
                 tc_fence_after();
-                // tiles that hold a positive column go through the masked path too: the positive logit of a row
-                // is taken from the similarity tile itself (the same MMA value its exponential uses)
-                const bool has_pos = positive_tile(rb, kt, dm);
+                // folded finalize only: tiles that hold a positive column go through the masked path too, the positive
+                // logit of a row is taken from the similarity tile itself (the same MMA value its exponential uses).
+                // Otherwise the finalize kernel computes it, and the slow path is kept to the self / ragged tiles
+                // (one of 8 ranks: a second masked tile among a CTA's 14 made the slowest CTA 47 % longer than the mean)
+                const bool has_pos = fold.enabled && positive_tile(rb, kt, dm);
                 const bool edge = edge_tile(rb, kt, dm) || has_pos;
                 const int self = ntx_self_col(rb * 128 + row_in_tile, dm.n_local, dm.rank);
                 const int my_row = rb * 128 + row_in_tile;
@@ -444,7 +455,15 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
                         __syncwarp();
                         if (lane == 0) mbar_arrive(&ctl->s_empty[g]);
                     }
-                    if (!edge) {
+                    // the masked form only for the 32-key chunks that hold a self (or, folded, a positive) column
+                    // of this warp's rows or run past the last key: warp-uniform
+                    bool masked = edge;
+                    if (edge) {
+                        const int c0 = kt * 128 + ch * 32;
+                        const bool mine = (self >= c0 && self < c0 + 32) || (has_pos && my_pos >= c0 && my_pos < c0 + 32);
+                        masked = c0 + 32 > dm.k_rows || __any_sync(0xffffffffu, mine);
+                    }
+                    if (!masked) {
                         // two logits per instruction: x = s * c1 - c1 (FFMA2), exp2 on MUFU or by the
                         // polynomial for NTX_FWD_POLY of every 4 pairs, row sums by FADD2
 #pragma unroll
@@ -473,6 +492,9 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         }
         NTX_TOC(te_total);
         if (threadIdx.x == 0) { NTX_TSAVE(4, te_total); NTX_TSAVE(5, te_wait); }
+#ifdef NTX_TIMELINE
+        if (threadIdx.x == 0) g_ntx_timers[blockIdx.x % 148][22] = clock64() - t_entry;
+#endif
 
         // ---------------------------------------------------------------- finish: this CTA's share of its row blocks
         // (loss.py:54-65: logsumexp - positive per row, then the reduction).  Group 0, one thread per row.
@@ -1054,8 +1076,13 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         __trap();
     }
     constexpr uint32_t tmem_base = 0;
-    // everything above overlapped the tail of the previous kernel on the stream; from here on its results are read
+    // everything above overlapped the tail of the previous kernel on the stream; from here on its results are read.
+    // (Measured and dropped: with a peer exchange the key tiles are ordered by the exchange's flag words, so the
+    // producer and the MMA warps could fill the pipeline before this wait; on two GPUs the step did not get shorter.)
     ntx_dep_wait();
+#ifdef NTX_TIMELINE
+    if (threadIdx.x == 0) g_ntx_timers[blockIdx.x % 148][16] = clock64() - t_entry;
+#endif
 
     if (warp == kProducerWarp) {
         if (elect_one()) {
@@ -1246,16 +1273,24 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
 
                 { NTX_TIC(te_wait); mbar_wait(&ctl->s_full[g], own & 1); NTX_TOC(te_wait); }
 #ifdef NTX_TIMELINE
-                if (own == 0 && threadIdx.x == 0) g_ntx_timers[blockIdx.x % 148][0] = clock64() - t_entry;
+                if (own == 0 && threadIdx.x == 0) g_ntx_timers[blockIdx.x % 148][17] = clock64() - t_entry;
 #endif
                 ++own;
                 tc_fence_after();
-                const bool edge = edge_tile(rb, kt, dm) || (rb * 128 + 128 > dm.q_rows);
+                const bool ragged = rb * 128 + 128 > dm.q_rows;
+                const bool edge_any = edge_tile(rb, kt, dm) || ragged;
                 const int self = ntx_self_col(rb * 128 + row_in_tile, dm.n_local, dm.rank);
 #pragma unroll 1
                 for (int ch = 0; ch < 4; ++ch) {
                     uint32_t v[32], pk[16], pk_lo[16];                    // pk_lo: two-term rows only
                     tmem_ld_32x32(taddr + ch * 32, v);
+                    // the masked form only for the 32-key chunks that hold a self column of this warp's rows or run
+                    // past the last key (warp-uniform), and for every chunk of a ragged last row block
+                    bool edge = edge_any;
+                    if (edge_any && !ragged) {
+                        const int c0 = kt * 128 + ch * 32;
+                        edge = c0 + 32 > dm.k_rows || __any_sync(0xffffffffu, self >= c0 && self < c0 + 32);
+                    }
                     tmem_ld_wait_dep(v);
                     if (!edge)
                         coef_chunk<false, kScaled, kSplit>(v, pk, pk_lo, bt + ch * 32, alpha, c1, nc1, 0, 0, 0, true);
@@ -1273,7 +1308,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
             }
             if (last_of_seg) {
 #ifdef NTX_TIMELINE
-                if (i + 1 == n_tiles && threadIdx.x == 0) g_ntx_timers[blockIdx.x % 148][1] = clock64() - t_entry;
+                if (i + 1 == n_tiles && threadIdx.x == 0) g_ntx_timers[blockIdx.x % 148][18] = clock64() - t_entry;
 #endif
                 { NTX_TIC(te_drain); drain(rb, seg); NTX_TOC(te_drain); }
                 ++seg;
@@ -1285,7 +1320,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         NTX_TOC(te_total);
         if (threadIdx.x == 0) { NTX_TSAVE(13, te_total); NTX_TSAVE(14, te_wait); NTX_TSAVE(7, te_drain); }
 #ifdef NTX_TIMELINE
-        if (threadIdx.x == 0) g_ntx_timers[blockIdx.x % 148][2] = clock64() - t_entry;
+        if (threadIdx.x == 0) g_ntx_timers[blockIdx.x % 148][19] = clock64() - t_entry;
 #endif
 
         // ---------------------------------------------------------------- finish: this CTA's share of its row blocks
@@ -1516,8 +1551,8 @@ int ntx_make_rows_tmap(void* map, const void* base, int rows, int ld, int box_ro
 }
 
 #ifdef NTX_TIMING
-extern "C" int ntx_debug_timers(long long* host_out) {   // 148 x 16 cycle counters
-    return cudaMemcpyFromSymbol(host_out, g_ntx_timers, sizeof(long long) * 148 * 16) == cudaSuccess ? 0 : -3;
+extern "C" int ntx_debug_timers(long long* host_out) {   // 148 x 24 cycle counters
+    return cudaMemcpyFromSymbol(host_out, g_ntx_timers, sizeof(long long) * 148 * 24) == cudaSuccess ? 0 : -3;
 }
 #endif
 
