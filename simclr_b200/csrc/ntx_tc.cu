@@ -1,4 +1,6 @@
-// bf16 mode of the fused NT-Xent kernels on the 5th-gen tensor cores (tcgen05).
+// The fused NT-Xent kernels on the 5th-gen tensor cores (tcgen05): bf16 rows, and fp32 inputs held as two bf16
+// terms per value (NTX_BF16X2 rows, the kSplit instantiations: three partial products per similarity, the
+// backward's coefficient tile split the same way -- fp32-grade results at 3x the MMA count).
 //
 // One persistent CTA per SM, warp specialised:
 //   NWG epilogue warpgroups (4 warps each); tile i of the CTA goes to group i % NWG.

@@ -157,3 +157,36 @@ def test_row_scale_is_accepted_only_as_handed_out():
     lay = _cabi.NtxLayout(4, 1, 0, be.row_scale(0.5, torch.bfloat16))
     rc = lib.ntx_fwd(4096, 4096, 8, 8, 8, 8, 0, ctypes.byref(lay), 0.5, 4096, 4096, 4096, 4096, 4096, 1 << 20, None)
     assert rc == -1 and b"row_scale" in lib.ntx_last_error()          # fp32 rows
+
+
+def test_two_term_rows_arguments_are_validated_without_a_device():
+    """NTX_BF16X2 (fp32 values as [hi | lo] bf16 terms): pitch, feature limit, temperature floor and the entry points
+    that do not take the layout answer with an error code and a message before any CUDA call."""
+    lib = _cabi.load()
+    X2 = _cabi.NTX_BF16X2
+    assert lib.ntx_row_pitch(128, X2) == 256 and lib.ntx_row_pitch(1, X2) == 128 and lib.ntx_row_pitch(0, X2) == 0
+    assert abs(lib.ntx_row_scale(0.5, X2) - lib.ntx_row_scale(0.5, _cabi.NTX_BF16)) < 1e-7
+    assert lib.ntx_row_scale(0.01, X2) == 1.0                              # below the fixed-shift range: unit rows
+    # normalise: one term must fit a 128-wide tile, ld is exactly the two-term pitch, rows 16-byte aligned
+    assert lib.ntx_l2norm(4096, 4096, 4, 200, 0, 4096, 512, X2, 4096, 1.0, None) == -1
+    assert b"128" in lib.ntx_last_error()
+    assert lib.ntx_l2norm(4096, 4096, 4, 100, 0, 4096, 128, X2, 4096, 1.0, None) == -1
+    assert b"ntx_row_pitch" in lib.ntx_last_error()
+    assert lib.ntx_l2norm(4096, 4096, 4, 100, 0, 4096 + 8, 256, X2, 4096, 1.0, None) == -1
+    assert b"aligned" in lib.ntx_last_error()
+    p = _cabi.NtxPlan()
+    assert lib.ntx_plan(16, 16, 129, X2, 148, ctypes.byref(p)) == -4
+    assert lib.ntx_plan(16, 16, 128, X2, 148, ctypes.byref(p)) == 0 and p.tensor_cores == 2 and p.d_pad == 128
+    assert lib.ntx_plan(16, 16, 128, 3, 148, ctypes.byref(p)) == -1        # no such rows dtype
+    lay = _cabi.NtxLayout(4, 1, 0)
+    # forward: wrong pitch for the layout, feature limit, temperature below the tensor-core floor
+    rc = lib.ntx_fwd(4096, 4096, 8, 8, 8, 64, X2, ctypes.byref(lay), 0.5, 4096, 4096, 4096, 4096, 4096, 1 << 20, None)
+    assert rc == -1 and b"ntx_row_pitch" in lib.ntx_last_error()
+    rc = lib.ntx_fwd(4096, 4096, 8, 8, 200, 512, X2, ctypes.byref(lay), 0.5, 4096, 4096, 4096, 4096, 4096, 1 << 20, None)
+    assert rc == -4 and b"128" in lib.ntx_last_error()
+    rc = lib.ntx_fwd(4096, 4096, 8, 8, 8, 128, X2, ctypes.byref(lay), 0.01, 4096, 4096, 4096, 4096, 4096, 1 << 20, None)
+    assert rc == -4 and b"temperature" in lib.ntx_last_error()
+    # the rows-backward (Jacobian from the normalised rows) takes fp32 or bf16 rows only
+    rc = lib.ntx_bwd_rows(4096, 4096, 8, 8, 8, 128, X2, ctypes.byref(lay), 0.5, 4096, 4096, 4096, 4096, 0, 0, 1.0, 4096,
+                          4096, 4096, 1 << 20, None)
+    assert rc == -1 and b"dtype" in lib.ntx_last_error()
