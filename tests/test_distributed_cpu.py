@@ -89,3 +89,52 @@ def test_gathered_loss_with_per_rank_row_weights():
         scale = np.abs(ref["dview0"]).max()
         assert np.abs(out[k]["g0"] - ref["dview0"][sl]).max() < 1e-5 * scale
         assert np.abs(out[k]["g1"] - ref["dview1"][sl]).max() < 1e-5 * scale
+
+
+def _worker_two_term(rank, port, n, d, tau, out):
+    _init(rank, port)
+    import simclr_b200.loss as loss_mod
+    from simclr_b200 import _cabi
+    from standin_backend import StandInBackend
+    loss_mod._backend = StandInBackend()
+    loss_mod._require_cuda = lambda t: None
+    seen = []
+    orig = StandInBackend.l2norm
+
+    def spy(self, view0, view1, rows, inv_norm, row_scale=1.0, rows_dtype=None):
+        seen.append((rows_dtype, rows.dtype, tuple(rows.shape)))
+        return orig(self, view0, view1, rows, inv_norm, row_scale, rows_dtype)
+
+    StandInBackend.l2norm = spy
+    g = torch.Generator().manual_seed(9)
+    v0 = torch.randn(n, d, generator=g)
+    v1 = torch.randn(n, d, generator=g) + 0.5 * v0
+    nl = n // WORLD
+    a = v0[rank * nl:(rank + 1) * nl].clone().requires_grad_(True)
+    b = v1[rank * nl:(rank + 1) * nl].clone().requires_grad_(True)
+    loss = loss_mod.NT_Xent(temperature=tau, gather=True)(a, b)
+    loss.backward()
+    out[rank] = {"loss": float(loss.detach()), "g0": a.grad.numpy().copy(), "g1": b.grad.numpy().copy(),
+                 "layout": seen[0][0] is _cabi.BF16X2, "store": seen[0][1] == torch.bfloat16, "shape": seen[0][2]}
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_gathered_fp32_batch_goes_through_two_term_rows():
+    """fp32 inputs with 2048 gathered keys: the module asks for two-term rows (bf16 storage of twice the bf16 pitch),
+    names the layout to every library call, gathers them like any row buffer, and the result keeps fp32 accuracy."""
+    from oracle import ntxent_oracle as orc
+    n, d, tau = 1024, 24, 0.5
+    out = _spawn(_worker_two_term, n, d, tau)
+    g = torch.Generator().manual_seed(9)
+    v0 = torch.randn(n, d, generator=g)
+    v1 = torch.randn(n, d, generator=g) + 0.5 * v0
+    ref = orc.ntxent_rows_fp64(v0.numpy(), v1.numpy(), tau, weights=orc.weights_for("mean", n))
+    nl = n // WORLD
+    scale = max(np.abs(ref["dview0"]).max(), np.abs(ref["dview1"]).max())
+    for k in range(WORLD):
+        assert out[k]["layout"] and out[k]["store"] and out[k]["shape"] == (2 * nl, 128)
+        sl = slice(k * nl, (k + 1) * nl)
+        assert abs(out[k]["loss"] - float(ref["loss"][:, sl].mean())) < 1e-5 * float(ref["loss"].mean())
+        assert np.abs(out[k]["g0"] / WORLD - ref["dview0"][sl]).max() < 1e-5 * scale
+        assert np.abs(out[k]["g1"] / WORLD - ref["dview1"][sl]).max() < 1e-5 * scale
