@@ -44,8 +44,9 @@ extern "C" {
  * kernels then form q.k = hi.lo + lo.hi + hi.hi with fp32 accumulation and split the backward's coefficient
  * tile the same way (C_hi.K_hi + C_hi.K_lo + C_lo.K_hi): fp32-grade results at tensor-core speed for callers whose
  * fp32 batches are large enough for the CUDA-core kernels to matter.  Error against the fp64 oracle, relative to
- * the largest gradient entry: 2e-7 at temperature 0.5, 1e-6 at 0.1, 1e-5 at 0.05 (it grows like 1/temperature; the
- * module uses this layout from temperature 0.1 upwards and the NTX_F32 kernels below).
+ * the largest gradient entry: 2e-7 at temperature 0.5, 1e-6 at 0.1, 1e-5 at 0.05 on random rows; 3e-6 at 0.5 and
+ * 1.4e-5 at 0.1 on tightly clustered rows (cosines near 1).  It grows with 1/temperature; the module uses this layout
+ * from temperature 0.35 upwards and the NTX_F32 kernels below.
  * Every entry point that takes a rows dtype accepts it (ntx_bwd_rows excepted), the peer exchange included. */
 #define NTX_BF16X2 2
 

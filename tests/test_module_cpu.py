@@ -56,7 +56,7 @@ def test_no_cpu_fallback():
 
 def test_rows_layout_choice(monkeypatch):
     """Which rows the module asks the library for (pure host logic): the input dtype, except bf16 outside the
-    tensor-core kernels' range -> fp32 rows, and large fp32 batches at temperature >= 0.1 -> two-term rows."""
+    tensor-core kernels' range -> fp32 rows, and large fp32 batches at temperature >= 0.35 -> two-term rows."""
     import torch
     from simclr_b200 import NT_Xent, _cabi
     from simclr_b200 import loss as loss_mod
@@ -66,7 +66,8 @@ def test_rows_layout_choice(monkeypatch):
     big = loss_mod.FP32_TC_MIN_KEYS
     assert NT_Xent(0.5)._rows_dtype(f32, big) is _cabi.BF16X2
     assert NT_Xent(0.5)._rows_dtype(f32, big - 2) is torch.float32            # small batch: CUDA-core kernels
-    assert NT_Xent(0.09)._rows_dtype(f32, big) is torch.float32               # rounding grows like 1 / temperature
+    assert NT_Xent(0.2)._rows_dtype(f32, big) is torch.float32                # rounding grows like 1 / temperature
+    assert NT_Xent(0.35)._rows_dtype(f32, big) is _cabi.BF16X2
     assert NT_Xent(0.5)._rows_dtype(torch.empty(4, 129), big) is torch.float32    # one term must fit a 128-wide tile
     assert NT_Xent(0.5)._rows_dtype(bf16, big) is torch.bfloat16
     assert NT_Xent(0.5, compute_dtype=torch.bfloat16)._rows_dtype(f32, big) is torch.bfloat16
