@@ -306,8 +306,14 @@ class NT_Xent(torch.nn.Module):
             raise RuntimeError(f"feature sizes differ: {view0.shape[1]} vs {view1.shape[1]}")
         if view0.dtype != view1.dtype or view0.device != view1.device:
             raise RuntimeError("view0 and view1 must share dtype and device")
+        if view0.dtype in (torch.float16, torch.float64):
+            # the reference takes these too (its result has the input dtype); here they are computed through the fp32
+            # path -- more accurate than the reference's fp16 arithmetic, fp32-accurate for fp64 inputs -- with two
+            # differentiable casts around it
+            return self.forward(view0.to(torch.float32), view1.to(torch.float32)).to(view0.dtype)
         if view0.dtype not in (torch.float32, torch.bfloat16):
-            raise TypeError(f"NT_Xent (B200) supports float32 and bfloat16 inputs, got {view0.dtype}")
+            raise TypeError(f"NT_Xent (B200) supports floating-point inputs (float32, bfloat16; float16 and float64 "
+                            f"through float32), got {view0.dtype}")
         _require_cuda(view0)
         if view0.shape[0] < 1 or view0.shape[1] < 1:
             raise RuntimeError("empty batch or feature dimension")
@@ -353,8 +359,11 @@ class NT_Xent(torch.nn.Module):
         """
         if z.dim() != 2 or z.shape[0] % 2 != 0 or z.shape[0] < 2 or z.shape[1] < 1:
             raise RuntimeError(f"forward_cat expects one (2N, D) tensor, got {tuple(z.shape)}")
+        if z.dtype in (torch.float16, torch.float64):          # as in forward: through the fp32 path
+            return self.forward_cat(z.to(torch.float32)).to(z.dtype)
         if z.dtype not in (torch.float32, torch.bfloat16):
-            raise TypeError(f"NT_Xent (B200) supports float32 and bfloat16 inputs, got {z.dtype}")
+            raise TypeError(f"NT_Xent (B200) supports floating-point inputs (float32, bfloat16; float16 and float64 "
+                            f"through float32), got {z.dtype}")
         _require_cuda(z)
         world, rank, group = 1, 0, None
         if self.gather and dist.is_available() and dist.is_initialized():

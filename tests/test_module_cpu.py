@@ -45,8 +45,34 @@ def test_shape_and_dtype_errors():
         m(torch.randn(4, 8), torch.randn(4, 9))
     with pytest.raises(RuntimeError):
         m(torch.randn(2, 4, 8), torch.randn(2, 4, 8))
-    with pytest.raises(TypeError):
+    with pytest.raises(TypeError):               # not a floating-point batch
+        m(torch.ones(4, 8, dtype=torch.int64), torch.ones(4, 8, dtype=torch.int64))
+    with pytest.raises(RuntimeError, match="no CPU path"):      # float64 / float16 are taken (through fp32): CUDA only
         m(torch.randn(4, 8).double(), torch.randn(4, 8).double())
+
+
+def test_float64_and_float16_inputs_go_through_the_fp32_path(monkeypatch):
+    """The reference returns the input dtype for float64 / float16 batches; so does the module,
+    computing in fp32 with differentiable casts around the call (checked here with the CPU stand-in for the kernels)."""
+    import numpy as np
+    import simclr_b200.loss as loss_mod
+    from oracle import ntxent_oracle as orc
+    from standin_backend import StandInBackend
+    monkeypatch.setattr(loss_mod, "_backend", StandInBackend())
+    monkeypatch.setattr(loss_mod, "_require_cuda", lambda t: None)
+    g = torch.Generator().manual_seed(3)
+    v0, v1 = torch.randn(24, 16, generator=g), torch.randn(24, 16, generator=g)
+    for dtype, tol in ((torch.float64, 1e-6), (torch.float16, 2e-3)):
+        a, b = v0.to(dtype).requires_grad_(True), v1.to(dtype).requires_grad_(True)
+        ref = orc.ntxent_rows_fp64(a.detach().double().numpy(), b.detach().double().numpy(), 0.5,
+                                   weights=orc.weights_for("mean", 24))
+        loss = NT_Xent(0.5)(a, b)
+        assert loss.dtype == dtype and loss.dim() == 0
+        loss.backward()
+        assert a.grad.dtype == dtype and abs(float(loss.detach()) - ref["loss"].mean()) < tol * ref["loss"].mean()
+        assert np.abs(a.grad.double().numpy() - ref["dview0"]).max() < tol * np.abs(ref["dview0"]).max() + 1e-4 * (dtype == torch.float16)
+        rows = NT_Xent(0.5, "none").forward_cat(torch.cat([a.detach(), b.detach()]))
+        assert rows.dtype == dtype and rows.shape == (2, 24)
 
 
 def test_no_cpu_fallback():
