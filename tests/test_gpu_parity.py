@@ -873,3 +873,23 @@ def test_integration_md_ctypes_stub_runs(dev):
     ref = orc.ntxent_rows_fp64(a.numpy(), b.numpy(), 0.5)
     assert rel_err(loss.cpu().numpy(), orc.reduce_rows(ref["loss"], "mean")) < FP32_TOL
     del keep
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float64, FP32_TOL), (torch.float16, 2e-3)])
+def test_float64_and_float16_inputs_on_device(dtype, tol, dev):
+    """The reference returns the input dtype for float64 / float16 batches; the module does too, through its fp32
+    path (for float16 that is more accurate than the reference's own half-precision arithmetic)."""
+    from simclr_b200 import NT_Xent
+    g = torch.Generator().manual_seed(41)
+    a = torch.randn(200, 48, generator=g).to(dtype)
+    b = torch.randn(200, 48, generator=g).to(dtype)
+    ref = orc.ntxent_rows_fp64(a.double().numpy(), b.double().numpy(), 0.5, weights=orc.weights_for("mean", 200))
+    ta, tb = a.to(dev).requires_grad_(True), b.to(dev).requires_grad_(True)
+    loss = NT_Xent(0.5)(ta, tb)
+    loss.backward()
+    assert loss.dtype == dtype and ta.grad.dtype == dtype
+    assert rel_err(loss.detach().double().cpu().numpy(), ref["loss"].mean()) < tol
+    scale = np.abs(ref["dview0"]).max()
+    slack = 1e-4 * scale if dtype == torch.float16 else 0.0        # the float16 gradient itself is rounded to 11 bits
+    assert np.abs(ta.grad.double().cpu().numpy() - ref["dview0"]).max() < tol * scale + slack
+    assert NT_Xent(0.5, "none")(ta.detach(), tb.detach()).dtype == dtype
