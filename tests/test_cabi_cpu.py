@@ -190,3 +190,33 @@ def test_two_term_rows_arguments_are_validated_without_a_device():
     rc = lib.ntx_bwd_rows(4096, 4096, 8, 8, 8, 128, X2, ctypes.byref(lay), 0.5, 4096, 4096, 4096, 4096, 0, 0, 1.0, 4096,
                           4096, 4096, 1 << 20, None)
     assert rc == -1 and b"dtype" in lib.ntx_last_error()
+
+
+def test_plan_invariants_fuzzed():
+    """ntx_plan over random shapes, rank counts, SM counts and all three rows layouts: the tile partition covers every
+    tile once, slot counts bound the CTAs sharing a row block, the scratch sizes cover the slots."""
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=150, deadline=None)
+    @given(n_local=st.integers(1, 3000), world=st.integers(1, 8), d=st.integers(1, 256), kind=st.integers(0, 2),
+           sms=st.integers(1, 160))
+    def check(n_local, world, d, kind, sms):
+        dtype = (torch.float32, torch.bfloat16, _cabi.BF16X2)[kind]
+        if dtype is _cabi.BF16X2 and d > 128:
+            with pytest.raises(_cabi.NtxError):
+                _cabi.Backend().plan(2 * n_local, 2 * n_local * world, d, dtype, sms)
+            return
+        q_rows, k_rows = 2 * n_local, 2 * n_local * world
+        p = _cabi.Backend().plan(q_rows, k_rows, d, dtype, sms)
+        assert p.row_blocks == -(-q_rows // p.tile_rows) and p.key_tiles == -(-k_rows // p.tile_keys)
+        T, G = p.row_blocks * p.key_tiles, p.grid
+        assert 1 <= G <= min(T, sms * (1 if p.tensor_cores else 2))
+        slots = max(owner(T, G, rb * p.key_tiles + p.key_tiles - 1) - owner(T, G, rb * p.key_tiles) + 1
+                    for rb in range(p.row_blocks))
+        assert p.max_slots == slots
+        rows_pad = p.row_blocks * p.tile_rows
+        assert p.fwd_ws_bytes >= p.fwd_ws_bytes_min >= slots * rows_pad * 4
+        assert p.bwd_ws_bytes >= slots * rows_pad * p.d_pad * 4
+        assert p.d_pad >= d and (p.fwd_symmetric == 0 or (p.tensor_cores == 1 and world == 1 and p.d_pad <= 128))
+
+    check()
