@@ -3,6 +3,10 @@
     NTXENT_B200_LIB=simclr_b200/libntxent_b200_timing.so python tools/timers.py [n] [d] [world]
 
 world > 1: the shapes of one rank of `world` (its 2n/world rows against all 2n keys), run on this one GPU.
+
+NTX_TIMELINE=1 also prints per-CTA stamps (cycles from kernel entry) of a build with both defines:
+    python -c "import os, simclr_b200.build as b; b.build(force=True, defines=('NTX_TIMING', 'NTX_TIMELINE'), \
+               out=os.path.join(b.PKG, 'libntxent_b200_timeline.so'))"
 """
 import ctypes
 import os
